@@ -1,0 +1,116 @@
+/*
+ * flatip_b200.h -- C ABI of the B200-native exact flat inner-product search library
+ * (libflatip_b200.so).  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * The library is the drop-in for the ONE native call on the reference's retrieval hot path:
+ *
+ *     distances, indices = self._index.search(embeddings, k)
+ *         /root/reference/src/pipeline/components/faiss_store.py:152   (also the warm-up, :106)
+ *
+ * i.e. faiss-cpu's SWIG entry IndexFlatIP.search(n, x, k, distances, labels), plus the pieces of
+ * the faiss.Index surface the reference touches around it (read_index -> fip_create + fip_add_*,
+ * index.ntotal -> fip_ntotal; faiss_store.py:66-69,73,182).  Each entry point below names the
+ * reference interface it replaces.  All functions return 0 on success or a negative fip_status;
+ * fip_last_error() returns a thread-local message for the last failure on the calling thread.
+ * Every function is safe to call from several host threads at once; calls on the same index are
+ * serialised internally (the reference calls search from a thread pool,
+ * /root/reference/src/pipeline/services/retrieval/api.py:348-349).
+ */
+#ifndef FLATIP_B200_H_
+#define FLATIP_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fip_index fip_index;
+
+enum fip_dtype { FIP_F32 = 0, FIP_F16 = 1, FIP_BF16 = 2 };
+
+enum fip_status {
+    FIP_OK = 0,
+    FIP_ERR_INVALID = -1,   /* bad argument (shape, k, dtype, null pointer)            */
+    FIP_ERR_CUDA = -2,      /* a CUDA call or kernel failed; see fip_last_error()        */
+    FIP_ERR_NOMEM = -3,     /* device or host allocation failed                           */
+    FIP_ERR_NODEVICE = -4,  /* no usable sm_100 device -- there is NO CPU fallback        */
+    FIP_ERR_STATE = -5      /* call not valid in the index's current state                */
+};
+
+enum fip_variant {
+    FIP_VARIANT_AUTO = 0,    /* chosen from arithmetic intensity (batch, dtype)           */
+    FIP_VARIANT_STREAM = 1,  /* K2: 128-bit vectorised CUDA-core streaming scan           */
+    FIP_VARIANT_TENSOR = 2   /* K1: TMA + tcgen05/TMEM GEMM with fused threshold filter   */
+};
+
+typedef struct fip_config {
+    int32_t dim;           /* vector dimension (faiss Index::d; settings.faiss_dim)      */
+    int32_t dtype;         /* storage dtype of the corpus: fip_dtype                     */
+    int32_t device;        /* CUDA device ordinal                                        */
+    int32_t reserved;
+    int64_t capacity_rows; /* rows to reserve up front (0 = grow on add)                 */
+    int64_t id_base;       /* global id of local row 0 (row-sharded corpora)             */
+} fip_config;
+
+/* faiss.read_index / IndexFlatIP(d) constructor  (faiss_store.py:66-69). */
+int fip_create(const fip_config* cfg, fip_index** out);
+/* FAISSStore.unload -> index destruction (faiss_store.py:160-171). */
+void fip_destroy(fip_index* idx);
+
+/* faiss Index::add(n, x): append n fp32 host rows, rounded (RNE) to the storage dtype. */
+int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n);
+/* Same, rows already on the device in `dtype` (fp32 is converted, equal dtypes are copied). */
+int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtype);
+/* Append n synthetic rows generated on the device: global rows [global_row0, global_row0+n) of
+ * the Philox corpus defined in rag-inference-pipeline_b200/synthetic.py (stands in for
+ * /root/reference/scripts/create_test_docs.py:87-96). */
+int fip_add_synthetic(fip_index* idx, int64_t n, uint64_t seed, int64_t global_row0);
+/* Drop all rows (keeps the allocation). */
+int fip_reset(fip_index* idx);
+/* faiss Index::reconstruct_n: copy rows [row0, row0+n) to the host, widened to fp32. */
+int fip_reconstruct(fip_index* idx, int64_t row0, int64_t n, float* out_host);
+
+/* faiss Index::ntotal (faiss_store.py:73,182). */
+int64_t fip_ntotal(const fip_index* idx);
+int32_t fip_dim(const fip_index* idx);
+int32_t fip_dtype_of(const fip_index* idx);
+
+/*
+ * faiss IndexFlatIP::search(n, x, k, distances, labels)  (faiss_store.py:152).
+ * queries: host fp32 [nq, dim] row-major; distances: host fp32 [nq, k]; ids: host int64 [nq, k].
+ * Each row is best-first under (score descending, id ascending); unfilled slots hold
+ * -FLT_MAX / -1 like faiss.  Blocking; host<->device copies are done inside the call.
+ */
+int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, float* distances,
+               int64_t* ids);
+/* Same contract with device-resident buffers (fp32 queries, fp32 distances, int64 ids) and a
+ * caller-supplied cudaStream_t (0 = the index's own stream).  Blocking on that stream. */
+int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
+                      float* distances_dev, int64_t* ids_dev, void* cuda_stream);
+
+/*
+ * Cross-shard merge (K3): in_d / in_i are device buffers [g, nq, k_in] as an all-gather of the
+ * per-shard search results leaves them (shard r holds lower ids than shard r+1); writes the
+ * global best k_out per query to out_d / out_i [nq, k_out].  No faiss-cpu equivalent in the
+ * reference (single process); it is what IndexShards::search does in upstream faiss.
+ */
+int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int32_t g, int64_t nq,
+                     int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream);
+
+/* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
+ * streaming kernel for 16-bit storage), "force_safe_mode" (0/1, testing the overflow fallback). */
+int fip_set_option(fip_index* idx, const char* key, int64_t value);
+/* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
+ * "candidate_capacity"; cumulative: "total_launches", "total_searches". */
+int64_t fip_get_stat(const fip_index* idx, const char* key);
+
+const char* fip_last_error(void);
+/* Library/ABI version, and the SM architecture the kernels were compiled for (100). */
+int32_t fip_abi_version(void);
+int32_t fip_compiled_sm(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLATIP_B200_H_ */

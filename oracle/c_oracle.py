@@ -1,0 +1,110 @@
+"""ctypes loader for oracle/faiss_flat_restatement.c -- TEST INFRASTRUCTURE ONLY.
+
+Used by tests, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl reference``
+legs.  Never imported by the product package.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import glob
+import os
+import subprocess
+
+import numpy as np
+
+# Same policy the reference sets before faiss spins up its OpenMP pool
+# (/root/reference/src/pipeline/runtime.py:51); without it libgomp's spinning workers starve the
+# BLAS threads and the sgemm path runs ~30x slower.
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_build", "libflatip_oracle.so")
+_lib = None
+_sgemm_ptr = None
+_blas_handle = None
+
+
+def build(force: bool = False) -> str:
+    src = os.path.join(_HERE, "faiss_flat_restatement.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.run(["make", "-C", _HERE, "-B" if force else "-s"], check=True)
+    return _LIB_PATH
+
+
+def _find_openblas_sgemm():
+    """Fortran-ABI ILP64 sgemm from the OpenBLAS that numpy bundles (scipy_sgemm_64_)."""
+    global _sgemm_ptr, _blas_handle
+    if _sgemm_ptr is not None:
+        return _sgemm_ptr
+    libdir = os.path.join(os.path.dirname(np.__file__), "..", "numpy.libs")
+    for path in sorted(glob.glob(os.path.join(libdir, "libscipy_openblas64_*.so"))):
+        try:
+            h = ctypes.CDLL(path)
+            fn = getattr(h, "scipy_sgemm_64_")
+        except (OSError, AttributeError):
+            continue
+        _blas_handle = h
+        _sgemm_ptr = ctypes.cast(fn, ctypes.c_void_p)
+        return _sgemm_ptr
+    _sgemm_ptr = ctypes.c_void_p(None)
+    return _sgemm_ptr
+
+
+def load():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.oracle_knn_inner_product.restype = ctypes.c_int
+        _lib.oracle_knn_inner_product.argtypes = [
+            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64,
+            ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+            ctypes.c_int]
+        _lib.oracle_max_threads.restype = ctypes.c_int
+        _lib.oracle_synthetic_rows.restype = ctypes.c_int
+        _lib.oracle_synthetic_rows.argtypes = [
+            ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_uint64,
+            ctypes.c_uint32, ctypes.c_int]
+    return _lib
+
+
+def has_blas() -> bool:
+    return bool(_find_openblas_sgemm().value)
+
+
+def max_threads() -> int:
+    return int(load().oracle_max_threads())
+
+
+def knn_inner_product(queries: np.ndarray, corpus: np.ndarray, k: int, *, id_base: int = 0,
+                      nthreads: int = 0, use_blas: bool = True):
+    """faiss-style CPU flat-IP search (fp32).  Returns (D float32 [B,k], I int64 [B,k])."""
+    lib = load()
+    q = np.ascontiguousarray(queries, dtype=np.float32)
+    x = np.ascontiguousarray(corpus, dtype=np.float32)
+    if q.ndim != 2 or x.ndim != 2 or q.shape[1] != x.shape[1]:
+        raise ValueError("shape mismatch")
+    B, d = q.shape
+    D = np.empty((B, k), dtype=np.float32)
+    I = np.empty((B, k), dtype=np.int64)
+    sg = _find_openblas_sgemm() if use_blas else ctypes.c_void_p(None)
+    rc = lib.oracle_knn_inner_product(q.ctypes.data, x.ctypes.data, d, B, x.shape[0], k, id_base,
+                                      D.ctypes.data, I.ctypes.data, sg, int(nthreads))
+    if rc != 0:
+        raise RuntimeError(f"oracle_knn_inner_product failed: {rc}")
+    return D, I
+
+
+_STORAGE = {"f32": 0, "f16": 1, "bf16": 2}
+
+
+def synthetic_corpus(row0: int, nrows: int, dim: int, dtype: str = "f32", seed: int = 1234,
+                     stream: int = 0) -> np.ndarray:
+    """Fast C restatement of ``synthetic.synthetic_corpus`` (same bits), for big test corpora."""
+    out = np.empty((nrows, dim), dtype=np.float32)
+    rc = load().oracle_synthetic_rows(out.ctypes.data, row0, nrows, dim, seed, stream,
+                                      _STORAGE[dtype])
+    if rc != 0:
+        raise RuntimeError("oracle_synthetic_rows failed")
+    return out

@@ -1,0 +1,25 @@
+"""B200-native exact flat inner-product retrieval (drop-in for the reference's FAISS hot path).
+
+Public surface:
+  B200FlatIPStore            component with the reference FAISSStore's interface (store.py)
+  create_b200_flat_ip_store  factory with the reference's (settings, config) signature
+  install                    registers the factory under "faiss" / "faiss_store"
+  FlatIPIndex                faiss.Index-like wrapper over the C ABI (one GPU, one shard)
+  ShardedFlatIPSearcher      row-sharded search across torch.distributed ranks (NCCL + K3 merge)
+"""
+
+from .factory import COMPONENT_TYPE, create_b200_flat_ip_store, install
+from .index import FlatIPIndex, merge_device
+from .store import B200FlatIPStore
+
+__all__ = [
+    "B200FlatIPStore", "FlatIPIndex", "ShardedFlatIPSearcher", "COMPONENT_TYPE",
+    "create_b200_flat_ip_store", "install", "merge_device",
+]
+
+
+def __getattr__(name):
+    if name == "ShardedFlatIPSearcher":  # torch is only imported when the sharded path is used
+        from .sharded import ShardedFlatIPSearcher
+        return ShardedFlatIPSearcher
+    raise AttributeError(name)

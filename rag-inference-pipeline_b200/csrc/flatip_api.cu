@@ -1,0 +1,736 @@
+// C ABI (include/flatip_b200.h) and host-side orchestration of the B200 flat-IP search.
+//
+// A search is a short sequence of launches on one stream:
+//   prepare queries -> [ scan phase p over rows [r_p, r_p+1)  ->  select/compact ] x P -> outputs
+// The scan kernels (K1 tensor-core / K2 streaming) only FILTER: a score survives when it beats the
+// query's running threshold (the k-th best score over all earlier phases) and is appended to that
+// query's candidate list.  The select kernel (K3) then keeps the k best and publishes the new
+// threshold.  Phase lengths grow geometrically (the expected number of survivors of a phase of m
+// rows after n rows is k*m/n), so a 12.5 M-row shard needs 4 phases at k = 100.  If a list ever
+// overflows (adversarial row order), the affected queries are redone in "safe mode", whose phases
+// are too short to overflow by construction -- results are exact for every input.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
+#include "../../include/flatip_b200.h"
+#include "common.cuh"
+#include "select.cuh"
+#include "stream_scan.cuh"
+#include "synthetic.cuh"
+#include "tc_scan.cuh"
+
+using namespace fip;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define FIP_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            cudaGetLastError();                                                              \
+            return fail(_e == cudaErrorMemoryAllocation ? FIP_ERR_NOMEM : FIP_ERR_CUDA,      \
+                        std::string(#expr) + ": " + cudaGetErrorString(_e));                 \
+        }                                                                                    \
+    } while (0)
+
+constexpr int kMaxK = 2048;
+constexpr int kMaxCap = 16384;  // select kernel sorts a whole list in shared memory (128 KB)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t ensure(size_t want) {
+        if (want <= n) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) n = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+template <typename T>
+struct PinnedBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t ensure(size_t want) {
+        if (want <= n) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        n = 0;
+        cudaError_t e = cudaMallocHost((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) n = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) !=
+                cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// 2-D K-major tile map: inner dim = `dim` elements of a 16-bit type, outer dim = rows.
+int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t rows, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)dim * 2};
+    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUtensorMapDataType dt =
+        dtype == kBF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    CUresult r = enc(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return FIP_OK;
+}
+
+__global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* overflow, int nq) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nq) { thr[i] = kNegInf; cnt[i] = 0u; }
+    if (i <= nq) overflow[i] = 0u;
+}
+__global__ void fill_u32_kernel(uint32_t* p, uint32_t v, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+__global__ void fill_padding_kernel(float* d, int64_t* id, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) { d[i] = kLowestF32; id[i] = -1; }
+}
+// dst rows[sel[j]] = src rows[j]
+__global__ void gather_rows_f32_kernel(const float* src, const int* sel, float* dst, int nsel, int width) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < (int64_t)nsel * width) {
+        int j = (int)(i / width), c = (int)(i - (int64_t)j * width);
+        dst[i] = src[(size_t)sel[j] * width + c];
+    }
+}
+__global__ void scatter_results_kernel(const float* sd, const int64_t* si, const int* sel, float* dd,
+                                       int64_t* di, int nsel, int k) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < (int64_t)nsel * k) {
+        int j = (int)(i / k), c = (int)(i - (int64_t)j * k);
+        dd[(size_t)sel[j] * k + c] = sd[i];
+        di[(size_t)sel[j] * k + c] = si[i];
+    }
+}
+
+}  // namespace
+
+struct fip_index {
+    fip_config cfg{};
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    void* corpus = nullptr;
+    int64_t n_rows = 0;
+    int64_t cap_rows = 0;
+    std::mutex mu;
+
+    // options
+    int variant = FIP_VARIANT_AUTO;
+    int stream_max_batch = 4;
+    int force_safe = 0;
+
+    // per-search workspace
+    DevBuf<float> thr, q_scale, q32, out_d;
+    DevBuf<uint32_t> cnt, overflow;
+    DevBuf<uint64_t> cand;
+    DevBuf<__half> q16;
+    DevBuf<int64_t> out_i;
+    DevBuf<int> sel;
+    DevBuf<float> sub_q, sub_d;
+    DevBuf<int64_t> sub_i;
+    PinnedBuf<float> h_q, h_d;
+    PinnedBuf<int64_t> h_i;
+    PinnedBuf<uint32_t> h_flags;
+    DevBuf<float> add_stage;
+
+    CUtensorMap tmap_x{};
+    bool tmap_x_valid = false;
+
+    // stats
+    int64_t st_launches = 0, st_variant = 0, st_phases = 0, st_overflow = 0, st_cap = 0;
+    int64_t st_total_launches = 0, st_total_searches = 0;
+
+    size_t row_bytes() const { return (size_t)cfg.dim * dtype_size(cfg.dtype); }
+};
+
+namespace {
+
+int use_device(const fip_index* idx) {
+    FIP_CUDA(cudaSetDevice(idx->cfg.device));
+    return FIP_OK;
+}
+
+int reserve_rows(fip_index* idx, int64_t want) {
+    if (want <= idx->cap_rows) return FIP_OK;
+    int64_t new_cap = std::max<int64_t>(want, idx->cap_rows + idx->cap_rows / 2);
+    void* p = nullptr;
+    FIP_CUDA(cudaMalloc(&p, (size_t)new_cap * idx->row_bytes()));
+    if (idx->corpus) {
+        cudaError_t e = cudaMemcpyAsync(p, idx->corpus, (size_t)idx->n_rows * idx->row_bytes(),
+                                        cudaMemcpyDeviceToDevice, idx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(idx->stream);
+        if (e != cudaSuccess) { cudaFree(p); FIP_CUDA(e); }
+        cudaFree(idx->corpus);
+    }
+    idx->corpus = p;
+    idx->cap_rows = new_cap;
+    idx->tmap_x_valid = false;
+    return FIP_OK;
+}
+
+int cap_for_k(int k, bool safe) {
+    if (safe) return kMaxCap;
+    int cap = std::max(4096, 16 * next_pow2(k));
+    return std::min(cap, kMaxCap);
+}
+
+struct SearchCtx {
+    fip_index* idx;
+    cudaStream_t stream;
+    int launches = 0;
+};
+
+template <typename T, int QB, int R>
+int launch_stream_pass(SearchCtx& c, const ScanArgs& a, const float* q32, int q0) {
+    fip_index* idx = c.idx;
+    auto kern = stream_scan_kernel<T, QB, R>;
+    size_t smem = (size_t)QB * a.dim * sizeof(float);
+    FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    FIP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+    per_sm = std::max(1, std::min(per_sm, 4));
+    int64_t groups = ((int64_t)(a.row_end - a.row_begin) + R - 1) / R;
+    int grid = (int)std::min<int64_t>((int64_t)idx->num_sms * per_sm, (groups + 7) / 8);
+    grid = std::max(grid, 1);
+    kern<<<grid, 256, smem, c.stream>>>(a, q32, q0);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    return FIP_OK;
+}
+
+template <typename T>
+int launch_stream_phase(SearchCtx& c, const ScanArgs& a, const float* q32) {
+    const int max_qb_smem = (int)((220 * 1024) / ((size_t)a.dim * sizeof(float)));
+    if (max_qb_smem < 1) return fail(FIP_ERR_INVALID, "dim too large for the streaming kernel");
+    for (int q0 = 0; q0 < a.nq;) {
+        int rem = a.nq - q0;
+        int qb = rem >= 16 ? 16 : next_pow2(rem);
+        while (qb > max_qb_smem) qb >>= 1;
+        int rc;
+        switch (qb) {
+            case 1: rc = launch_stream_pass<T, 1, 8>(c, a, q32, q0); break;
+            case 2: rc = launch_stream_pass<T, 2, 8>(c, a, q32, q0); break;
+            case 4: rc = launch_stream_pass<T, 4, 8>(c, a, q32, q0); break;
+            case 8: rc = launch_stream_pass<T, 8, 4>(c, a, q32, q0); break;
+            default: rc = launch_stream_pass<T, 16, 4>(c, a, q32, q0); qb = 16; break;
+        }
+        if (rc) return rc;
+        q0 += qb;
+    }
+    return FIP_OK;
+}
+
+int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int nq_pad) {
+    fip_index* idx = c.idx;
+    const int n_qtiles = nq_pad / tc::BM;
+    const int64_t n_ctiles = ((int64_t)(a.row_end - a.row_begin) + tc::BN - 1) / tc::BN;
+    int grid = (int)std::min<int64_t>(idx->num_sms, n_ctiles * n_qtiles);
+    if (a.dtype == kBF16) {
+        auto kern = tc::tc_scan_kernel<1>;
+        FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        kern<<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(tmap_q, idx->tmap_x, a, n_qtiles);
+    } else {
+        auto kern = tc::tc_scan_kernel<0>;
+        FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
+        kern<<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(tmap_q, idx->tmap_x, a, n_qtiles);
+    }
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    return FIP_OK;
+}
+
+int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
+                  int64_t* out_i, const float* out_scale) {
+    SelectArgs s{};
+    s.cand = idx->cand.p; s.cnt = idx->cnt.p; s.thr = idx->thr.p; s.cap = (uint32_t)cap; s.k = k;
+    s.final_pass = final_pass ? 1 : 0; s.out_d = out_d; s.out_i = out_i; s.id_base = idx->cfg.id_base;
+    s.out_scale = out_scale; s.overflow = idx->overflow.p;
+    size_t smem = (size_t)cap * sizeof(uint64_t);
+    FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    int threads = std::min(1024, std::max(64, cap / 2));
+    select_topk_kernel<<<nq, threads, smem, c.stream>>>(s);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    return FIP_OK;
+}
+
+// One complete search of `nq` device-resident fp32 queries; results to device out_d / out_i.
+// Does not synchronise.  safe: phases short enough that a list can never overflow.
+int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
+               bool safe, int* variant_used, int* phases_used, int* cap_used) {
+    fip_index* idx = c.idx;
+    const int64_t n = idx->n_rows;
+    const int dim = idx->cfg.dim;
+    if (n == 0) {
+        int64_t tot = (int64_t)nq * k;
+        fill_padding_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c.stream>>>(out_d, out_i, tot);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+        *variant_used = 0; *phases_used = 0; *cap_used = 0;
+        return FIP_OK;
+    }
+    const int cap = cap_for_k(k, safe);
+    FIP_CUDA(idx->thr.ensure(nq));
+    FIP_CUDA(idx->cnt.ensure(nq));
+    FIP_CUDA(idx->overflow.ensure((size_t)nq + 1));
+    FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
+
+    int variant = idx->variant;
+    const bool tc_ok = idx->cfg.dtype != kF32 && dim % tc::BK == 0;
+    if (variant == FIP_VARIANT_AUTO)
+        // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
+        // CUDA-core kernel stays HBM-bound only while nq * dim FMAs per row fit under the FP32 pipe
+        // (nq <= ~4 for 16-bit storage); above that the tensor pipe is needed to stay on the HBM
+        // roof, and above ~210 flop/byte (nq > ~210) the tensor pipe itself is the roof.
+        variant = (tc_ok && nq > idx->stream_max_batch) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
+    if (variant == FIP_VARIANT_TENSOR && !tc_ok)
+        return fail(FIP_ERR_INVALID,
+                    "tensor-core variant needs fp16/bf16 storage and dim % 64 == 0");
+
+    init_lists_kernel<<<(nq + 256) / 256, 256, 0, c.stream>>>(idx->thr.p, idx->cnt.p, idx->overflow.p, nq);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+
+    CUtensorMap tmap_q{};
+    int nq_pad = 0;
+    const float* out_scale = nullptr;
+    if (variant == FIP_VARIANT_TENSOR) {
+        nq_pad = (nq + tc::BM - 1) / tc::BM * tc::BM;
+        FIP_CUDA(idx->q16.ensure((size_t)nq_pad * dim));
+        FIP_CUDA(idx->q_scale.ensure(nq));
+        tc::prepare_queries_f16_kernel<<<(nq_pad + 7) / 8, 256, 0, c.stream>>>(
+            q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+        int rc = make_tmap(&tmap_q, idx->q16.p, kF16, dim, (uint64_t)nq_pad, tc::BM);
+        if (rc) return rc;
+        if (!idx->tmap_x_valid) {
+            rc = make_tmap(&idx->tmap_x, idx->corpus, idx->cfg.dtype, dim, (uint64_t)n, tc::BN);
+            if (rc) return rc;
+            idx->tmap_x_valid = true;
+        }
+        out_scale = idx->q_scale.p;
+    }
+
+    ScanArgs a{};
+    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.dtype = idx->cfg.dtype; a.nq = nq;
+    a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
+
+    auto scan = [&](int64_t r0, int64_t r1, bool dense) -> int {
+        a.row_begin = (uint32_t)r0; a.row_end = (uint32_t)r1; a.dense = dense ? 1 : 0;
+        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, nq_pad);
+        switch (idx->cfg.dtype) {
+            case kF32: return launch_stream_phase<float>(c, a, q32);
+            case kF16: return launch_stream_phase<__half>(c, a, q32);
+            default: return launch_stream_phase<__nv_bfloat16>(c, a, q32);
+        }
+    };
+
+    const int keff = std::max(k, 16);
+    const double growth = std::max(2.0, ((double)cap / 2 - keff) / keff);
+    int phases = 0;
+    // phase 0: no threshold yet, every score of the first rows is written (slot = row)
+    int64_t m = std::min<int64_t>(n, cap);
+    int rc = scan(0, m, true);
+    if (rc) return rc;
+    fill_u32_kernel<<<(nq + 255) / 256, 256, 0, c.stream>>>(idx->cnt.p, (uint32_t)m, nq);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    int64_t pos = m;
+    phases++;
+    rc = launch_select(c, idx, nq, k, cap, pos == n, out_d, out_i, out_scale);
+    if (rc) return rc;
+    while (pos < n) {
+        if (safe) m = std::max<int64_t>(256, (int64_t)(cap - k) / 256 * 256);
+        else m = std::max<int64_t>(256, (int64_t)((double)pos * growth) / 256 * 256);
+        m = std::min<int64_t>(m, n - pos);
+        rc = scan(pos, pos + m, false);
+        if (rc) return rc;
+        pos += m;
+        phases++;
+        rc = launch_select(c, idx, nq, k, cap, pos == n, out_d, out_i, out_scale);
+        if (rc) return rc;
+    }
+    *variant_used = variant; *phases_used = phases; *cap_used = cap;
+    return FIP_OK;
+}
+
+// Search + overflow check + safe-mode redo of overflowed queries.  Synchronises the stream.
+int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
+                   cudaStream_t stream) {
+    SearchCtx c{idx, stream};
+    int variant = 0, phases = 0, cap = 0;
+    int rc = run_search(c, q32, nq, k, out_d, out_i, idx->force_safe != 0, &variant, &phases, &cap);
+    if (rc) return rc;
+    int n_over = 0;
+    if (idx->n_rows > 0) {
+        FIP_CUDA(idx->h_flags.ensure((size_t)nq + 1));
+        FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p, idx->overflow.p, sizeof(uint32_t) * ((size_t)nq + 1),
+                                 cudaMemcpyDeviceToHost, stream));
+    }
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    if (idx->n_rows > 0 && idx->h_flags.p[0]) {
+        std::vector<int> sel;
+        for (int q = 0; q < nq; ++q)
+            if (idx->h_flags.p[1 + q]) sel.push_back(q);
+        n_over = (int)sel.size();
+        FIP_CUDA(idx->sel.ensure(sel.size()));
+        FIP_CUDA(idx->sub_q.ensure(sel.size() * (size_t)idx->cfg.dim));
+        FIP_CUDA(idx->sub_d.ensure(sel.size() * (size_t)k));
+        FIP_CUDA(idx->sub_i.ensure(sel.size() * (size_t)k));
+        FIP_CUDA(cudaMemcpyAsync(idx->sel.p, sel.data(), sel.size() * sizeof(int),
+                                 cudaMemcpyHostToDevice, stream));
+        int64_t tot = (int64_t)n_over * idx->cfg.dim;
+        gather_rows_f32_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(
+            q32, idx->sel.p, idx->sub_q.p, n_over, idx->cfg.dim);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+        int v2, p2, c2;
+        rc = run_search(c, idx->sub_q.p, n_over, k, idx->sub_d.p, idx->sub_i.p, true, &v2, &p2, &c2);
+        if (rc) return rc;
+        tot = (int64_t)n_over * k;
+        scatter_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(
+            idx->sub_d.p, idx->sub_i.p, idx->sel.p, out_d, out_i, n_over, k);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+        FIP_CUDA(cudaStreamSynchronize(stream));  // sel (host vector) must outlive the H2D copy
+        phases += p2;
+    }
+    idx->st_launches = c.launches; idx->st_variant = variant; idx->st_phases = phases;
+    idx->st_overflow = n_over; idx->st_cap = cap;
+    idx->st_total_launches += c.launches; idx->st_total_searches++;
+    return FIP_OK;
+}
+
+int check_search_args(const fip_index* idx, const void* q, int64_t nq, int32_t k, const void* d,
+                      const void* i) {
+    if (!idx) return fail(FIP_ERR_INVALID, "null index");
+    if (nq < 0 || nq > (1 << 20)) return fail(FIP_ERR_INVALID, "nq out of range");
+    if (k < 1 || k > kMaxK) return fail(FIP_ERR_INVALID, "k must be in [1, 2048]");
+    if (nq > 0 && (!q || !d || !i)) return fail(FIP_ERR_INVALID, "null buffer");
+    return FIP_OK;
+}
+
+}  // namespace
+
+// ================================================================================= C ABI
+extern "C" {
+
+int fip_create(const fip_config* cfg, fip_index** out) {
+    if (!cfg || !out) return fail(FIP_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (cfg->dim <= 0) return fail(FIP_ERR_INVALID, "dim must be positive");
+    if (cfg->dtype != FIP_F32 && cfg->dtype != FIP_F16 && cfg->dtype != FIP_BF16)
+        return fail(FIP_ERR_INVALID, "unknown dtype");
+    if ((cfg->dim * dtype_size(cfg->dtype)) % 16 != 0)
+        return fail(FIP_ERR_INVALID, "row size must be a multiple of 16 bytes "
+                                     "(dim % 4 == 0 for fp32, dim % 8 == 0 for fp16/bf16)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(FIP_ERR_NODEVICE, "no CUDA device visible; this library has no CPU fallback");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(FIP_ERR_INVALID, "bad device ordinal");
+    cudaDeviceProp prop;
+    FIP_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return fail(FIP_ERR_NODEVICE, std::string("device '") + prop.name +
+                                          "' is not sm_100 (B200); kernels are built for sm_100a only");
+    FIP_CUDA(cudaSetDevice(cfg->device));
+    fip_index* idx = new (std::nothrow) fip_index();
+    if (!idx) return fail(FIP_ERR_NOMEM, "host allocation failed");
+    idx->cfg = *cfg;
+    idx->num_sms = prop.multiProcessorCount;
+    cudaError_t e = cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete idx; FIP_CUDA(e); }
+    if (cfg->capacity_rows > 0) {
+        int rc = reserve_rows(idx, cfg->capacity_rows);
+        if (rc) { fip_destroy(idx); return rc; }
+    }
+    *out = idx;
+    return FIP_OK;
+}
+
+void fip_destroy(fip_index* idx) {
+    if (!idx) return;
+    cudaSetDevice(idx->cfg.device);
+    if (idx->stream) cudaStreamSynchronize(idx->stream);
+    if (idx->corpus) cudaFree(idx->corpus);
+    idx->thr.release(); idx->q_scale.release(); idx->q32.release(); idx->out_d.release();
+    idx->cnt.release(); idx->overflow.release(); idx->cand.release(); idx->q16.release();
+    idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
+    idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
+    idx->h_flags.release(); idx->add_stage.release();
+    if (idx->stream) cudaStreamDestroy(idx->stream);
+    delete idx;
+}
+
+static int convert_append(fip_index* idx, const float* src_dev, int64_t n) {
+    const int64_t tot = n * idx->cfg.dim;
+    char* dst = (char*)idx->corpus + (size_t)idx->n_rows * idx->row_bytes();
+    unsigned grid = (unsigned)std::min<int64_t>((tot + 255) / 256, 148 * 32);
+    switch (idx->cfg.dtype) {
+        case kF32:
+            FIP_CUDA(cudaMemcpyAsync(dst, src_dev, (size_t)tot * 4, cudaMemcpyDeviceToDevice, idx->stream));
+            break;
+        case kF16:
+            convert_rows_kernel<__half><<<grid, 256, 0, idx->stream>>>(src_dev, (__half*)dst, tot);
+            break;
+        default:
+            convert_rows_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>(src_dev, (__nv_bfloat16*)dst, tot);
+            break;
+    }
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+
+int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n) {
+    if (!idx || (n > 0 && !rows) || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    int rc = use_device(idx);
+    if (rc) return rc;
+    if (idx->n_rows + n >= (int64_t)0xFFFFFF00ll) return fail(FIP_ERR_INVALID, "shard limited to 2^32-256 rows");
+    rc = reserve_rows(idx, idx->n_rows + n);
+    if (rc) return rc;
+    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(64 << 20) / ((int64_t)idx->cfg.dim * 4));
+    FIP_CUDA(idx->add_stage.ensure((size_t)std::min(chunk_rows, n) * idx->cfg.dim));
+    for (int64_t r = 0; r < n; r += chunk_rows) {
+        int64_t m = std::min(chunk_rows, n - r);
+        FIP_CUDA(cudaMemcpyAsync(idx->add_stage.p, rows + r * idx->cfg.dim, (size_t)m * idx->cfg.dim * 4,
+                                 cudaMemcpyHostToDevice, idx->stream));
+        rc = convert_append(idx, idx->add_stage.p, m);
+        if (rc) return rc;
+        FIP_CUDA(cudaStreamSynchronize(idx->stream));
+        idx->n_rows += m;
+    }
+    idx->tmap_x_valid = false;
+    return FIP_OK;
+}
+
+int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtype) {
+    if (!idx || (n > 0 && !rows_dev) || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    int rc = use_device(idx);
+    if (rc) return rc;
+    if (idx->n_rows + n >= (int64_t)0xFFFFFF00ll) return fail(FIP_ERR_INVALID, "shard limited to 2^32-256 rows");
+    rc = reserve_rows(idx, idx->n_rows + n);
+    if (rc) return rc;
+    if (dtype == idx->cfg.dtype) {
+        char* dst = (char*)idx->corpus + (size_t)idx->n_rows * idx->row_bytes();
+        FIP_CUDA(cudaMemcpyAsync(dst, rows_dev, (size_t)n * idx->row_bytes(), cudaMemcpyDeviceToDevice, idx->stream));
+    } else if (dtype == FIP_F32) {
+        rc = convert_append(idx, (const float*)rows_dev, n);
+        if (rc) return rc;
+    } else {
+        return fail(FIP_ERR_INVALID, "fip_add_device: rows must be fp32 or the index's storage dtype");
+    }
+    FIP_CUDA(cudaStreamSynchronize(idx->stream));
+    idx->n_rows += n;
+    idx->tmap_x_valid = false;
+    return FIP_OK;
+}
+
+int fip_add_synthetic(fip_index* idx, int64_t n, uint64_t seed, int64_t global_row0) {
+    if (!idx || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    int rc = use_device(idx);
+    if (rc) return rc;
+    if (idx->n_rows + n >= (int64_t)0xFFFFFF00ll) return fail(FIP_ERR_INVALID, "shard limited to 2^32-256 rows");
+    rc = reserve_rows(idx, idx->n_rows + n);
+    if (rc) return rc;
+    char* dst = (char*)idx->corpus + (size_t)idx->n_rows * idx->row_bytes();
+    const int grid = idx->num_sms * 16;
+    switch (idx->cfg.dtype) {
+        case kF32: synthetic_fill_kernel<float><<<grid, 256, 0, idx->stream>>>((float*)dst, n, idx->cfg.dim, global_row0, seed, 0u); break;
+        case kF16: synthetic_fill_kernel<__half><<<grid, 256, 0, idx->stream>>>((__half*)dst, n, idx->cfg.dim, global_row0, seed, 0u); break;
+        default: synthetic_fill_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((__nv_bfloat16*)dst, n, idx->cfg.dim, global_row0, seed, 0u); break;
+    }
+    FIP_CUDA(cudaGetLastError());
+    FIP_CUDA(cudaStreamSynchronize(idx->stream));
+    idx->n_rows += n;
+    idx->tmap_x_valid = false;
+    return FIP_OK;
+}
+
+int fip_reset(fip_index* idx) {
+    if (!idx) return fail(FIP_ERR_INVALID, "null index");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    idx->n_rows = 0;
+    idx->tmap_x_valid = false;
+    return FIP_OK;
+}
+
+int fip_reconstruct(fip_index* idx, int64_t row0, int64_t n, float* out_host) {
+    if (!idx || !out_host || row0 < 0 || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    if (row0 + n > idx->n_rows) return fail(FIP_ERR_INVALID, "row range out of bounds");
+    if (n == 0) return FIP_OK;
+    int rc = use_device(idx);
+    if (rc) return rc;
+    const int64_t tot = n * idx->cfg.dim;
+    const char* src = (const char*)idx->corpus + (size_t)row0 * idx->row_bytes();
+    if (idx->cfg.dtype == kF32) {
+        FIP_CUDA(cudaMemcpyAsync(out_host, src, (size_t)tot * 4, cudaMemcpyDeviceToHost, idx->stream));
+    } else {
+        FIP_CUDA(idx->add_stage.ensure((size_t)tot));
+        unsigned grid = (unsigned)std::min<int64_t>((tot + 255) / 256, 148 * 32);
+        if (idx->cfg.dtype == kF16)
+            widen_rows_kernel<__half><<<grid, 256, 0, idx->stream>>>((const __half*)src, idx->add_stage.p, tot);
+        else
+            widen_rows_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((const __nv_bfloat16*)src, idx->add_stage.p, tot);
+        FIP_CUDA(cudaGetLastError());
+        FIP_CUDA(cudaMemcpyAsync(out_host, idx->add_stage.p, (size_t)tot * 4, cudaMemcpyDeviceToHost, idx->stream));
+    }
+    FIP_CUDA(cudaStreamSynchronize(idx->stream));
+    return FIP_OK;
+}
+
+int64_t fip_ntotal(const fip_index* idx) { return idx ? idx->n_rows : 0; }
+int32_t fip_dim(const fip_index* idx) { return idx ? idx->cfg.dim : 0; }
+int32_t fip_dtype_of(const fip_index* idx) { return idx ? idx->cfg.dtype : -1; }
+
+int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, float* distances,
+               int64_t* ids) {
+    int rc = check_search_args(idx, queries, nq, k, distances, ids);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    rc = use_device(idx);
+    if (rc) return rc;
+    const size_t qn = (size_t)nq * idx->cfg.dim, on = (size_t)nq * k;
+    FIP_CUDA(idx->h_q.ensure(qn));
+    FIP_CUDA(idx->h_d.ensure(on));
+    FIP_CUDA(idx->h_i.ensure(on));
+    FIP_CUDA(idx->q32.ensure(qn));
+    FIP_CUDA(idx->out_d.ensure(on));
+    FIP_CUDA(idx->out_i.ensure(on));
+    memcpy(idx->h_q.p, queries, qn * sizeof(float));
+    FIP_CUDA(cudaMemcpyAsync(idx->q32.p, idx->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, idx->stream));
+    rc = search_checked(idx, idx->q32.p, (int)nq, k, idx->out_d.p, idx->out_i.p, idx->stream);
+    if (rc) return rc;
+    FIP_CUDA(cudaMemcpyAsync(idx->h_d.p, idx->out_d.p, on * sizeof(float), cudaMemcpyDeviceToHost, idx->stream));
+    FIP_CUDA(cudaMemcpyAsync(idx->h_i.p, idx->out_i.p, on * sizeof(int64_t), cudaMemcpyDeviceToHost, idx->stream));
+    FIP_CUDA(cudaStreamSynchronize(idx->stream));
+    memcpy(distances, idx->h_d.p, on * sizeof(float));
+    memcpy(ids, idx->h_i.p, on * sizeof(int64_t));
+    return FIP_OK;
+}
+
+int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
+                      float* distances_dev, int64_t* ids_dev, void* cuda_stream) {
+    int rc = check_search_args(idx, queries_dev, nq, k, distances_dev, ids_dev);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    rc = use_device(idx);
+    if (rc) return rc;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : idx->stream;
+    return search_checked(idx, queries_dev, (int)nq, k, distances_dev, ids_dev, s);
+}
+
+int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int32_t g, int64_t nq,
+                     int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream) {
+    if (!in_d || !in_i || !out_d || !out_i || g < 1 || nq < 0 || k_in < 1 || k_out < 1)
+        return fail(FIP_ERR_INVALID, "bad argument");
+    if ((int64_t)g * k_in > kMaxCap) return fail(FIP_ERR_INVALID, "g * k_in must be <= 16384");
+    if (nq == 0) return FIP_OK;
+    FIP_CUDA(cudaSetDevice(device));
+    MergeArgs m{in_d, in_i, g, (int)nq, k_in, k_out, out_d, out_i};
+    int n = next_pow2(g * k_in);
+    size_t smem = (size_t)n * sizeof(uint64_t);
+    FIP_CUDA(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 1024)));
+    int threads = std::min(1024, std::max(32, n / 2));
+    merge_topk_kernel<<<(unsigned)nq, threads, smem, (cudaStream_t)cuda_stream>>>(m);
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+
+int fip_set_option(fip_index* idx, const char* key, int64_t value) {
+    if (!idx || !key) return fail(FIP_ERR_INVALID, "bad argument");
+    std::lock_guard<std::mutex> lock(idx->mu);
+    std::string k(key);
+    if (k == "variant") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "variant must be 0, 1 or 2");
+        idx->variant = (int)value;
+    } else if (k == "stream_max_batch") {
+        idx->stream_max_batch = (int)std::max<int64_t>(0, value);
+    } else if (k == "force_safe_mode") {
+        idx->force_safe = value != 0;
+    } else {
+        return fail(FIP_ERR_INVALID, "unknown option " + k);
+    }
+    return FIP_OK;
+}
+
+int64_t fip_get_stat(const fip_index* idx, const char* key) {
+    if (!idx || !key) return -1;
+    std::string k(key);
+    if (k == "launches") return idx->st_launches;
+    if (k == "variant") return idx->st_variant;
+    if (k == "phases") return idx->st_phases;
+    if (k == "overflow_queries") return idx->st_overflow;
+    if (k == "candidate_capacity") return idx->st_cap;
+    if (k == "total_launches") return idx->st_total_launches;
+    if (k == "total_searches") return idx->st_total_searches;
+    return -1;
+}
+
+const char* fip_last_error(void) { return g_last_error.c_str(); }
+int32_t fip_abi_version(void) { return 1; }
+int32_t fip_compiled_sm(void) { return 100; }
+
+}  // extern "C"

@@ -1,0 +1,177 @@
+"""`B200FlatIPStore`: drop-in for the reference's ``FAISSStore`` component.
+
+Mirror of ``/root/reference/src/pipeline/components/faiss_store.py:21-189`` -- same constructor
+(``settings``), ``load() / search(embeddings, k) / unload()``, ``is_loaded`` / ``index_size``
+properties, ``settings`` / ``index_path`` attributes, the same exceptions with the same messages
+(the reference's tests match on them, ``/root/reference/tests/test_components.py:47,92,112,133``)
+and the same ``(distances, indices)`` return contract -- but the index lives in B200 HBM and
+``search`` runs the hand-written sm_100a kernels behind libflatip_b200.so.  There is no CPU path.
+
+It is looked up by the retrieval service under the registry name ``faiss_store``
+(``/root/reference/src/pipeline/services/retrieval/api.py:218,383,537``); see ``factory.py``.
+
+``settings.faiss_index_path`` may name
+  * a faiss flat index file (``IxFI``) -- what the reference's ``faiss.read_index`` consumes,
+  * a FIPB corpus file written by ``index_io.write_fipb`` (fp32 / fp16 / bf16 rows), or
+  * ``synthetic:<rows>[?dim=..&dtype=..&seed=..]`` -- a Philox corpus generated on the device.
+"""
+
+from __future__ import annotations
+
+import gc
+import logging
+import os
+import threading
+from pathlib import Path
+from urllib.parse import parse_qs
+
+import numpy as np
+
+from . import index_io
+from .index import FlatIPIndex
+from .synthetic import CORPUS_SEED
+
+logger = logging.getLogger(__name__)
+
+_UPLOAD_CHUNK_BYTES = 256 << 20
+
+
+class B200FlatIPStore:
+    """Exact flat inner-product store on one B200 (same surface as the reference FAISSStore)."""
+
+    def __init__(self, settings, config: dict | None = None) -> None:
+        config = dict(config or {})
+        self.settings = settings
+        self._raw_path = str(settings.faiss_index_path)
+        self.index_path = Path(self._raw_path)
+        self._index: FlatIPIndex | None = None
+        self._is_loaded = False
+        self._lock = threading.Lock()
+        self.device = int(config.get("device", os.environ.get("FLATIP_B200_DEVICE", 0)))
+        # None = keep the dtype the file holds (fp32 for faiss files, like the reference).
+        self.storage_dtype = config.get("storage_dtype", os.environ.get("FLATIP_B200_DTYPE"))
+        self.id_base = int(config.get("id_base", 0))
+        self.variant = config.get("variant", os.environ.get("FLATIP_B200_VARIANT", "auto"))
+
+    # ------------------------------------------------------------------------------- load
+    def _load_synthetic(self) -> FlatIPIndex:
+        spec = self._raw_path[len("synthetic:"):]
+        rows_s, _, query = spec.partition("?")
+        opts = {k: v[0] for k, v in parse_qs(query).items()}
+        dim = int(opts.get("dim", self.settings.faiss_dim))
+        dtype = opts.get("dtype", self.storage_dtype or "f32")
+        seed = int(opts.get("seed", CORPUS_SEED))
+        row0 = int(opts.get("row0", self.id_base))
+        nrows = int(float(rows_s))
+        index = FlatIPIndex(dim, dtype, self.device, id_base=row0, capacity_rows=nrows)
+        index.add_synthetic(nrows, seed, row0)
+        return index
+
+    def _load_file(self) -> FlatIPIndex:
+        info = index_io.read_header(str(self.index_path))
+        if info.metric != "ip":
+            raise ValueError("only inner-product flat indexes are supported (file holds an "
+                             f"{info.metric.upper()} index)")
+        dtype = self.storage_dtype or info.dtype
+        rows = index_io.open_rows(str(self.index_path), info)
+        index = FlatIPIndex(info.dim, dtype, self.device, id_base=info.id_base + self.id_base,
+                            capacity_rows=info.ntotal)
+        step = max(1, _UPLOAD_CHUNK_BYTES // (info.dim * 4))
+        for r0 in range(0, info.ntotal, step):
+            chunk = rows[r0:r0 + step]
+            if info.dtype == "bf16":
+                chunk = (np.asarray(chunk).astype(np.uint32) << np.uint32(16)).view(np.float32)
+            index.add(np.asarray(chunk, dtype=np.float32))
+        return index
+
+    def load(self) -> None:
+        """Bring the corpus into HBM (reference: ``FAISSStore.load``, faiss_store.py:40-111).
+
+        Raises FileNotFoundError if the index file does not exist, RuntimeError for any other
+        failure -- including a missing CUDA library or GPU (no CPU fallback).
+        """
+        if self._is_loaded:
+            logger.info("FAISS index already loaded")
+            return
+        synthetic = self._raw_path.startswith("synthetic:")
+        if not synthetic and not self.index_path.exists():
+            msg = f"FAISS index not found at {self.index_path}"
+            raise FileNotFoundError(msg)
+        logger.info("Loading FAISS index from %s", self._raw_path)
+        try:
+            index = self._load_synthetic() if synthetic else self._load_file()
+            if self.variant != "auto":
+                index.set_variant(self.variant)
+            self._index = index
+            self._is_loaded = True
+            logger.info("FAISS index loaded successfully: %d vectors, dimension=%d (B200 %s, "
+                        "device %d)", index.ntotal, index.d, index.dtype, self.device)
+            if index.ntotal > 0:
+                logger.info("Warming up FAISS index...")
+                index.search(np.zeros((1, index.d), dtype=np.float32), 1)
+                logger.info("FAISS index warmup complete")
+        except Exception as e:
+            logger.exception("Failed to load FAISS index")
+            self._index = None
+            self._is_loaded = False
+            msg = f"FAISS index loading failed: {e}"
+            raise RuntimeError(msg) from e
+
+    # ------------------------------------------------------------------------------ search
+    def search(self, embeddings: np.ndarray, k: int) -> tuple[np.ndarray, np.ndarray]:
+        """Exact inner-product top-k (reference: ``FAISSStore.search``, faiss_store.py:113-158).
+
+        embeddings: (batch, dim) float array.  Returns (distances float32 [batch, k], indices
+        int64 [batch, k]), each row best-first; unfilled slots are -FLT_MAX / -1 as in faiss.
+        """
+        if not self._is_loaded or self._index is None:
+            msg = "FAISS index not loaded. Call load() first."
+            raise RuntimeError(msg)
+        if embeddings.ndim != 2:
+            msg = f"Embeddings must be 2D array, got shape {embeddings.shape}"
+            raise ValueError(msg)
+        if embeddings.shape[1] != self.settings.faiss_dim:
+            msg = (
+                f"Embedding dimension mismatch: expected {self.settings.faiss_dim}, "
+                f"got {embeddings.shape[1]}"
+            )
+            raise ValueError(msg)
+        embeddings = embeddings.astype("float32")
+        logger.debug("Searching FAISS index with %d queries, k=%d", embeddings.shape[0], k)
+        try:
+            distances, indices = self._index.search(embeddings, k)
+            logger.debug("FAISS search completed: found %s results", indices.shape)
+        except Exception:
+            logger.exception("FAISS search failed")
+            raise
+        else:
+            return distances, indices
+
+    # ----------------------------------------------------------------------------- teardown
+    def unload(self) -> None:
+        if self._is_loaded:
+            logger.info("Unloading FAISS index")
+            if self._index is not None:
+                self._index.close()
+            self._index = None
+            self._is_loaded = False
+            gc.collect()
+
+    @property
+    def is_loaded(self) -> bool:
+        return self._is_loaded
+
+    @property
+    def index_size(self) -> int:
+        if not self._is_loaded or self._index is None:
+            return 0
+        return int(self._index.ntotal)
+
+    @property
+    def native_index(self) -> FlatIPIndex | None:
+        return self._index
+
+    def __repr__(self) -> str:
+        status = "loaded" if self._is_loaded else "not loaded"
+        size = self.index_size if self._is_loaded else "unknown"
+        return f"B200FlatIPStore(path={self._raw_path}, status={status}, size={size})"

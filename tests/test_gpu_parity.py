@@ -1,0 +1,375 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on
+identical seeded inputs.  Acceptance rule (BASELINE.json north_star): ids bit-exact outside
+near-tie windows; scores within 1e-5 relative (fp32 storage) / 1e-3 (fp16, bf16 storage)."""
+import os
+import threading
+
+import numpy as np
+import pytest
+
+import c_oracle
+import flatip_oracle
+from flatip_oracle import SCORE_RTOL
+from rag_inference_pipeline_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _index(dim, dtype, **kw):
+    from rag_inference_pipeline_b200 import FlatIPIndex
+    return FlatIPIndex(dim, dtype, 0, **kw)
+
+
+def _check(D, I, Dr, Ir, dtype, kplus1=None):
+    res = flatip_oracle.compare_with_oracle(D, I, Dr, Ir, rtol=SCORE_RTOL[dtype], kplus1_ref=kplus1)
+    assert res["score_ok"], res
+    assert res["id_mismatch_outside_window"] == 0, res
+    # windows must stay rare on random data, otherwise the rule is vacuous
+    assert res["id_mismatch_total"] <= max(2, I.size // 200), res
+    for row in D:  # best-first
+        assert np.all(np.diff(row) <= 0)
+    return res
+
+
+def test_device_generator_matches_host_restatement():
+    for dtype in synthetic.DTYPES:
+        idx = _index(72, dtype)
+        idx.add_synthetic(1500, 1234, 987654321)
+        got = idx.reconstruct_n(0, 1500)
+        assert np.array_equal(got, synthetic.synthetic_corpus(987654321, 1500, 72, dtype))
+        idx.close()
+
+
+def test_reference_fixture_inputs():
+    """The reference's only real-index fixture (tests/test_retrieval_service.py:202-212,260-261),
+    as a flat-IP search; expected values from the fp64 oracle (parity unpinned, see make_golden)."""
+    g = np.load(os.path.join(GOLDEN, "reference_fixture_flatip.npz"))
+    idx = _index(768, "f32")
+    idx.add(g["corpus"])
+    assert idx.ntotal == 10
+    for k in (1, 3, 10, 12):
+        D, I = idx.search(g["queries"], k)
+        assert np.array_equal(I, g[f"I_k{k}"])
+        np.testing.assert_allclose(D[I >= 0], g[f"D_k{k}"][I >= 0], rtol=1e-5)
+        assert np.all(D[I < 0] == np.finfo(np.float32).min)
+    idx.close()
+
+
+@pytest.mark.parametrize("tag", ["f32_3000x64_q5_k10", "f16_5000x128_q33_k100", "bf16_2500x64_q8_k7"])
+@pytest.mark.parametrize("variant", ["stream", "tensor"])
+def test_golden_synthetic_cases(tag, variant):
+    dtype, shape, q, k = tag.split("_")
+    if variant == "tensor" and dtype == "f32":
+        pytest.skip("tensor-core variant stores 16-bit corpora")
+    n, dim = (int(v) for v in shape.split("x"))
+    nq, k = int(q[1:]), int(k[1:])
+    g = np.load(os.path.join(GOLDEN, "synthetic_cases.npz"))
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    idx.set_variant(variant)
+    D, I = idx.search(synthetic.synthetic_queries(nq, dim), k)
+    assert idx.last_variant() == variant
+    _check(D, I, g[f"D_{tag}"], g[f"I_{tag}"], dtype)
+    idx.close()
+
+
+CASES = [
+    # variant, dtype, n, dim, nq, k
+    ("stream", "f32", 20000, 768, 32, 10),      # config 2 shape, scaled down
+    ("stream", "f32", 9999, 100, 1, 1),
+    ("stream", "f16", 30011, 256, 3, 100),
+    ("stream", "bf16", 12345, 64, 17, 50),
+    ("tensor", "f16", 50000, 768, 64, 100),     # config 3 shape, scaled down
+    ("tensor", "f16", 40000, 384, 130, 1024),   # config 5: large k, ragged query tile
+    ("tensor", "bf16", 70001, 768, 200, 100),   # config 4: bf16, ragged corpus tile
+    ("tensor", "bf16", 300, 64, 5, 10),         # corpus smaller than one tile
+    ("tensor", "f16", 4096, 128, 128, 2048),    # k at its maximum, corpus == one dense phase
+]
+
+
+@pytest.mark.parametrize("variant,dtype,n,dim,nq,k", CASES)
+def test_parity_with_oracle(variant, dtype, n, dim, nq, k):
+    corpus = c_oracle.synthetic_corpus(0, n, dim, dtype)
+    queries = synthetic.synthetic_queries(nq, dim)
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, min(k + 1, max(n, 1)) if n > k else k)
+    kplus1 = Dr[:, k] if Dr.shape[1] > k else None
+    Dr, Ir = Dr[:, :k], Ir[:, :k]
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    idx.set_variant(variant)
+    D, I = idx.search(queries, k)
+    assert idx.last_variant() == variant
+    assert idx.stat("launches") > 0
+    _check(D, I, Dr, Ir, dtype, kplus1)
+    idx.close()
+
+
+def test_auto_variant_follows_arithmetic_intensity():
+    idx = _index(128, "f16")
+    idx.add_synthetic(5000, 1, 0)
+    idx.search(synthetic.synthetic_queries(2, 128), 5)
+    assert idx.last_variant() == "stream"      # tiny batch: HBM-bound on CUDA cores
+    idx.search(synthetic.synthetic_queries(64, 128), 5)
+    assert idx.last_variant() == "tensor"      # needs the tensor pipe to stay on the HBM roof
+    idx.close()
+    idx = _index(128, "f32")
+    idx.add_synthetic(5000, 1, 0)
+    idx.search(synthetic.synthetic_queries(64, 128), 5)
+    assert idx.last_variant() == "stream"      # fp32 storage: exact fp32 products
+    idx.close()
+
+
+@pytest.mark.parametrize("variant,dtype", [("stream", "f32"), ("tensor", "f16")])
+def test_edge_cases(variant, dtype):
+    dim = 64
+    idx = _index(dim, dtype)
+    q = synthetic.synthetic_queries(4, dim)
+    # empty corpus -> all padding, like faiss
+    D, I = idx.search(q, 7)
+    assert np.all(I == -1) and np.all(D == np.finfo(np.float32).min)
+    # k > ntotal
+    idx.add_synthetic(5, 3, 0)
+    idx.set_variant(variant)
+    D, I = idx.search(q, 9)
+    corpus = synthetic.synthetic_corpus(0, 5, dim, dtype, seed=3)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, 9)
+    _check(D, I, Dr, Ir, dtype)
+    assert np.all(I[:, 5:] == -1)
+    # zero queries -> empty result
+    D0, I0 = idx.search(np.zeros((0, dim), np.float32), 3)
+    assert D0.shape == (0, 3) and I0.shape == (0, 3)
+    # the all-zero warm-up query of FAISSStore.load (faiss_store.py:103-107)
+    Dz, Iz = idx.search(np.zeros((1, dim), np.float32), 1)
+    assert Iz[0, 0] == 0 and Dz[0, 0] == 0.0    # all scores tie at 0 -> lowest id
+    idx.close()
+
+
+def test_bad_arguments_raise():
+    from rag_inference_pipeline_b200._native import FlatIPError
+    from rag_inference_pipeline_b200 import FlatIPIndex
+    idx = _index(64, "f16")
+    idx.add_synthetic(100, 1, 0)
+    with pytest.raises(FlatIPError):
+        idx.search(synthetic.synthetic_queries(2, 64), 0)
+    with pytest.raises(FlatIPError):
+        idx.search(synthetic.synthetic_queries(2, 64), 5000)
+    with pytest.raises(ValueError):
+        idx.search(synthetic.synthetic_queries(2, 32), 5)
+    with pytest.raises(FlatIPError):
+        FlatIPIndex(70, "f16", 0)      # rows must be 16-byte multiples
+    idx.close()
+
+
+@pytest.mark.parametrize("variant,dtype", [("stream", "f32"), ("tensor", "f16")])
+def test_exact_duplicates_order_by_id(variant, dtype):
+    dim, k = 64, 12
+    base = synthetic.synthetic_corpus(0, 3000, dim, dtype)
+    corpus = np.concatenate([base, base[:500], base[100:200]])
+    queries = base[100:108] / np.linalg.norm(base[100:108], axis=1, keepdims=True)
+    idx = _index(dim, dtype)
+    idx.add(corpus)
+    idx.set_variant(variant)
+    D, I = idx.search(queries.astype(np.float32), k)
+    Dr, Ir = flatip_oracle.flat_ip_search(queries.astype(np.float32), corpus, k)
+    for qi in range(8):
+        r = 100 + qi
+        assert list(I[qi, :3]) == [r, 3000 + r, 3500 + qi]     # equal scores: ids ascending
+        assert D[qi, 0] == D[qi, 1] == D[qi, 2]
+    _check(D, I, Dr, Ir, dtype)
+    idx.close()
+
+
+@pytest.mark.parametrize("variant,dtype", [("stream", "f32"), ("tensor", "f16")])
+def test_adversarial_order_overflow_fallback(variant, dtype):
+    """Rows sorted so that every new row beats everything before it: the candidate lists overflow
+    and the safe-mode redo must still return the exact answer."""
+    dim, n, k = 64, 60000, 10
+    rng = np.random.default_rng(5)
+    direction = rng.standard_normal(dim).astype(np.float32)
+    direction /= np.linalg.norm(direction)
+    noise = 0.01 * rng.standard_normal((n, dim)).astype(np.float32)
+    corpus = synthetic.round_to_storage(
+        noise + np.linspace(0.0, 4.0, n, dtype=np.float32)[:, None] * direction[None, :], dtype)
+    queries = np.stack([direction, -direction, synthetic.synthetic_queries(1, dim)[0]])
+    idx = _index(dim, dtype)
+    idx.add(corpus)
+    idx.set_variant(variant)
+    D, I = idx.search(queries, k)
+    assert idx.stat("overflow_queries") >= 1
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k)
+    _check(D, I, Dr, Ir, dtype)
+    idx.close()
+
+
+def test_forced_safe_mode_matches():
+    dim, n, k = 128, 50000, 20
+    corpus = c_oracle.synthetic_corpus(0, n, dim, "f16")
+    q = synthetic.synthetic_queries(9, dim)
+    idx = _index(dim, "f16")
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    D1, I1 = idx.search(q, k)
+    idx.set_option("force_safe_mode", 1)
+    D2, I2 = idx.search(q, k)
+    assert idx.stat("phases") > 3
+    assert np.array_equal(I1, I2) and np.array_equal(D1, D2)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
+    _check(D1, I1, Dr, Ir, "f16")
+    idx.close()
+
+
+def test_results_are_deterministic_and_thread_safe():
+    """search is called from a thread pool with overlapping batches
+    (/root/reference/src/pipeline/services/retrieval/api.py:348-349) and feeds a sha256-keyed cache
+    (api.py:398-421): same input -> same bits, from any thread."""
+    dim, n, k = 128, 40000, 10
+    idx = _index(dim, "f16")
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    qs = [synthetic.synthetic_queries(8 + 5 * t, dim, seed=100 + t) for t in range(6)]
+    expected = [idx.search(q, k) for q in qs]
+    results = [None] * len(qs)
+
+    def work(t):
+        for _ in range(3):
+            results[t] = idx.search(qs[t], k)
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(len(qs))]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    for (D, I), (De, Ie) in zip(results, expected):
+        assert np.array_equal(I, Ie) and np.array_equal(D, De)
+    idx.close()
+
+
+def test_id_base_and_incremental_add():
+    dim, k = 64, 5
+    corpus = synthetic.synthetic_corpus(0, 3000, dim, "f32")
+    idx = _index(dim, "f32", id_base=1_000_000)
+    idx.add(corpus[:1000])
+    idx.add(corpus[1000:])
+    assert idx.ntotal == 3000
+    q = synthetic.synthetic_queries(4, dim)
+    D, I = idx.search(q, k)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k, id_base=1_000_000)
+    _check(D, I, Dr, Ir, "f32")
+    idx.close()
+
+
+def test_merge_kernel_matches_oracle():
+    import torch
+    from rag_inference_pipeline_b200 import merge_device
+
+    rng = np.random.default_rng(3)
+    g, nq, k = 8, 37, 100
+    d = np.sort(rng.standard_normal((g, nq, k)).astype(np.float32), axis=2)[:, :, ::-1].copy()
+    d[:, :, 40:60] = d[:, :, 40:41]                 # runs of equal scores inside a shard
+    d[3] = d[2]                                     # and equal scores across shards
+    ids = np.sort(rng.integers(0, 1000, (g, nq, k)), axis=2) + (np.arange(g) * 1000)[:, None, None]
+    ids = ids.astype(np.int64)
+    ids[5, :, 90:] = -1                             # a shard with fewer than k rows
+    d[5, :, 90:] = np.finfo(np.float32).min
+    Dr, Ir = flatip_oracle.merge_sorted_lists(d, ids, k)
+    td, ti = torch.from_numpy(d).cuda(), torch.from_numpy(ids).cuda()
+    od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    oi = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    merge_device(0, td.data_ptr(), ti.data_ptr(), g, nq, k, k, od.data_ptr(), oi.data_ptr(),
+                 torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(od.cpu().numpy(), Dr)
+    # among equal scores the oracle orders by id; the kernel by (shard, position) == id here
+    assert np.array_equal(oi.cpu().numpy(), Ir)
+
+
+def test_sharded_search_equals_single_index():
+    """Row-shard emulation on one GPU: g shard indexes searched one after the other, results
+    stacked like an all-gather leaves them, merged by K3 == one index over the whole corpus."""
+    import torch
+    from rag_inference_pipeline_b200 import merge_device
+    from rag_inference_pipeline_b200.sharded import shard_range
+
+    dim, n, nq, k, g = 128, 100_003, 48, 100, 4
+    q = synthetic.synthetic_queries(nq, dim)
+    whole = _index(dim, "f16")
+    whole.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    Dw, Iw = whole.search(q, k)
+    whole.close()
+    ds, is_ = [], []
+    for r in range(g):
+        b, e = shard_range(n, r, g)
+        sh = _index(dim, "f16", id_base=b)
+        sh.add_synthetic(e - b, synthetic.CORPUS_SEED, b)
+        d, i = sh.search(q, k)
+        ds.append(d)
+        is_.append(i)
+        sh.close()
+    td = torch.from_numpy(np.stack(ds)).cuda()
+    ti = torch.from_numpy(np.stack(is_)).cuda()
+    od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    oi = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    merge_device(0, td.data_ptr(), ti.data_ptr(), g, nq, k, k, od.data_ptr(), oi.data_ptr(),
+                 torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(oi.cpu().numpy(), Iw)
+    assert np.array_equal(od.cpu().numpy(), Dw)
+
+
+def test_store_dropin_on_gpu(tmp_path):
+    """B200FlatIPStore end to end: faiss flat file -> load (with warm-up) -> search -> unload."""
+    import types
+    from rag_inference_pipeline_b200 import B200FlatIPStore, index_io
+
+    dim, n, k = 768, 2000, 10
+    corpus = synthetic.synthetic_corpus(0, n, dim, "f32")
+    path = tmp_path / "faiss_index.bin"
+    index_io.write_faiss_flat(str(path), corpus)
+    settings = types.SimpleNamespace(faiss_index_path=str(path), faiss_dim=dim, faiss_use_mmap=False)
+    store = B200FlatIPStore(settings)
+    store.load()
+    store.load()  # second call is a no-op, like the reference
+    assert store.is_loaded and store.index_size == n
+    q = synthetic.synthetic_queries(32, dim)
+    D, I = store.search(q.astype(np.float64), k)     # any float dtype is accepted
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
+    _check(D, I, Dr, Ir, "f32")
+    assert isinstance(I[0].tolist()[0], int) and isinstance(D[0].tolist()[0], float)
+    store.unload()
+    assert not store.is_loaded
+    # fp16 storage + synthetic URI
+    s2 = types.SimpleNamespace(faiss_index_path=f"synthetic:{n}?dim={dim}&dtype=f16", faiss_dim=dim)
+    st2 = B200FlatIPStore(s2)
+    st2.load()
+    D2, I2 = st2.search(q, k)
+    Dr2, Ir2 = flatip_oracle.flat_ip_search(q, synthetic.synthetic_corpus(0, n, dim, "f16"), k)
+    _check(D2, I2, Dr2, Ir2, "f16")
+    st2.unload()
+
+
+def test_large_scale_properties():
+    """10 M x 768 bf16, batch 1024, k = 100 (BASELINE config 4 at full size): too big for the
+    oracle, so check size-independent properties -- rows sorted, returned scores reproduce on the
+    host from regenerated rows, and no sampled corpus block holds a row that should have displaced
+    the k-th result."""
+    dim, n, nq, k = 768, 10_000_000, 1024, 100
+    idx = _index(dim, "bf16", capacity_rows=n)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    q = synthetic.synthetic_queries(nq, dim)
+    D, I = idx.search(q, k)
+    assert idx.last_variant() == "tensor" and idx.stat("overflow_queries") == 0
+    assert np.all(np.diff(D, axis=1) <= 0) and I.min() >= 0 and I.max() < n
+    for row in I[::97]:
+        assert len(set(row.tolist())) == k
+    # recompute a sample of returned scores from regenerated rows (fp64)
+    for qi in range(0, nq, 61):
+        rows = np.stack([c_oracle.synthetic_corpus(int(r), 1, dim, "bf16")[0] for r in I[qi, ::9]])
+        ref = rows.astype(np.float64) @ q[qi].astype(np.float64)
+        np.testing.assert_allclose(D[qi, ::9], ref, rtol=1e-3, atol=1e-3)
+    # sampled blocks: nothing outside the result may beat the k-th score by more than the tolerance
+    for b0 in (0, 4_999_936, n - 4096):
+        blk = c_oracle.synthetic_corpus(b0, 4096, dim, "bf16")
+        s = q.astype(np.float32) @ blk.T
+        for qi in range(0, nq, 17):
+            better = np.nonzero(s[qi] > D[qi, -1] + 1e-3 * max(1.0, abs(D[qi, -1])))[0] + b0
+            assert set(better.tolist()) <= set(I[qi].tolist())
+    idx.close()
