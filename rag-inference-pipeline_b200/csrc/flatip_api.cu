@@ -168,6 +168,7 @@ struct fip_index {
     int variant = FIP_VARIANT_AUTO;
     int stream_max_batch = 4;
     int force_safe = 0;
+    int query_split = 0;  // 0 = auto (1 for fp16 storage, 2 for bf16)
 
     // per-search workspace
     DevBuf<float> thr, q_scale, q32, out_d;
@@ -270,23 +271,27 @@ int launch_stream_phase(SearchCtx& c, const ScanArgs& a, const float* q32) {
     return FIP_OK;
 }
 
-int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int nq_pad) {
+template <int kFmt, int kSplit>
+int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles, int grid) {
+    auto kern = tc::tc_scan_kernel<kFmt, kSplit>;
+    constexpr int smem = tc::Cfg<kSplit>::SMEM_BYTES;
+    FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kern<<<grid, tc::NUM_THREADS, smem, c.stream>>>(tmap_q, c.idx->tmap_x, a, n_qtiles);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    return FIP_OK;
+}
+
+int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int nq_pad, int split) {
     fip_index* idx = c.idx;
     const int n_qtiles = nq_pad / tc::BM;
     const int64_t n_ctiles = ((int64_t)(a.row_end - a.row_begin) + tc::BN - 1) / tc::BN;
     int grid = (int)std::min<int64_t>(idx->num_sms, n_ctiles * n_qtiles);
-    if (a.dtype == kBF16) {
-        auto kern = tc::tc_scan_kernel<1>;
-        FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        kern<<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(tmap_q, idx->tmap_x, a, n_qtiles);
-    } else {
-        auto kern = tc::tc_scan_kernel<0>;
-        FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES));
-        kern<<<grid, tc::NUM_THREADS, tc::SMEM_BYTES, c.stream>>>(tmap_q, idx->tmap_x, a, n_qtiles);
-    }
-    FIP_CUDA(cudaGetLastError());
-    c.launches++;
-    return FIP_OK;
+    if (a.dtype == kBF16)
+        return split == 2 ? launch_tc_kernel<1, 2>(c, a, tmap_q, n_qtiles, grid)
+                          : launch_tc_kernel<1, 1>(c, a, tmap_q, n_qtiles, grid);
+    return split == 2 ? launch_tc_kernel<0, 2>(c, a, tmap_q, n_qtiles, grid)
+                      : launch_tc_kernel<0, 1>(c, a, tmap_q, n_qtiles, grid);
 }
 
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
@@ -320,12 +325,6 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         *variant_used = 0; *phases_used = 0; *cap_used = 0;
         return FIP_OK;
     }
-    const int cap = cap_for_k(k, safe);
-    FIP_CUDA(idx->thr.ensure(nq));
-    FIP_CUDA(idx->cnt.ensure(nq));
-    FIP_CUDA(idx->overflow.ensure((size_t)nq + 1));
-    FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
-
     int variant = idx->variant;
     const bool tc_ok = idx->cfg.dtype != kF32 && dim % tc::BK == 0;
     if (variant == FIP_VARIANT_AUTO)
@@ -337,23 +336,42 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (variant == FIP_VARIANT_TENSOR && !tc_ok)
         return fail(FIP_ERR_INVALID,
                     "tensor-core variant needs fp16/bf16 storage and dim % 64 == 0");
+    // The tensor-core scan filters on 16-bit-rounded queries: keep a margin of extra candidates
+    // (k' = k + max(16, k/4)) and rescore the survivors exactly before the final selection.
+    const bool rescore = variant == FIP_VARIANT_TENSOR;
+    const int k_out = k;
+    if (rescore) k = k + std::max(16, k / 4);
+    const int cap = cap_for_k(k, safe);
+    FIP_CUDA(idx->thr.ensure(nq));
+    FIP_CUDA(idx->cnt.ensure(nq));
+    FIP_CUDA(idx->overflow.ensure((size_t)nq + 1));
+    FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
 
     init_lists_kernel<<<(nq + 256) / 256, 256, 0, c.stream>>>(idx->thr.p, idx->cnt.p, idx->overflow.p, nq);
     FIP_CUDA(cudaGetLastError());
     c.launches++;
 
     CUtensorMap tmap_q{};
-    int nq_pad = 0;
+    int nq_pad = 0, split = 1;
     const float* out_scale = nullptr;
     if (variant == FIP_VARIANT_TENSOR) {
         nq_pad = (nq + tc::BM - 1) / tc::BM * tc::BM;
-        FIP_CUDA(idx->q16.ensure((size_t)nq_pad * dim));
+        // fp16 storage: one fp16 term; bf16 storage: bf16 hi + lo terms (see tc_scan.cuh).
+        split = idx->query_split ? idx->query_split : (idx->cfg.dtype == kBF16 ? 2 : 1);
+        FIP_CUDA(idx->q16.ensure((size_t)split * nq_pad * dim));
         FIP_CUDA(idx->q_scale.ensure(nq));
-        tc::prepare_queries_f16_kernel<<<(nq_pad + 7) / 8, 256, 0, c.stream>>>(
-            q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
+        const unsigned pgrid = (nq_pad + 7) / 8;
+        if (idx->cfg.dtype == kBF16) {
+            auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->q16.p);
+            if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
+            else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
+        } else {
+            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
+            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
+        }
         FIP_CUDA(cudaGetLastError());
         c.launches++;
-        int rc = make_tmap(&tmap_q, idx->q16.p, kF16, dim, (uint64_t)nq_pad, tc::BM);
+        int rc = make_tmap(&tmap_q, idx->q16.p, idx->cfg.dtype, dim, (uint64_t)split * nq_pad, tc::BM);
         if (rc) return rc;
         if (!idx->tmap_x_valid) {
             rc = make_tmap(&idx->tmap_x, idx->corpus, idx->cfg.dtype, dim, (uint64_t)n, tc::BN);
@@ -369,7 +387,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
 
     auto scan = [&](int64_t r0, int64_t r1, bool dense) -> int {
         a.row_begin = (uint32_t)r0; a.row_end = (uint32_t)r1; a.dense = dense ? 1 : 0;
-        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, nq_pad);
+        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, nq_pad, split);
         switch (idx->cfg.dtype) {
             case kF32: return launch_stream_phase<float>(c, a, q32);
             case kF16: return launch_stream_phase<__half>(c, a, q32);
@@ -389,7 +407,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     c.launches++;
     int64_t pos = m;
     phases++;
-    rc = launch_select(c, idx, nq, k, cap, pos == n, out_d, out_i, out_scale);
+    rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale);
     if (rc) return rc;
     while (pos < n) {
         if (safe) m = std::max<int64_t>(256, (int64_t)(cap - k) / 256 * 256);
@@ -399,7 +417,22 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         if (rc) return rc;
         pos += m;
         phases++;
-        rc = launch_select(c, idx, nq, k, cap, pos == n, out_d, out_i, out_scale);
+        rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale);
+        if (rc) return rc;
+    }
+    if (rescore) {
+        // lists now hold the k' best by 16-bit-query score: recompute them exactly, then select k.
+        const int64_t warps = (int64_t)nq * k;
+        const unsigned grid = (unsigned)std::min<int64_t>((warps + 7) / 8, (int64_t)idx->num_sms * 8);
+        if (idx->cfg.dtype == kBF16)
+            rescore_kernel<__nv_bfloat16><<<grid, 256, 0, c.stream>>>(
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __nv_bfloat16*)idx->corpus, q32, dim);
+        else
+            rescore_kernel<__half><<<grid, 256, 0, c.stream>>>(
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __half*)idx->corpus, q32, dim);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+        rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr);
         if (rc) return rc;
     }
     *variant_used = variant; *phases_used = phases; *cap_used = cap;
@@ -708,6 +741,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         idx->variant = (int)value;
     } else if (k == "stream_max_batch") {
         idx->stream_max_batch = (int)std::max<int64_t>(0, value);
+    } else if (k == "query_split") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "query_split must be 0 (auto), 1 or 2");
+        idx->query_split = (int)value;
     } else if (k == "force_safe_mode") {
         idx->force_safe = value != 0;
     } else {

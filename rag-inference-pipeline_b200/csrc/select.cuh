@@ -11,6 +11,7 @@
 #pragma once
 
 #include "common.cuh"
+#include "stream_scan.cuh"
 
 namespace fip {
 
@@ -74,6 +75,48 @@ __global__ void select_topk_kernel(SelectArgs a) {
             a.out_d[(size_t)q * a.k + i] = valid ? key_score(key) * scale : kLowestF32;
             a.out_i[(size_t)q * a.k + i] = valid ? a.id_base + (int64_t)key_row(key) : -1;
         }
+    }
+}
+
+// Exact rescoring of the surviving candidates (tensor-core variant).  The tcgen05 scan sees the
+// fp32 queries rounded to 16 bits, so its scores carry ~1e-4 relative error; that is fine for
+// FILTERING (the lists keep a margin of extra candidates) but not for the reported distances or
+// the final order.  One warp per (query, candidate): re-read the stored row (exact 16-bit values)
+// and the original fp32 query, accumulate in fp32, and rewrite the key with the exact score.
+// Work: nq * k' rows of dim elements -- microseconds next to the scan.
+template <typename T>
+__global__ void rescore_kernel(uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt,
+                               uint32_t cap, int nq, int kprime, const T* __restrict__ corpus,
+                               const float* __restrict__ q32, int dim) {
+    constexpr int EPV = 16 / sizeof(T);
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int nvec = dim / EPV;
+    for (int64_t w = warp; w < (int64_t)nq * kprime; w += nwarps) {
+        const int q = (int)(w / kprime), slot = (int)(w - (int64_t)q * kprime);
+        if (slot >= (int)min(cnt[q], cap)) continue;  // warp-uniform
+        const uint64_t key = cand[(size_t)q * cap + slot];
+        const uint32_t row = key_row(key);
+        const T* x = corpus + (size_t)row * dim;
+        const float* qv = q32 + (size_t)q * dim;
+        float acc = 0.f;
+        for (int v = lane; v < nvec; v += 32) {
+            uint4 raw = *reinterpret_cast<const uint4*>(x + (size_t)v * EPV);
+            float xf[EPV];
+            VecOps<T>::unpack(raw, xf);
+#pragma unroll
+            for (int h = 0; h < EPV / 4; ++h) {
+                float4 qq = *reinterpret_cast<const float4*>(qv + (size_t)v * EPV + 4 * h);
+                acc = fmaf(xf[4 * h + 0], qq.x, acc);
+                acc = fmaf(xf[4 * h + 1], qq.y, acc);
+                acc = fmaf(xf[4 * h + 2], qq.z, acc);
+                acc = fmaf(xf[4 * h + 3], qq.w, acc);
+            }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);
+        if (lane == 0) cand[(size_t)q * cap + slot] = make_key(acc, row);
     }
 }
 

@@ -20,7 +20,10 @@
 
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "common.cuh"
+#include "synthetic.cuh"
 
 namespace fip {
 namespace tc {
@@ -29,14 +32,20 @@ constexpr int BM = 128;   // queries per tile  (UMMA M)
 constexpr int BN = 256;   // corpus rows per tile (UMMA N)
 constexpr int BK = 64;    // K elements per stage: 64 * 2 B = 128 B = one SWIZZLE_128B atom
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
-constexpr int A_BYTES = BM * BK * 2;
+constexpr int A_BYTES = BM * BK * 2;   // one query operand tile (per split term)
 constexpr int B_BYTES = BN * BK * 2;
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int TMEM_COLS = 512;  // two 256-column fp32 accumulators
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+// kSplit = number of 16-bit terms the fp32 queries are split into (q = q0 + q1 ...): 1 for fp16
+// storage (fp16 queries, 2^-11 rounding, repaired by the exact rescoring pass), 2 for bf16 storage
+// (bf16 hi + lo, 2^-17).  tcgen05.mma kind::f16 needs A and B in the SAME 16-bit format
+// (mixing fp16 x bf16 is an illegal instruction on sm_100a), hence bf16 queries for bf16 corpora.
+template <int kSplit> struct Cfg {
+    static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_BYTES;
+    static constexpr int STAGES = kSplit == 1 ? 4 : 3;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -158,12 +167,15 @@ __host__ __device__ constexpr uint32_t make_idesc(int fmt_a, int fmt_b, int m, i
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-// fmt: 0 = fp16, 1 = bf16 (UMMA F16F32Format).  Queries are always fp16 (power-of-two scaled per
-// query by prepare_queries_f16_kernel); the corpus is fp16 or bf16.
-template <int kFmtB>
+// kFmt: 0 = fp16, 1 = bf16 (UMMA F16F32Format) for both operands.  tmap_q covers the prepared query
+// matrix [kSplit * nq_pad, dim] (term t of query q at row t * nq_pad + q).
+template <int kFmt, int kSplit>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                ScanArgs a, int n_qtiles) {
+    constexpr int STAGES = Cfg<kSplit>::STAGES;
+    constexpr int STAGE_BYTES = Cfg<kSplit>::STAGE_BYTES;
+    constexpr int B_OFF = kSplit * A_BYTES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = base + STAGES * STAGE_BYTES;
@@ -208,15 +220,18 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
                     mbar_wait(empty_bar(s), ph ^ 1u);
                     mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
                     const uint32_t sa = base + s * STAGE_BYTES;
-                    tma_load_2d(sa, &tmap_q, full_bar(s), kb * BK, qt * BM);
-                    tma_load_2d(sa + A_BYTES, &tmap_x, full_bar(s), kb * BK, row0);
+#pragma unroll
+                    for (int part = 0; part < kSplit; ++part)
+                        tma_load_2d(sa + part * A_BYTES, &tmap_q, full_bar(s), kb * BK,
+                                    part * n_qtiles * BM + qt * BM);
+                    tma_load_2d(sa + B_OFF, &tmap_x, full_bar(s), kb * BK, row0);
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ===================== MMA issuer
-            constexpr uint32_t idesc = make_idesc(/*A fp16*/ 0, kFmtB, BM, BN);
+            constexpr uint32_t idesc = make_idesc(kFmt, kFmt, BM, BN);
             int s = 0, it = 0;
             uint32_t ph = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
@@ -229,13 +244,16 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
                     mbar_wait(full_bar(s), ph);
                     tcgen05_fence_after();
                     const uint32_t sa = base + s * STAGE_BYTES;
-                    const uint64_t adesc = make_sw128_desc(sa);
-                    const uint64_t bdesc = make_sw128_desc(sa + A_BYTES);
+                    const uint64_t bdesc = make_sw128_desc(sa + B_OFF);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        // advance 16 elements = 32 bytes inside the swizzle atom: +2 in 16-byte units
-                        umma_f16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc,
-                                 (uint32_t)((kb | k) != 0));
+                    for (int part = 0; part < kSplit; ++part) {
+                        const uint64_t adesc = make_sw128_desc(sa + part * A_BYTES);
+#pragma unroll
+                        for (int k = 0; k < BK / UMMA_K; ++k) {
+                            // advance 16 elements = 32 bytes inside the swizzle atom: +2 (16-byte units)
+                            umma_f16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc,
+                                     (uint32_t)((kb | k | part) != 0));
+                        }
                     }
                     umma_commit(empty_bar(s));  // frees the smem stage when these MMAs retire
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
@@ -297,30 +315,44 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     }
 }
 
-// Queries fp32 [nq, dim] -> fp16 [nq_pad, dim] with a per-query power-of-two scale so the largest
-// component lands in [0.5, 1) (exact to undo: out_scale[q] = 2^e).  Rows >= nq are zero.
-// One warp per query row.
-__global__ void prepare_queries_f16_kernel(const float* __restrict__ q32, __half* __restrict__ q16,
-                                           float* __restrict__ out_scale, int nq, int nq_pad,
-                                           int dim) {
+// Queries fp32 [nq, dim] -> kSplit 16-bit terms [kSplit][nq_pad][dim] with q ~= sum of the terms.
+// fp16: a per-query power-of-two scale first moves the largest component into [0.5, 1) so the
+// fp16 range is never an issue (exact to undo: out_scale[q] = 2^e); bf16 keeps scale 1.
+// Rows >= nq are zero.  One warp per query row.
+template <typename T16, int kSplit>
+__global__ void prepare_queries_kernel(const float* __restrict__ q32, T16* __restrict__ q16,
+                                       float* __restrict__ out_scale, int nq, int nq_pad, int dim) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= nq_pad) return;
-    __half* dst = q16 + (size_t)row * dim;
     if (row >= nq) {
-        for (int c = lane; c < dim; c += 32) dst[c] = __float2half_rn(0.f);
+        for (int t = 0; t < kSplit; ++t)
+            for (int c = lane; c < dim; c += 32)
+                q16[((size_t)t * nq_pad + row) * dim + c] = to_storage<T16>(0.f);
         return;
     }
     const float* src = q32 + (size_t)row * dim;
-    float mx = 0.f;
-    for (int c = lane; c < dim; c += 32) mx = fmaxf(mx, fabsf(src[c]));
+    float up = 1.0f, down = 1.0f;
+    if (sizeof(T16) == 2 && std::is_same<T16, __half>::value) {
+        float mx = 0.f;
+        for (int c = lane; c < dim; c += 32) mx = fmaxf(mx, fabsf(src[c]));
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
-    int e = 0;
-    if (mx > 0.f && mx < __builtin_huge_valf()) (void)frexpf(mx, &e);  // mx = m * 2^e, m in [0.5,1)
-    e = max(-100, min(100, e));
-    const float up = ldexpf(1.0f, -e), down = ldexpf(1.0f, e);
-    for (int c = lane; c < dim; c += 32) dst[c] = __float2half_rn(src[c] * up);
+        for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
+        int e = 0;
+        if (mx > 0.f && mx < __builtin_huge_valf()) (void)frexpf(mx, &e);  // mx = m * 2^e
+        e = max(-100, min(100, e));
+        up = ldexpf(1.0f, -e);
+        down = ldexpf(1.0f, e);
+    }
+    for (int c = lane; c < dim; c += 32) {
+        float rem = src[c] * up;
+#pragma unroll
+        for (int t = 0; t < kSplit; ++t) {
+            T16 h = to_storage<T16>(rem);
+            q16[((size_t)t * nq_pad + row) * dim + c] = h;
+            rem -= from_storage<T16>(h);
+        }
+    }
     if (lane == 0) out_scale[row] = down;
 }
 
