@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""Benchmark of the flat inner-product retrieval hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU algorithm
+
+Workload (default `cfg3`, the configuration the metric is quoted on): exact flat-IP search over a
+synthetic 100 M x 768 fp16 corpus, batch 1024, k = 100, the corpus row-sharded over the N GPUs of
+one box (strong scaling: total rows fixed).  A "step" is one search of one batch.  Prints ONE JSON
+line on rank 0.  Other workloads (`--workload cfg2|cfg4|cfg5`, `--rows`, `--batch`) are for the
+parity / sweep numbers quoted in DESIGN.md, not bench lines.
+
+For N > 1 launch with torchrun (one rank per GPU); RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* are
+read from the environment.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (total_rows, dim, dtype, batch, k)
+    "cfg2": (1_000_000, 768, "f32", 32, 10),
+    "cfg3": (100_000_000, 768, "f16", 1024, 100),
+    "cfg4": (10_000_000, 768, "bf16", 1024, 100),
+    "cfg5": (10_000_000, 384, "f16", 256, 1024),
+}
+METRIC = "QPS (100M x 768 fp16 flat-IP, k=100, batch 1024)"
+UNIT = "queries/s"
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "tflops_burst": float(p["bf16_tflops"]),
+                "tflops_sustained": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "source": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0,
+            "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(self.gpu_index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[4:8]):
+                if val.lower() == "active":
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU legs (oracle = test infrastructure; used ONLY as the reported baseline / reference arm)
+# ------------------------------------------------------------------------------------------
+def cpu_oracle_qps(total_rows, dim, dtype, batch, k, *, target_s=15.0, steps=1, warmup=0,
+                   max_rows=2_000_000):
+    """Times the C/OpenMP/BLAS restatement of faiss-cpu's IndexFlatIP.search (oracle/) on a bounded
+    sample of the workload and scales linearly in corpus rows (a flat scan is linear in N)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+
+    import c_oracle
+    from rag_inference_pipeline_b200.synthetic import synthetic_queries
+
+    q = synthetic_queries(batch, dim)
+    pilot_rows = min(total_rows, 50_000)
+    x = c_oracle.synthetic_corpus(0, pilot_rows, dim, dtype)
+    c_oracle.knn_inner_product(q, x, k)  # warm (thread pool, BLAS init)
+    t0 = time.perf_counter()
+    c_oracle.knn_inner_product(q, x, k)
+    pilot = time.perf_counter() - t0
+    rows = int(min(total_rows, max_rows, max(pilot_rows, pilot_rows * target_s / max(pilot, 1e-6))))
+    if rows != pilot_rows:
+        x = c_oracle.synthetic_corpus(0, rows, dim, dtype)
+    for _ in range(warmup):
+        c_oracle.knn_inner_product(q, x, k)
+    times = []
+    for _ in range(max(1, steps)):
+        t0 = time.perf_counter()
+        c_oracle.knn_inner_product(q, x, k)
+        times.append(time.perf_counter() - t0)
+    t = sum(times) / len(times)
+    scaled = t * (total_rows / rows)
+    return {
+        "value": batch / scaled, "unit": UNIT, "cores": c_oracle.max_threads(), "kind": "port",
+        "sample": (f"oracle/faiss_flat_restatement.c (faiss-cpu algorithm: sgemm blocks + "
+                   f"{'reservoir' if k >= 100 else 'heap'}, OpenBLAS) on {rows} of {total_rows} rows "
+                   f"(fp32 copies of the {dtype} values), batch {batch}, k {k}; {t:.2f} s per search, "
+                   f"scaled linearly to {total_rows} rows; host cpu_count={os.cpu_count()}"),
+        "ms_per_step_scaled": scaled * 1e3,
+    }
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores.
+    faiss-cpu cannot be installed here (no wheel, no network), so this is the oracle port of its
+    algorithm -- the one other place bench.py may execute oracle/."""
+    if rank != 0:
+        return
+    total_rows, dim, dtype, batch, k = workload(args)
+    r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, target_s=12.0, steps=args.steps,
+                       warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": r["ms_per_step_scaled"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "cpu_baseline": {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def workload(args):
+    total_rows, dim, dtype, batch, k = WORKLOADS[args.workload]
+    if args.rows:
+        total_rows = args.rows
+    if args.batch:
+        batch = args.batch
+    if args.k:
+        k = args.k
+    return total_rows, dim, dtype, batch, k
+
+
+def workload_config(args, world):
+    total_rows, dim, dtype, batch, k = workload(args)
+    return {
+        "workload": (f"exact flat-IP search, synthetic {total_rows} x {dim} {dtype} corpus "
+                     f"row-sharded over {world} GPU(s), batch {batch}, k {k}"
+                     + (" (BASELINE configs[2])" if args.workload == "cfg3" and not args.rows else "")),
+        "total_rows": total_rows, "dim": dim, "storage": dtype, "batch": batch, "k": k,
+        "sharding": f"rows/{world}", "l2": "inputs larger than L2 (corpus shard >> 126 MB), no flush",
+    }
+
+
+def run_b200(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from rag_inference_pipeline_b200.sharded import ShardedFlatIPSearcher
+    from rag_inference_pipeline_b200.synthetic import CORPUS_SEED, synthetic_queries
+
+    total_rows, dim, dtype, batch, k = workload(args)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=rank, world_size=world,
+                                     device=local_rank)
+    t0 = time.time()
+    searcher.load_synthetic(CORPUS_SEED)
+    load_s = time.time() - t0
+    if args.variant != "auto":
+        searcher.index.set_variant(args.variant)
+    searcher.index.set_option("profile_events", 1)
+
+    q_np = synthetic_queries(batch, dim)
+    q_dev = torch.from_numpy(q_np).to(dev)
+    q_pinned = torch.from_numpy(q_np).pin_memory()
+
+    # ---- device-resident timing ("value") ----
+    for _ in range(max(args.warmup, 3)):
+        D, I = searcher.search_tensor(q_dev, k)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches = 0
+    scan_ns = 0
+    scan_launches = 0
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        D, I = searcher.search_tensor(q_dev, k)
+        launches += searcher.index.stat("launches") + (1 if world > 1 else 0)
+        scan_ns += searcher.index.stat("scan_time_ns")
+        scan_launches += searcher.index.stat("scan_launches")
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end-to-end timing through the host-buffer API ("e2e"): pinned host queries -> H2D ->
+    #      search -> D2H of distances + ids, every step ----
+    def e2e_step():
+        if world == 1:
+            return searcher.index.search(q_np, k)  # fip_search: pinned staging inside the C ABI
+        qd = q_pinned.to(dev, non_blocking=True)
+        d, i = searcher.search_tensor(qd, k)
+        return d.cpu(), i.cpu()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        De, Ie = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    tms = torch.tensor([ms, e2e_s * 1e3, float(scan_ns)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max, scan_ns_max = (float(v) for v in tms.tolist())
+    variant = searcher.index.last_variant()
+    phases = searcher.index.stat("phases")
+    overflow = searcher.index.stat("overflow_queries")
+
+    # ---- sanity: sorted rows, ids in range, and a host spot check of returned scores ----
+    verify = None
+    if rank == 0:
+        Dh, Ih = D.cpu().numpy(), I.cpu().numpy()
+        ok_sorted = bool(np.all(np.diff(Dh, axis=1) <= 0))
+        ok_range = bool(Ih.min() >= 0 and Ih.max() < total_rows) if total_rows >= k else True
+        from rag_inference_pipeline_b200.synthetic import synthetic_corpus
+        errs = []
+        for qi in (0, batch // 2, batch - 1):
+            for j in (0, k // 2, k - 1):
+                row = synthetic_corpus(int(Ih[qi, j]), 1, dim, dtype)[0].astype(np.float64)
+                errs.append(abs(float(row @ q_np[qi].astype(np.float64)) - float(Dh[qi, j])))
+        verify = {"sorted": ok_sorted, "ids_in_range": ok_range,
+                  "max_abs_err_of_9_recomputed_scores": max(errs)}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, target_s=12.0)
+        cpu_baseline = {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        peaks = load_peaks()
+        ms_per_step = ms_max / args.steps
+        n_local = searcher.local_rows  # rank 0's shard (the largest)
+        esize = 4 if dtype == "f32" else 2
+        scan_s = scan_ns_max * 1e-9
+        scans = max(1, scan_launches)
+        if variant == "tensor" and batch > 210:
+            flops_per_search = 2.0 * batch * n_local * dim   # algorithmic: no padding / split credit
+            achieved = flops_per_search * args.steps / scan_s / 1e12 if scan_s > 0 else None
+            roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops_sustained"],
+                    "unit": "TFLOP/s",
+                    "peak_source": f"{peaks['source']} (sustained cuBLAS bf16, kernel timed inside a long step)"}
+        else:
+            bytes_per_search = float(n_local) * dim * esize + batch * dim * 4 + batch * k * 12
+            achieved = bytes_per_search * args.steps / scan_s / 1e9 if scan_s > 0 else None
+            roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "peak_source": f"{peaks['source']} (copy bandwidth)"}
+        roof["frac"] = (roof["achieved"] / roof["peak"]) if roof["achieved"] else None
+        roof["kernel"] = "tc_scan_kernel" if variant == "tensor" else "stream_scan_kernel"
+        roof["launches_timed"] = scan_launches
+        roof["avg_launch_ms"] = scan_s * 1e3 / scans
+        roof["kernel_share_of_step"] = scan_s * 1e3 / ms_max if ms_max > 0 else None
+        traffic_path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        roof["traffic"] = None
+        if os.path.exists(traffic_path):
+            with open(traffic_path) as f:
+                roof["traffic"] = json.load(f).get(f"{args.workload}_gpus{world}")
+        line = {
+            "metric": METRIC, "value": batch / (ms_per_step * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": {"f16": "f16", "bf16": "bf16", "f32": "f32"}[dtype],
+            "data": "synthetic", "config": workload_config(args, world),
+            "clocks": clocks,
+            "e2e": {"value": batch / (e2e_ms_max * 1e-3 / args.steps), "unit": UNIT,
+                    "h2d_bytes_per_step": batch * dim * 4, "d2h_bytes_per_step": batch * k * 12,
+                    "api": "FlatIPIndex.search (fip_search, host buffers)" if world == 1 else
+                           "ShardedFlatIPSearcher.search_tensor + pinned H2D / D2H"},
+            "gpu_launches": launches,
+            "roofline": roof,
+            "cpu_baseline": cpu_baseline,
+            "variant": variant, "phases_per_search": phases, "overflow_queries": overflow,
+            "corpus_load_s": load_s, "verify": verify,
+        }
+        print(json.dumps(line), flush=True)
+    searcher.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="cfg3")
+    ap.add_argument("--rows", type=int, default=0, help="override total corpus rows")
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--k", type=int, default=0)
+    ap.add_argument("--variant", choices=["auto", "stream", "tensor"], default="auto")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if args.gpus > 1 and world == 1:
+        sys.exit("for --gpus N > 1 launch with: python -m torch.distributed.run --nnodes=1 "
+                 "--nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...")
+    run_b200(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

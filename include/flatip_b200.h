@@ -99,10 +99,13 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
                      int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream);
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
- * streaming kernel for 16-bit storage), "force_safe_mode" (0/1, testing the overflow fallback). */
+ * streaming kernel for 16-bit storage), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
+ * in the tensor-core variant), "profile_events" (0/1: time every scan launch with CUDA events),
+ * "force_safe_mode" (0/1, testing the overflow fallback). */
 int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
- * "candidate_capacity"; cumulative: "total_launches", "total_searches". */
+ * "candidate_capacity", "scan_time_ns" / "scan_launches" (device time and count of the scan
+ * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);
 
 const char* fip_last_error(void);

@@ -169,6 +169,11 @@ struct fip_index {
     int stream_max_batch = 4;
     int force_safe = 0;
     int query_split = 0;  // 0 = auto (1 for fp16 storage, 2 for bf16)
+    int profile = 0;      // 1: bracket every scan launch with CUDA events (bench roofline)
+    std::vector<cudaEvent_t> ev;  // start/stop pairs
+    int ev_used = 0;
+    double st_scan_ms = 0.0;      // device time of the scan kernels of the last search
+    int64_t st_scan_launches = 0;
 
     // per-search workspace
     DevBuf<float> thr, q_scale, q32, out_d;
@@ -385,14 +390,27 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.dtype = idx->cfg.dtype; a.nq = nq;
     a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
 
-    auto scan = [&](int64_t r0, int64_t r1, bool dense) -> int {
-        a.row_begin = (uint32_t)r0; a.row_end = (uint32_t)r1; a.dense = dense ? 1 : 0;
+    auto scan_launch = [&]() -> int {
         if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, nq_pad, split);
         switch (idx->cfg.dtype) {
             case kF32: return launch_stream_phase<float>(c, a, q32);
             case kF16: return launch_stream_phase<__half>(c, a, q32);
             default: return launch_stream_phase<__nv_bfloat16>(c, a, q32);
         }
+    };
+    auto scan = [&](int64_t r0, int64_t r1, bool dense) -> int {
+        a.row_begin = (uint32_t)r0; a.row_end = (uint32_t)r1; a.dense = dense ? 1 : 0;
+        const bool timed = idx->profile && idx->ev_used + 2 <= (int)idx->ev.size();
+        if (timed) FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_used], c.stream));
+        const int before = c.launches;
+        int r = scan_launch();
+        if (r) return r;
+        if (timed) {
+            FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_used + 1], c.stream));
+            idx->ev_used += 2;
+            idx->st_scan_launches += c.launches - before;
+        }
+        return FIP_OK;
     };
 
     const int keff = std::max(k, 16);
@@ -444,6 +462,12 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
                    cudaStream_t stream) {
     SearchCtx c{idx, stream};
     int variant = 0, phases = 0, cap = 0;
+    idx->ev_used = 0;
+    idx->st_scan_launches = 0;
+    if (idx->profile && idx->ev.empty()) {
+        idx->ev.resize(128);
+        for (auto& e : idx->ev) FIP_CUDA(cudaEventCreate(&e));
+    }
     int rc = run_search(c, q32, nq, k, out_d, out_i, idx->force_safe != 0, &variant, &phases, &cap);
     if (rc) return rc;
     int n_over = 0;
@@ -479,6 +503,12 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
         c.launches++;
         FIP_CUDA(cudaStreamSynchronize(stream));  // sel (host vector) must outlive the H2D copy
         phases += p2;
+    }
+    idx->st_scan_ms = 0.0;
+    for (int i = 0; i + 1 < idx->ev_used; i += 2) {
+        float ms = 0.f;
+        FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i], idx->ev[i + 1]));
+        idx->st_scan_ms += ms;
     }
     idx->st_launches = c.launches; idx->st_variant = variant; idx->st_phases = phases;
     idx->st_overflow = n_over; idx->st_cap = cap;
@@ -545,6 +575,7 @@ void fip_destroy(fip_index* idx) {
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
     idx->h_flags.release(); idx->add_stage.release();
+    for (auto& e : idx->ev) cudaEventDestroy(e);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
 }
@@ -744,6 +775,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
     } else if (k == "query_split") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "query_split must be 0 (auto), 1 or 2");
         idx->query_split = (int)value;
+    } else if (k == "profile_events") {
+        idx->profile = value != 0;
     } else if (k == "force_safe_mode") {
         idx->force_safe = value != 0;
     } else {
@@ -760,6 +793,8 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "phases") return idx->st_phases;
     if (k == "overflow_queries") return idx->st_overflow;
     if (k == "candidate_capacity") return idx->st_cap;
+    if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
+    if (k == "scan_launches") return idx->st_scan_launches;
     if (k == "total_launches") return idx->st_total_launches;
     if (k == "total_searches") return idx->st_total_searches;
     return -1;

@@ -208,12 +208,17 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     const int nkb = a.dim / BK;
     const int n_ctiles = (int)((a.row_end - a.row_begin + BN - 1) / BN);
     const int total_tiles = n_ctiles * n_qtiles;
+    // Static schedule: CTA b owns the CONTIGUOUS tile range [t_begin, t_end) of the (corpus tile
+    // major, query tile minor) order, so it walks all query tiles of one corpus tile back to back:
+    // the corpus tile is fetched from HBM once and re-read from L2 for the other query tiles.
+    const int t_begin = (int)(((long long)total_tiles * blockIdx.x) / gridDim.x);
+    const int t_end = (int)(((long long)total_tiles * (blockIdx.x + 1)) / gridDim.x);
 
     if (warp == 0) {
         if (lane == 0) {  // ===================== TMA producer
             int s = 0;
             uint32_t ph = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            for (int t = t_begin; t < t_end; ++t) {
                 const int ct = t / n_qtiles, qt = t - ct * n_qtiles;
                 const int row0 = (int)a.row_begin + ct * BN;
                 for (int kb = 0; kb < nkb; ++kb) {
@@ -234,7 +239,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             constexpr uint32_t idesc = make_idesc(kFmt, kFmt, BM, BN);
             int s = 0, it = 0;
             uint32_t ph = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            for (int t = t_begin; t < t_end; ++t, ++it) {
                 const int buf = it & 1;
                 const uint32_t aph = (uint32_t)(it >> 1) & 1u;
                 mbar_wait(tempty_bar(buf), aph ^ 1u);  // epilogue has drained this accumulator
@@ -264,7 +269,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     } else if (warp >= EPI_WARP0) {  // ========== epilogue: TMEM -> registers -> threshold filter
         const int w = warp - EPI_WARP0;  // == warp % 4: TMEM lanes [32w, 32w+32)
         int it = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        for (int t = t_begin; t < t_end; ++t, ++it) {
             const int ct = t / n_qtiles, qt = t - ct * n_qtiles;
             const int buf = it & 1;
             const uint32_t aph = (uint32_t)(it >> 1) & 1u;
@@ -275,14 +280,14 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             mbar_wait(tfull_bar(buf), aph);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
+            if (a.dense) {
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                float v[32];
-                tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-                const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-                if (row_base >= a.row_end) continue;  // warp-uniform
-                const bool full_chunk = row_base + 32 <= a.row_end;
-                if (a.dense) {
+                for (int c = 0; c < BN / 32; ++c) {
+                    float v[32];
+                    tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+                    const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+                    if (row_base >= a.row_end) continue;  // warp-uniform
+                    const bool full_chunk = row_base + 32 <= a.row_end;
                     if (active) {
                         uint64_t* dst = a.cand + (size_t)q * a.cap + (row_base - a.row_begin);
 #pragma unroll
@@ -290,15 +295,45 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
                             if (full_chunk || row_base + j < a.row_end)
                                 dst[j] = make_key(v[j], row_base + j);
                     }
-                } else {
-                    float mx = v[0];
+                }
+            } else {
+                // Pass 1: count this thread's survivors in the tile (registers only).
+                uint32_t npass = 0;
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    float v[32];
+                    tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+                    const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+                    if (row_base >= a.row_end) continue;  // warp-uniform
+                    const bool full_chunk = row_base + 32 <= a.row_end;
 #pragma unroll
-                    for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
-                    if (mx > thr) {  // rare
+                    for (int j = 0; j < 32; ++j)
+                        npass += (v[j] > thr && (full_chunk || row_base + j < a.row_end)) ? 1u : 0u;
+                }
+                // Pass 2 (only when some thread of the warp has survivors): ONE atomic per thread
+                // reserves its slots, then the accumulator is re-read and the survivors written.
+                // (One returning atomic per survivor would serialise ~1 us round trips.)
+                if (__any_sync(0xFFFFFFFFu, npass != 0)) {
+                    uint32_t slot = npass ? atomicAdd(a.cnt + q, npass) : 0u;
+                    uint64_t* dst = a.cand + (size_t)q * a.cap;
+#pragma unroll 1
+                    for (int c = 0; c < BN / 32; ++c) {
+                        float v[32];
+                        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+                        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+                        if (row_base >= a.row_end) continue;  // warp-uniform
+                        const bool full_chunk = row_base + 32 <= a.row_end;
+                        float mx = v[0];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (v[j] > thr && (full_chunk || row_base + j < a.row_end))
-                                append_candidate(a, q, v[j], row_base + j);
+                        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
+                        if (mx > thr) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (v[j] > thr && (full_chunk || row_base + j < a.row_end)) {
+                                    if (slot < a.cap) dst[slot] = make_key(v[j], row_base + j);
+                                    ++slot;
+                                }
+                        }
                     }
                 }
             }
