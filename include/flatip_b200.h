@@ -100,11 +100,11 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel for 16-bit storage), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
- * in the tensor-core variant), "profile_events" (0/1: time every scan launch with CUDA events),
+ * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs), "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback). */
 int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
- * "candidate_capacity", "scan_time_ns" / "scan_launches" (device time and count of the scan
+ * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_time_ns" / "scan_launches" (device time and count of the scan
  * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);
 

@@ -104,16 +104,18 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-// 2-D K-major tile map: inner dim = `dim` elements of a 16-bit type, outer dim = rows.
-int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t rows, int box_rows) {
+// 2-D K-major tile map: inner dim = `dim` elements, outer dim = rows; box = 128 bytes x 128 rows.
+int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t rows) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    const int esize = dtype_size(dtype);
     cuuint64_t dims[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)dim * 2};
-    cuuint32_t box[2] = {(cuuint32_t)tc::BK, (cuuint32_t)box_rows};
+    cuuint64_t strides[1] = {(cuuint64_t)dim * esize};
+    cuuint32_t box[2] = {(cuuint32_t)(tc::BK_BYTES / esize), (cuuint32_t)tc::BOX_ROWS};
     cuuint32_t estr[2] = {1, 1};
-    CUtensorMapDataType dt =
-        dtype == kBF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    CUtensorMapDataType dt = dtype == kBF16  ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                             : dtype == kF16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                             : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUresult r = enc(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -168,7 +170,9 @@ struct fip_index {
     int variant = FIP_VARIANT_AUTO;
     int stream_max_batch = 4;
     int force_safe = 0;
-    int query_split = 0;  // 0 = auto (1 for fp16 storage, 2 for bf16)
+    int query_split = 0;  // 0 = auto (1 for fp16 / fp32 storage, 2 for bf16)
+    int cta_pair = 0;     // 0 = auto, 1 = single-CTA MMAs, 2 = CTA pairs (cta_group::2)
+    int max_clusters = -1;  // co-resident 2-CTA clusters of the pair kernel (queried once)
     int profile = 0;      // 1: bracket every scan launch with CUDA events (bench roofline)
     std::vector<cudaEvent_t> ev;  // start/stop pairs
     int ev_used = 0;
@@ -179,7 +183,7 @@ struct fip_index {
     DevBuf<float> thr, q_scale, q32, out_d;
     DevBuf<uint32_t> cnt, overflow;
     DevBuf<uint64_t> cand;
-    DevBuf<__half> q16;
+    DevBuf<uint8_t> qprep;  // prepared query terms in the MMA operand type
     DevBuf<int64_t> out_i;
     DevBuf<int> sel;
     DevBuf<float> sub_q, sub_d;
@@ -193,7 +197,7 @@ struct fip_index {
     bool tmap_x_valid = false;
 
     // stats
-    int64_t st_launches = 0, st_variant = 0, st_phases = 0, st_overflow = 0, st_cap = 0;
+    int64_t st_launches = 0, st_variant = 0, st_phases = 0, st_overflow = 0, st_cap = 0, st_pair = 0;
     int64_t st_total_launches = 0, st_total_searches = 0;
 
     size_t row_bytes() const { return (size_t)cfg.dim * dtype_size(cfg.dtype); }
@@ -276,27 +280,59 @@ int launch_stream_phase(SearchCtx& c, const ScanArgs& a, const float* q32) {
     return FIP_OK;
 }
 
-template <int kFmt, int kSplit>
-int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles, int grid) {
-    auto kern = tc::tc_scan_kernel<kFmt, kSplit>;
-    constexpr int smem = tc::Cfg<kSplit>::SMEM_BYTES;
+template <int kFmt, int kSplit, int kCtas>
+int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles) {
+    fip_index* idx = c.idx;
+    auto kern = tc::tc_scan_kernel<kFmt, kSplit, kCtas>;
+    constexpr int smem = tc::Cfg<kFmt, kSplit, kCtas>::SMEM_BYTES;
     FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    kern<<<grid, tc::NUM_THREADS, smem, c.stream>>>(tmap_q, c.idx->tmap_x, a, n_qtiles);
-    FIP_CUDA(cudaGetLastError());
+    const int64_t n_ctiles = ((int64_t)(a.row_end - a.row_begin) + tc::BN - 1) / tc::BN;
+    const int64_t group_tiles = n_ctiles * (n_qtiles / kCtas);
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(tc::NUM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = c.stream;
+    cudaLaunchAttribute attr[1];
+    int groups = idx->num_sms / kCtas;
+    if (kCtas == 2) {
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (idx->max_clusters < 0) {
+            cfg.gridDim = dim3(idx->num_sms / 2 * 2);
+            int n = 0;
+            FIP_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+            idx->max_clusters = std::max(1, n);
+        }
+        groups = std::min(groups, idx->max_clusters);
+    }
+    groups = (int)std::min<int64_t>(groups, group_tiles);
+    cfg.gridDim = dim3((unsigned)(groups * kCtas));
+    FIP_CUDA(cudaLaunchKernelEx(&cfg, kern, tmap_q, idx->tmap_x, a, n_qtiles));
     c.launches++;
     return FIP_OK;
 }
 
-int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int nq_pad, int split) {
-    fip_index* idx = c.idx;
-    const int n_qtiles = nq_pad / tc::BM;
-    const int64_t n_ctiles = ((int64_t)(a.row_end - a.row_begin) + tc::BN - 1) / tc::BN;
-    int grid = (int)std::min<int64_t>(idx->num_sms, n_ctiles * n_qtiles);
-    if (a.dtype == kBF16)
-        return split == 2 ? launch_tc_kernel<1, 2>(c, a, tmap_q, n_qtiles, grid)
-                          : launch_tc_kernel<1, 1>(c, a, tmap_q, n_qtiles, grid);
-    return split == 2 ? launch_tc_kernel<0, 2>(c, a, tmap_q, n_qtiles, grid)
-                      : launch_tc_kernel<0, 1>(c, a, tmap_q, n_qtiles, grid);
+int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles, int split,
+                    bool pair) {
+    switch (a.dtype) {
+        case kF32:
+            return pair ? launch_tc_kernel<2, 1, 2>(c, a, tmap_q, n_qtiles)
+                        : launch_tc_kernel<2, 1, 1>(c, a, tmap_q, n_qtiles);
+        case kBF16:
+            if (split == 2)
+                return pair ? launch_tc_kernel<1, 2, 2>(c, a, tmap_q, n_qtiles)
+                            : launch_tc_kernel<1, 2, 1>(c, a, tmap_q, n_qtiles);
+            return pair ? launch_tc_kernel<1, 1, 2>(c, a, tmap_q, n_qtiles)
+                        : launch_tc_kernel<1, 1, 1>(c, a, tmap_q, n_qtiles);
+        default:
+            if (split == 2)
+                return pair ? launch_tc_kernel<0, 2, 2>(c, a, tmap_q, n_qtiles)
+                            : launch_tc_kernel<0, 2, 1>(c, a, tmap_q, n_qtiles);
+            return pair ? launch_tc_kernel<0, 1, 2>(c, a, tmap_q, n_qtiles)
+                        : launch_tc_kernel<0, 1, 1>(c, a, tmap_q, n_qtiles);
+    }
 }
 
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
@@ -331,18 +367,19 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         return FIP_OK;
     }
     int variant = idx->variant;
-    const bool tc_ok = idx->cfg.dtype != kF32 && dim % tc::BK == 0;
+    const bool tc_ok = (dim * dtype_size(idx->cfg.dtype)) % tc::BK_BYTES == 0;
     if (variant == FIP_VARIANT_AUTO)
         // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
         // CUDA-core kernel stays HBM-bound only while nq * dim FMAs per row fit under the FP32 pipe
-        // (nq <= ~4 for 16-bit storage); above that the tensor pipe is needed to stay on the HBM
-        // roof, and above ~210 flop/byte (nq > ~210) the tensor pipe itself is the roof.
+        // (nq <= ~4); above that the tensor pipe is needed to stay on the HBM roof, and above
+        // ~210 flop/byte (nq > ~210 for 16-bit storage) the tensor pipe itself is the roof.
         variant = (tc_ok && nq > idx->stream_max_batch) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
     if (variant == FIP_VARIANT_TENSOR && !tc_ok)
-        return fail(FIP_ERR_INVALID,
-                    "tensor-core variant needs fp16/bf16 storage and dim % 64 == 0");
-    // The tensor-core scan filters on 16-bit-rounded queries: keep a margin of extra candidates
-    // (k' = k + max(16, k/4)) and rescore the survivors exactly before the final selection.
+        return fail(FIP_ERR_INVALID, "tensor-core variant needs rows that are a multiple of 128 bytes "
+                                     "(dim % 64 == 0 for fp16/bf16, dim % 32 == 0 for fp32)");
+    // The tensor-core scan filters on rounded operands (fp16 / bf16-pair queries, tf32 for fp32
+    // storage): keep a margin of extra candidates (k' = k + max(16, k/4)) and rescore the
+    // survivors exactly (fp32 FMA on the stored values) before the final selection.
     const bool rescore = variant == FIP_VARIANT_TENSOR;
     const int k_out = k;
     if (rescore) k = k + std::max(16, k / 4);
@@ -357,33 +394,48 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     c.launches++;
 
     CUtensorMap tmap_q{};
-    int nq_pad = 0, split = 1;
+    int nq_pad = 0, split = 1, n_qtiles = 0;
+    bool pair = false;
     const float* out_scale = nullptr;
     if (variant == FIP_VARIANT_TENSOR) {
-        nq_pad = (nq + tc::BM - 1) / tc::BM * tc::BM;
-        // fp16 storage: one fp16 term; bf16 storage: bf16 hi + lo terms (see tc_scan.cuh).
-        split = idx->query_split ? idx->query_split : (idx->cfg.dtype == kBF16 ? 2 : 1);
-        FIP_CUDA(idx->q16.ensure((size_t)split * nq_pad * dim));
+        n_qtiles = (nq + tc::BM - 1) / tc::BM;
+        // CTA pairs (cta_group::2) take two query tiles per corpus tile: worth it when that does
+        // not pad the batch by more than ~15 %.
+        pair = idx->cta_pair == 2 || (idx->cta_pair == 0 && n_qtiles >= 2 &&
+                                      (n_qtiles % 2 == 0 || n_qtiles >= 7));
+        if (pair) n_qtiles = (n_qtiles + 1) / 2 * 2;
+        nq_pad = n_qtiles * tc::BM;
+        // fp16 / fp32 storage: one term; bf16 storage: bf16 hi + lo terms (see tc_scan.cuh).
+        split = idx->cfg.dtype == kF32 ? 1
+                : idx->query_split     ? idx->query_split
+                                       : (idx->cfg.dtype == kBF16 ? 2 : 1);
+        const size_t esize = dtype_size(idx->cfg.dtype);
+        FIP_CUDA(idx->qprep.ensure((size_t)split * nq_pad * dim * esize));
         FIP_CUDA(idx->q_scale.ensure(nq));
         const unsigned pgrid = (nq_pad + 7) / 8;
         if (idx->cfg.dtype == kBF16) {
-            auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->q16.p);
+            auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->qprep.p);
             if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
             else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
+        } else if (idx->cfg.dtype == kF16) {
+            auto* dst = reinterpret_cast<__half*>(idx->qprep.p);
+            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
+            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
         } else {
-            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
-            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, idx->q16.p, idx->q_scale.p, nq, nq_pad, dim);
+            tc::prepare_queries_kernel<float, 1><<<pgrid, 256, 0, c.stream>>>(
+                q32, reinterpret_cast<float*>(idx->qprep.p), idx->q_scale.p, nq, nq_pad, dim);
         }
         FIP_CUDA(cudaGetLastError());
         c.launches++;
-        int rc = make_tmap(&tmap_q, idx->q16.p, idx->cfg.dtype, dim, (uint64_t)split * nq_pad, tc::BM);
+        int rc = make_tmap(&tmap_q, idx->qprep.p, idx->cfg.dtype, dim, (uint64_t)split * nq_pad);
         if (rc) return rc;
         if (!idx->tmap_x_valid) {
-            rc = make_tmap(&idx->tmap_x, idx->corpus, idx->cfg.dtype, dim, (uint64_t)n, tc::BN);
+            rc = make_tmap(&idx->tmap_x, idx->corpus, idx->cfg.dtype, dim, (uint64_t)n);
             if (rc) return rc;
             idx->tmap_x_valid = true;
         }
         out_scale = idx->q_scale.p;
+        idx->st_pair = pair ? 2 : 1;
     }
 
     ScanArgs a{};
@@ -391,7 +443,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
 
     auto scan_launch = [&]() -> int {
-        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, nq_pad, split);
+        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, n_qtiles, split, pair);
         switch (idx->cfg.dtype) {
             case kF32: return launch_stream_phase<float>(c, a, q32);
             case kF16: return launch_stream_phase<__half>(c, a, q32);
@@ -445,6 +497,9 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         if (idx->cfg.dtype == kBF16)
             rescore_kernel<__nv_bfloat16><<<grid, 256, 0, c.stream>>>(
                 idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __nv_bfloat16*)idx->corpus, q32, dim);
+        else if (idx->cfg.dtype == kF32)
+            rescore_kernel<float><<<grid, 256, 0, c.stream>>>(
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const float*)idx->corpus, q32, dim);
         else
             rescore_kernel<__half><<<grid, 256, 0, c.stream>>>(
                 idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __half*)idx->corpus, q32, dim);
@@ -571,7 +626,7 @@ void fip_destroy(fip_index* idx) {
     if (idx->stream) cudaStreamSynchronize(idx->stream);
     if (idx->corpus) cudaFree(idx->corpus);
     idx->thr.release(); idx->q_scale.release(); idx->q32.release(); idx->out_d.release();
-    idx->cnt.release(); idx->overflow.release(); idx->cand.release(); idx->q16.release();
+    idx->cnt.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
     idx->h_flags.release(); idx->add_stage.release();
@@ -775,6 +830,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
     } else if (k == "query_split") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "query_split must be 0 (auto), 1 or 2");
         idx->query_split = (int)value;
+    } else if (k == "cta_pair") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "cta_pair must be 0 (auto), 1 or 2");
+        idx->cta_pair = (int)value;
     } else if (k == "profile_events") {
         idx->profile = value != 0;
     } else if (k == "force_safe_mode") {
@@ -793,6 +851,7 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "phases") return idx->st_phases;
     if (k == "overflow_queries") return idx->st_overflow;
     if (k == "candidate_capacity") return idx->st_cap;
+    if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
     if (k == "scan_launches") return idx->st_scan_launches;
     if (k == "total_launches") return idx->st_total_launches;

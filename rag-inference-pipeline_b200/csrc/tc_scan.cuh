@@ -5,177 +5,146 @@
 // Replaces faiss's exhaustive_inner_product_blas (sgemm on 4096 x 1024 blocks + block result
 // handler) behind IndexFlatIP.search (/root/reference/src/pipeline/components/faiss_store.py:152).
 //
-// Tiling: queries are the UMMA M operand (128 rows = the 128 TMEM lanes), corpus rows the N
-// operand (256 columns), K = 64 elements (one 128-byte swizzle atom) per pipeline stage.  Putting
-// queries on the lanes makes the fused selection thread-private: `tcgen05.ld.32x32b` gives every
-// epilogue thread ONE query and a run of corpus-row scores, so the thread compares against that
-// query's threshold held in a register and only the rare survivors touch memory.
+// Tiling: queries are the UMMA M operand (128 rows per CTA = the 128 TMEM lanes), corpus rows the N
+// operand (256 columns), K = 128 bytes (one SWIZZLE_128B atom: 64 fp16/bf16 or 32 fp32 elements)
+// per pipeline stage.  Putting queries on the lanes makes the fused selection thread-private:
+// `tcgen05.ld.32x32b` gives every epilogue thread ONE query and a run of corpus-row scores, so the
+// thread compares against that query's threshold held in a register and only the rare survivors
+// touch memory.
 //
-// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
-// warp 2 = TMEM allocator, warps 4..7 = epilogue (warp % 4 selects the TMEM lane quarter).
-// Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer (MMA <-> epilogue),
-// persistent static tile schedule (tile = corpus tile major, query tile minor, so CTAs running
-// concurrently share corpus tiles through L2 and HBM reads the corpus once).
+// kCtas = 2 (CTA pair, cta_group::2): two CTAs on one TPC share a corpus tile.  Each loads its own
+// 128-query A tile and HALF of the 256-row B tile; one thread of the leader CTA issues
+// M = 256 x N = 256 MMAs that read both halves and write each CTA's 128 x 256 accumulator into that
+// CTA's TMEM.  Per tile and CTA the L2 -> smem traffic drops from A + B to A + B/2 and a stage
+// shrinks from 48 KB to 32 KB, so the ring is 6 deep instead of 4.
+//
+// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader
+// CTA only), warp 2 = TMEM allocator, warps 4..7 = epilogue (warp % 4 selects the TMEM lane
+// quarter).  Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
+// (MMA <-> epilogue), persistent static tile schedule (corpus tile major, query tile minor, so the
+// query tiles of one corpus tile run back to back and re-read it from L2; HBM sees it once).
 #pragma once
-
-#include <cuda.h>
 
 #include <type_traits>
 
 #include "common.cuh"
 #include "synthetic.cuh"
+#include "tc_ptx.cuh"
 
 namespace fip {
 namespace tc {
 
-constexpr int BM = 128;   // queries per tile  (UMMA M)
-constexpr int BN = 256;   // corpus rows per tile (UMMA N)
-constexpr int BK = 64;    // K elements per stage: 64 * 2 B = 128 B = one SWIZZLE_128B atom
-constexpr int UMMA_K = 16;
-constexpr int A_BYTES = BM * BK * 2;   // one query operand tile (per split term)
-constexpr int B_BYTES = BN * BK * 2;
-constexpr int TMEM_COLS = 512;  // two 256-column fp32 accumulators
+constexpr int BM = 128;          // queries per CTA tile (UMMA M per CTA)
+constexpr int BN = 256;          // corpus rows per tile (UMMA N)
+constexpr int BK_BYTES = 128;    // K bytes per stage = one SWIZZLE_128B atom
+constexpr int BOX_ROWS = 128;    // rows per TMA box (both operands)
+constexpr int A_BYTES = BM * BK_BYTES;         // one query operand tile (per split term)
+constexpr int B_BYTES = BN * BK_BYTES;         // full corpus tile
+constexpr int TMEM_COLS = 512;   // two 256-column fp32 accumulators
 constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
-// kSplit = number of 16-bit terms the fp32 queries are split into (q = q0 + q1 ...): 1 for fp16
-// storage (fp16 queries, 2^-11 rounding, repaired by the exact rescoring pass), 2 for bf16 storage
-// (bf16 hi + lo, 2^-17).  tcgen05.mma kind::f16 needs A and B in the SAME 16-bit format
+
+// kFmt: 0 = fp16, 1 = bf16 (kind::f16), 2 = fp32 storage read as tf32 (kind::tf32).
+// kSplit = number of terms the fp32 queries are split into (q = q0 + q1): 1 for fp16 / fp32
+// storage, 2 for bf16 storage (bf16 hi + lo, 2^-17).  tcgen05.mma needs A and B in the SAME format
 // (mixing fp16 x bf16 is an illegal instruction on sm_100a), hence bf16 queries for bf16 corpora.
-template <int kSplit> struct Cfg {
-    static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_BYTES;
-    static constexpr int STAGES = kSplit == 1 ? 4 : 3;
+// The filter runs on these rounded products; survivors are rescored exactly (select.cuh).
+template <int kFmt, int kSplit, int kCtas> struct Cfg {
+    static constexpr int ELEM_BYTES = kFmt == 2 ? 4 : 2;
+    static constexpr int BK = BK_BYTES / ELEM_BYTES;       // elements per stage
+    static constexpr int MMAS_PER_STAGE = 4;               // 32 bytes of K per instruction
+    static constexpr int B_LOCAL_BYTES = B_BYTES / kCtas;  // this CTA's share of the corpus tile
+    static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_LOCAL_BYTES;
+    static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n\t"
-        "selp.b32 %0, 1, 0, P1;\n\t"
-        "}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity), "r"(0x989680u)
-        : "memory");
-    return ok != 0;
-}
-// Blocking wait with a watchdog: a pipeline bug traps (CUDA error on the host) instead of hanging
-// the GPU.  No legitimate wait in this kernel lasts anywhere near 2^32 cycles (> 2 s).
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > (1ll << 32)) {
-            printf("flatip_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n",
-                   (int)blockIdx.x, (int)threadIdx.x, bar, parity);
-            __trap();
+// Epilogue of one 128 x 256 accumulator for one thread (= one query): filter against `thr`.
+// Two passes over TMEM, both guarded by a per-chunk max so the common "nothing passes" case costs
+// ~0.6 instructions per score: pass 1 counts the survivors, ONE atomic per thread reserves their
+// slots, pass 2 writes them with predicated (branch-free) stores.
+__device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t taddr, int q, bool active,
+                                                float thr, uint32_t tile_row0) {
+    uint32_t npass = 0;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+        if (row_base >= a.row_end) break;  // warp-uniform
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (row_base + j >= a.row_end) v[j] = kNegInf;
+        }
+        float mx = v[0];
+#pragma unroll
+        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
+        if (mx > thr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) npass += v[j] > thr ? 1u : 0u;
+        }
+    }
+    if (!__any_sync(0xFFFFFFFFu, npass != 0)) return;
+    uint32_t slot = (npass && active) ? atomicAdd(a.cnt + q, npass) : 0u;
+    uint64_t* dst = a.cand + (size_t)q * a.cap;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+        if (row_base >= a.row_end) break;
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        if (row_base + 32 > a.row_end) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (row_base + j >= a.row_end) v[j] = kNegInf;
+        }
+        float mx = v[0];
+#pragma unroll
+        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
+        if (mx > thr) {
+            const uint32_t inv_row = 0xFFFFFFFFu - row_base;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const bool pass = v[j] > thr;
+                st_global_v2_pred(dst + slot, inv_row - (uint32_t)j, orderable_f32(v[j]),
+                                  pass && slot < a.cap);
+                slot += pass ? 1u : 0u;
+            }
         }
     }
 }
-__device__ __forceinline__ void fence_barrier_init() {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
-                                            int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() {
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_after() {
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem),
-                 "r"(ncols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
-                 : "memory");
-}
-// tcgen05.commit: arrive on `bar` once every MMA issued so far by this thread has completed.
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
-                 : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, 128 x BN x 16, fp32 accumulate.
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
-                                         uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
-          "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
-          "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
-          "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]),
-          "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+
+// Phase 0: every score of the tile is written at slot = row - row_begin (no threshold yet).
+__device__ __forceinline__ void epilogue_dense(const ScanArgs& a, uint32_t taddr, int q, bool active,
+                                               uint32_t tile_row0) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+        if (row_base >= a.row_end) break;
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        uint64_t* dst = a.cand + (size_t)q * a.cap + (row_base - a.row_begin);
+        const uint32_t inv_row = 0xFFFFFFFFu - row_base;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+        for (int j = 0; j < 32; ++j)
+            st_global_v2_pred(dst + j, inv_row - (uint32_t)j, orderable_f32(v[j]),
+                              active && row_base + j < a.row_end);
+    }
 }
 
-// Shared-memory matrix descriptor for a K-major operand tile laid out by TMA with SWIZZLE_128B:
-// rows of 128 bytes, 8-row groups 1024 bytes apart (SBO); LBO is unused for swizzled K-major.
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);  // start address       bits [0,14)
-    d |= (uint64_t)1 << 16;                        // leading byte offset bits [16,30) (ignored)
-    d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset  bits [32,46)
-    d |= (uint64_t)1 << 46;                        // descriptor version 1 (sm_100)
-    d |= (uint64_t)2 << 61;                        // layout type SWIZZLE_128B
-    return d;
-}
-// Instruction descriptor, kind::f16: fp32 accumulate, both operands K-major.
-__host__ __device__ constexpr uint32_t make_idesc(int fmt_a, int fmt_b, int m, int n) {
-    return (1u << 4) | ((uint32_t)fmt_a << 7) | ((uint32_t)fmt_b << 10) |
-           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-
-// kFmt: 0 = fp16, 1 = bf16 (UMMA F16F32Format) for both operands.  tmap_q covers the prepared query
-// matrix [kSplit * nq_pad, dim] (term t of query q at row t * nq_pad + q).
-template <int kFmt, int kSplit>
+// tmap_q covers the prepared query matrix [kSplit * nq_pad, dim] (term t of query q at row
+// t * nq_pad + q); tmap_x the corpus shard [n_rows, dim].  Both use [BK x 128]-element boxes.
+// Launch with a (2,1,1) cluster when kCtas == 2; gridDim.x must then be even.
+template <int kFmt, int kSplit, int kCtas>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                ScanArgs a, int n_qtiles) {
-    constexpr int STAGES = Cfg<kSplit>::STAGES;
-    constexpr int STAGE_BYTES = Cfg<kSplit>::STAGE_BYTES;
+    using C = Cfg<kFmt, kSplit, kCtas>;
+    constexpr int STAGES = C::STAGES;
+    constexpr int STAGE_BYTES = C::STAGE_BYTES;
     constexpr int B_OFF = kSplit * A_BYTES;
+    constexpr int B_BOXES = C::B_LOCAL_BYTES / (BOX_ROWS * BK_BYTES);  // 2 (single CTA) or 1 (pair)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = base + STAGES * STAGE_BYTES;
@@ -189,6 +158,8 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = kCtas == 2 ? cluster_ctarank() : 0u;
+    const bool leader = cta_rank == 0;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_q);
@@ -196,53 +167,73 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 128); }
+        // tempty: one arrival per epilogue warp of every CTA of the group (lives in the leader)
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 4 * kCtas); }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+    if (warp == 2) tmem_alloc<kCtas>(tmem_slot, TMEM_COLS);
     tcgen05_fence_before();
-    __syncthreads();
+    if (kCtas == 2) cluster_sync_all(); else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
-    const int nkb = a.dim / BK;
+    const int nkb = (a.dim * C::ELEM_BYTES) / BK_BYTES;
     const int n_ctiles = (int)((a.row_end - a.row_begin + BN - 1) / BN);
-    const int total_tiles = n_ctiles * n_qtiles;
-    // Static schedule: CTA b owns the CONTIGUOUS tile range [t_begin, t_end) of the (corpus tile
-    // major, query tile minor) order, so it walks all query tiles of one corpus tile back to back:
-    // the corpus tile is fetched from HBM once and re-read from L2 for the other query tiles.
-    const int t_begin = (int)(((long long)total_tiles * blockIdx.x) / gridDim.x);
-    const int t_end = (int)(((long long)total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    // A "group tile" is one corpus tile x kCtas adjacent query tiles (one per CTA of the group).
+    const int n_qgroups = n_qtiles / kCtas;
+    const int total_tiles = n_ctiles * n_qgroups;
+    const int group = (int)blockIdx.x / kCtas, n_groups = (int)gridDim.x / kCtas;
+    // Static schedule: group g owns the CONTIGUOUS range [t_begin, t_end) of the (corpus tile major,
+    // query group minor) order, so it walks all query tiles of one corpus tile back to back.
+    const int t_begin = (int)(((long long)total_tiles * group) / n_groups);
+    const int t_end = (int)(((long long)total_tiles * (group + 1)) / n_groups);
 
     if (warp == 0) {
-        if (lane == 0) {  // ===================== TMA producer
+        if (lane == 0) {  // ===================== TMA producer (every CTA loads its own operands)
+            const uint32_t full0 = kCtas == 2 ? mapa_shared(full_bar(0), 0) : full_bar(0);
             int s = 0;
             uint32_t ph = 0;
             for (int t = t_begin; t < t_end; ++t) {
-                const int ct = t / n_qtiles, qt = t - ct * n_qtiles;
-                const int row0 = (int)a.row_begin + ct * BN;
+                const int ct = t / n_qgroups, qg = t - ct * n_qgroups;
+                const int qt = qg * kCtas + (int)cta_rank;
+                const int row0 = (int)a.row_begin + ct * BN + (int)cta_rank * C::B_LOCAL_BYTES / BK_BYTES;
                 for (int kb = 0; kb < nkb; ++kb) {
                     mbar_wait(empty_bar(s), ph ^ 1u);
-                    mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
                     const uint32_t sa = base + s * STAGE_BYTES;
+                    if (kCtas == 1) {
+                        mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
 #pragma unroll
-                    for (int part = 0; part < kSplit; ++part)
-                        tma_load_2d(sa + part * A_BYTES, &tmap_q, full_bar(s), kb * BK,
-                                    part * n_qtiles * BM + qt * BM);
-                    tma_load_2d(sa + B_OFF, &tmap_x, full_bar(s), kb * BK, row0);
+                        for (int part = 0; part < kSplit; ++part)
+                            tma_load_2d(sa + part * A_BYTES, &tmap_q, full_bar(s), kb * C::BK,
+                                        part * n_qtiles * BM + qt * BM);
+#pragma unroll
+                        for (int b = 0; b < B_BOXES; ++b)
+                            tma_load_2d(sa + B_OFF + b * BOX_ROWS * BK_BYTES, &tmap_x, full_bar(s),
+                                        kb * C::BK, row0 + b * BOX_ROWS);
+                    } else {
+                        // the leader's barrier collects the bytes of BOTH CTAs' loads
+                        if (leader) mbar_arrive_expect_tx(full_bar(s), 2 * STAGE_BYTES);
+                        const uint32_t fb = full0 + 8u * s;
+#pragma unroll
+                        for (int part = 0; part < kSplit; ++part)
+                            tma_load_2d_pair(sa + part * A_BYTES, &tmap_q, fb, kb * C::BK,
+                                             part * n_qtiles * BM + qt * BM);
+                        tma_load_2d_pair(sa + B_OFF, &tmap_x, fb, kb * C::BK, row0);
+                    }
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ===================== MMA issuer
-            constexpr uint32_t idesc = make_idesc(kFmt, kFmt, BM, BN);
+        if (lane == 0 && leader) {  // ===================== MMA issuer
+            constexpr uint32_t idesc = make_idesc(kFmt, kFmt, BM * kCtas, BN);
+            constexpr int kKind = kFmt == 2 ? 1 : 0;
             int s = 0, it = 0;
             uint32_t ph = 0;
             for (int t = t_begin; t < t_end; ++t, ++it) {
                 const int buf = it & 1;
                 const uint32_t aph = (uint32_t)(it >> 1) & 1u;
-                mbar_wait(tempty_bar(buf), aph ^ 1u);  // epilogue has drained this accumulator
+                mbar_wait<kCtas == 2>(tempty_bar(buf), aph ^ 1u);  // epilogues drained this accumulator
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)buf * BN;
                 for (int kb = 0; kb < nkb; ++kb) {
@@ -254,23 +245,25 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
                     for (int part = 0; part < kSplit; ++part) {
                         const uint64_t adesc = make_sw128_desc(sa + part * A_BYTES);
 #pragma unroll
-                        for (int k = 0; k < BK / UMMA_K; ++k) {
-                            // advance 16 elements = 32 bytes inside the swizzle atom: +2 (16-byte units)
-                            umma_f16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc,
-                                     (uint32_t)((kb | k | part) != 0));
+                        for (int k = 0; k < C::MMAS_PER_STAGE; ++k) {
+                            // advance 32 bytes inside the swizzle atom: +2 (16-byte units)
+                            umma<kCtas, kKind>(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc,
+                                               (uint32_t)((kb | k | part) != 0));
                         }
                     }
-                    umma_commit(empty_bar(s));  // frees the smem stage when these MMAs retire
+                    umma_commit<kCtas>(empty_bar(s));  // frees the smem stage (in both CTAs)
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
                 }
-                umma_commit(tfull_bar(buf));  // accumulator complete -> epilogue
+                umma_commit<kCtas>(tfull_bar(buf));  // accumulator complete -> epilogue(s)
             }
         }
     } else if (warp >= EPI_WARP0) {  // ========== epilogue: TMEM -> registers -> threshold filter
         const int w = warp - EPI_WARP0;  // == warp % 4: TMEM lanes [32w, 32w+32)
+        const uint32_t tempty0 = kCtas == 2 ? mapa_shared(tempty_bar(0), 0) : tempty_bar(0);
         int it = 0;
         for (int t = t_begin; t < t_end; ++t, ++it) {
-            const int ct = t / n_qtiles, qt = t - ct * n_qtiles;
+            const int ct = t / n_qgroups, qg = t - ct * n_qgroups;
+            const int qt = qg * kCtas + (int)cta_rank;
             const int buf = it & 1;
             const uint32_t aph = (uint32_t)(it >> 1) & 1u;
             const int q = qt * BM + w * 32 + lane;
@@ -280,82 +273,32 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             mbar_wait(tfull_bar(buf), aph);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
-            if (a.dense) {
-#pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    float v[32];
-                    tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-                    const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-                    if (row_base >= a.row_end) continue;  // warp-uniform
-                    const bool full_chunk = row_base + 32 <= a.row_end;
-                    if (active) {
-                        uint64_t* dst = a.cand + (size_t)q * a.cap + (row_base - a.row_begin);
-#pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (full_chunk || row_base + j < a.row_end)
-                                dst[j] = make_key(v[j], row_base + j);
-                    }
-                }
-            } else {
-                // Pass 1: count this thread's survivors in the tile (registers only).
-                uint32_t npass = 0;
-#pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    float v[32];
-                    tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-                    const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-                    if (row_base >= a.row_end) continue;  // warp-uniform
-                    const bool full_chunk = row_base + 32 <= a.row_end;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        npass += (v[j] > thr && (full_chunk || row_base + j < a.row_end)) ? 1u : 0u;
-                }
-                // Pass 2 (only when some thread of the warp has survivors): ONE atomic per thread
-                // reserves its slots, then the accumulator is re-read and the survivors written.
-                // (One returning atomic per survivor would serialise ~1 us round trips.)
-                if (__any_sync(0xFFFFFFFFu, npass != 0)) {
-                    uint32_t slot = npass ? atomicAdd(a.cnt + q, npass) : 0u;
-                    uint64_t* dst = a.cand + (size_t)q * a.cap;
-#pragma unroll 1
-                    for (int c = 0; c < BN / 32; ++c) {
-                        float v[32];
-                        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-                        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-                        if (row_base >= a.row_end) continue;  // warp-uniform
-                        const bool full_chunk = row_base + 32 <= a.row_end;
-                        float mx = v[0];
-#pragma unroll
-                        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
-                        if (mx > thr) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (v[j] > thr && (full_chunk || row_base + j < a.row_end)) {
-                                    if (slot < a.cap) dst[slot] = make_key(v[j], row_base + j);
-                                    ++slot;
-                                }
-                        }
-                    }
-                }
-            }
+            if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0);
+            else epilogue_filter(a, taddr, q, active, thr, tile_row0);
             tcgen05_fence_before();
-            mbar_arrive(tempty_bar(buf));
+            __syncwarp();
+            if (lane == 0) {
+                if (kCtas == 2) mbar_arrive_cluster(tempty0 + 8u * buf);
+                else mbar_arrive(tempty_bar(buf));
+            }
         }
     }
 
     tcgen05_fence_before();
-    __syncthreads();
+    if (kCtas == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 2) {
         tcgen05_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        tmem_dealloc<kCtas>(tmem_base, TMEM_COLS);
     }
 }
 
-// Queries fp32 [nq, dim] -> kSplit 16-bit terms [kSplit][nq_pad][dim] with q ~= sum of the terms.
-// fp16: a per-query power-of-two scale first moves the largest component into [0.5, 1) so the
-// fp16 range is never an issue (exact to undo: out_scale[q] = 2^e); bf16 keeps scale 1.
+// Queries fp32 [nq, dim] -> kSplit terms [kSplit][nq_pad][dim] in the MMA operand type T, with
+// q ~= sum of the terms.  fp16: a per-query power-of-two scale first moves the largest component
+// into [0.5, 1) so the fp16 range is never an issue (exact to undo: out_scale[q] = 2^e); bf16 and
+// fp32 (tf32 operand: the tensor core ignores the low 13 mantissa bits) keep scale 1.
 // Rows >= nq are zero.  One warp per query row.
-template <typename T16, int kSplit>
-__global__ void prepare_queries_kernel(const float* __restrict__ q32, T16* __restrict__ q16,
+template <typename T, int kSplit>
+__global__ void prepare_queries_kernel(const float* __restrict__ q32, T* __restrict__ qt,
                                        float* __restrict__ out_scale, int nq, int nq_pad, int dim) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
@@ -363,12 +306,12 @@ __global__ void prepare_queries_kernel(const float* __restrict__ q32, T16* __res
     if (row >= nq) {
         for (int t = 0; t < kSplit; ++t)
             for (int c = lane; c < dim; c += 32)
-                q16[((size_t)t * nq_pad + row) * dim + c] = to_storage<T16>(0.f);
+                qt[((size_t)t * nq_pad + row) * dim + c] = to_storage<T>(0.f);
         return;
     }
     const float* src = q32 + (size_t)row * dim;
     float up = 1.0f, down = 1.0f;
-    if (sizeof(T16) == 2 && std::is_same<T16, __half>::value) {
+    if (std::is_same<T, __half>::value) {
         float mx = 0.f;
         for (int c = lane; c < dim; c += 32) mx = fmaxf(mx, fabsf(src[c]));
 #pragma unroll
@@ -383,9 +326,9 @@ __global__ void prepare_queries_kernel(const float* __restrict__ q32, T16* __res
         float rem = src[c] * up;
 #pragma unroll
         for (int t = 0; t < kSplit; ++t) {
-            T16 h = to_storage<T16>(rem);
-            q16[((size_t)t * nq_pad + row) * dim + c] = h;
-            rem -= from_storage<T16>(h);
+            T h = to_storage<T>(rem);
+            qt[((size_t)t * nq_pad + row) * dim + c] = h;
+            rem -= from_storage<T>(h);
         }
     }
     if (lane == 0) out_scale[row] = down;

@@ -60,6 +60,9 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
     idx.add_synthetic(n, 1234, 0)
     print(f"generated {n}x{dim} {dtype} in {time.time()-t:.2f}s")
     idx.set_variant(variant)
+    if os.environ.get("FIP_CTA_PAIR"):
+        idx.set_option("cta_pair", int(os.environ["FIP_CTA_PAIR"]))
+    idx.set_option("profile_events", 1)
     q = torch.from_numpy(synthetic_queries(nq, dim)).cuda()
     D = torch.empty((nq, k), dtype=torch.float32, device="cuda")
     I = torch.empty((nq, k), dtype=torch.int64, device="cuda")
@@ -78,7 +81,8 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
     tfs = 2.0 * nq * n * dim / ms / 1e9
     print(f"TIME {variant} {dtype} n={n} d={dim} nq={nq} k={k}: {ms:.3f} ms/search  {nq/ms*1e3:.0f} QPS  "
           f"{gbs:.0f} GB/s  {tfs:.1f} TFLOP/s  launches={idx.stat('launches')} phases={idx.stat('phases')} "
-          f"overflow={idx.stat('overflow_queries')}")
+          f"overflow={idx.stat('overflow_queries')} cta_group={idx.stat('cta_group')} "
+          f"scan_ms={idx.stat('scan_time_ns')/1e6:.3f}")
     idx.close()
 
 

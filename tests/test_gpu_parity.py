@@ -60,8 +60,6 @@ def test_reference_fixture_inputs():
 @pytest.mark.parametrize("variant", ["stream", "tensor"])
 def test_golden_synthetic_cases(tag, variant):
     dtype, shape, q, k = tag.split("_")
-    if variant == "tensor" and dtype == "f32":
-        pytest.skip("tensor-core variant stores 16-bit corpora")
     n, dim = (int(v) for v in shape.split("x"))
     nq, k = int(q[1:]), int(k[1:])
     g = np.load(os.path.join(GOLDEN, "synthetic_cases.npz"))
@@ -85,6 +83,10 @@ CASES = [
     ("tensor", "bf16", 70001, 768, 200, 100),   # config 4: bf16, ragged corpus tile
     ("tensor", "bf16", 300, 64, 5, 10),         # corpus smaller than one tile
     ("tensor", "f16", 4096, 128, 128, 2048),    # k at its maximum, corpus == one dense phase
+    ("tensor", "f32", 20000, 768, 32, 10),      # config 2 shape on the tf32 tensor path
+    ("tensor", "f32", 33333, 96, 150, 100),     # fp32, dim % 32 == 0 only, two query tiles (CTA pair)
+    ("tensor", "f16", 30000, 768, 1000, 100),   # 8 query tiles: CTA-pair kernel, ragged last tile
+    ("tensor", "bf16", 25000, 128, 900, 50),    # 8 tiles (7 padded to 8), bf16 hi+lo terms, pair
 ]
 
 
@@ -116,7 +118,29 @@ def test_auto_variant_follows_arithmetic_intensity():
     idx = _index(128, "f32")
     idx.add_synthetic(5000, 1, 0)
     idx.search(synthetic.synthetic_queries(64, 128), 5)
-    assert idx.last_variant() == "stream"      # fp32 storage: exact fp32 products
+    assert idx.last_variant() == "tensor"      # fp32 storage: tf32 filter + exact fp32 rescoring
+    idx.search(synthetic.synthetic_queries(3, 128), 5)
+    assert idx.last_variant() == "stream"
+    idx.close()
+
+
+@pytest.mark.parametrize("dtype,dim", [("f16", 256), ("bf16", 128), ("f32", 64)])
+def test_cta_pair_and_single_cta_kernels_agree(dtype, dim):
+    """The cta_group::2 kernel and the single-CTA kernel must return identical results."""
+    n, nq, k = 41000, 300, 20
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    idx.set_variant("tensor")
+    q = synthetic.synthetic_queries(nq, dim)
+    out = {}
+    for mode in (1, 2):
+        idx.set_option("cta_pair", mode)
+        out[mode] = idx.search(q, k)
+        assert idx.stat("cta_group") == mode
+    np.testing.assert_array_equal(out[1][1], out[2][1])
+    np.testing.assert_array_equal(out[1][0], out[2][0])
+    Dr, Ir = flatip_oracle.flat_ip_search(q, c_oracle.synthetic_corpus(0, n, dim, dtype), k)
+    _check(out[2][0], out[2][1], Dr, Ir, dtype)
     idx.close()
 
 
