@@ -52,6 +52,29 @@ __host__ __device__ inline uint32_t key_row(uint64_t key) {
     return 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFu);
 }
 
+// Lists in GLOBAL memory hold RAW keys (score bits << 32 | 0xFFFFFFFF - row): the scan epilogues
+// store them without any ALU work per survivor.  The select kernel converts raw <-> orderable when
+// it stages a list in shared memory.  The row half is identical in both forms.
+__host__ __device__ inline uint64_t make_raw_key(float score, uint32_t row) {
+#ifdef __CUDA_ARCH__
+    uint32_t u = __float_as_uint(score);
+#else
+    uint32_t u;
+    memcpy(&u, &score, 4);
+#endif
+    return ((uint64_t)u << 32) | (uint64_t)(0xFFFFFFFFu - row);
+}
+__host__ __device__ inline uint64_t raw_to_key(uint64_t raw) {
+    uint32_t u = (uint32_t)(raw >> 32);
+    uint32_t o = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    return ((uint64_t)o << 32) | (raw & 0xFFFFFFFFull);
+}
+__host__ __device__ inline uint64_t key_to_raw(uint64_t key) {
+    uint32_t o = (uint32_t)(key >> 32);
+    uint32_t u = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+    return ((uint64_t)u << 32) | (key & 0xFFFFFFFFull);
+}
+
 constexpr float kNegInf = -__builtin_huge_valf();
 constexpr float kLowestF32 = -FLT_MAX;  // faiss pads unfilled result slots with -FLT_MAX / id -1
 
@@ -75,7 +98,7 @@ struct ScanArgs {
 __device__ __forceinline__ void append_candidate(const ScanArgs& a, int q, float score,
                                                  uint32_t row) {
     uint32_t slot = atomicAdd(a.cnt + q, 1u);
-    if (slot < a.cap) a.cand[(size_t)q * a.cap + slot] = make_key(score, row);
+    if (slot < a.cap) a.cand[(size_t)q * a.cap + slot] = make_raw_key(score, row);
 }
 
 inline int next_pow2(int v) {

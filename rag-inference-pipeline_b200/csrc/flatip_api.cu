@@ -129,10 +129,6 @@ __global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* overflow,
     if (i < nq) { thr[i] = kNegInf; cnt[i] = 0u; }
     if (i <= nq) overflow[i] = 0u;
 }
-__global__ void fill_u32_kernel(uint32_t* p, uint32_t v, int n) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = v;
-}
 __global__ void fill_padding_kernel(float* d, int64_t* id, int64_t n) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n) { d[i] = kLowestF32; id[i] = -1; }
@@ -178,6 +174,7 @@ struct fip_index {
     int ev_used = 0;
     double st_scan_ms = 0.0;      // device time of the scan kernels of the last search
     int64_t st_scan_launches = 0;
+    std::vector<float> st_scan_each, st_gap_each;  // per scan launch; gap = time to the next scan
 
     // per-search workspace
     DevBuf<float> thr, q_scale, q32, out_d;
@@ -336,16 +333,15 @@ int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, 
 }
 
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
-                  int64_t* out_i, const float* out_scale) {
+                  int64_t* out_i, const float* out_scale, int64_t dense_count = -1) {
     SelectArgs s{};
     s.cand = idx->cand.p; s.cnt = idx->cnt.p; s.thr = idx->thr.p; s.cap = (uint32_t)cap; s.k = k;
     s.final_pass = final_pass ? 1 : 0; s.out_d = out_d; s.out_i = out_i; s.id_base = idx->cfg.id_base;
-    s.out_scale = out_scale; s.overflow = idx->overflow.p;
-    size_t smem = (size_t)cap * sizeof(uint64_t);
+    s.out_scale = out_scale; s.overflow = idx->overflow.p; s.dense_count = (int)dense_count;
+    size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
-    int threads = std::min(1024, std::max(64, cap / 2));
-    select_topk_kernel<<<nq, threads, smem, c.stream>>>(s);
+    select_topk_kernel<<<nq, kSelectThreads, smem, c.stream>>>(s);
     FIP_CUDA(cudaGetLastError());
     c.launches++;
     return FIP_OK;
@@ -472,12 +468,9 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     int64_t m = std::min<int64_t>(n, cap);
     int rc = scan(0, m, true);
     if (rc) return rc;
-    fill_u32_kernel<<<(nq + 255) / 256, 256, 0, c.stream>>>(idx->cnt.p, (uint32_t)m, nq);
-    FIP_CUDA(cudaGetLastError());
-    c.launches++;
     int64_t pos = m;
     phases++;
-    rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale);
+    rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale, m);
     if (rc) return rc;
     while (pos < n) {
         if (safe) m = std::max<int64_t>(256, (int64_t)(cap - k) / 256 * 256);
@@ -560,10 +553,17 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
         phases += p2;
     }
     idx->st_scan_ms = 0.0;
+    idx->st_scan_each.clear();
+    idx->st_gap_each.clear();
     for (int i = 0; i + 1 < idx->ev_used; i += 2) {
         float ms = 0.f;
         FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i], idx->ev[i + 1]));
         idx->st_scan_ms += ms;
+        idx->st_scan_each.push_back(ms);
+        if (i + 2 < idx->ev_used) {
+            FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i + 1], idx->ev[i + 2]));
+            idx->st_gap_each.push_back(ms);
+        }
     }
     idx->st_launches = c.launches; idx->st_variant = variant; idx->st_phases = phases;
     idx->st_overflow = n_over; idx->st_cap = cap;
@@ -854,6 +854,12 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
     if (k == "scan_launches") return idx->st_scan_launches;
+    if (k.rfind("scan_ns_", 0) == 0 || k.rfind("gap_ns_", 0) == 0) {
+        const bool gap = k[0] == 'g';
+        const auto& v = gap ? idx->st_gap_each : idx->st_scan_each;
+        const size_t i = (size_t)atoi(k.c_str() + (gap ? 7 : 8));
+        return i < v.size() ? (int64_t)(v[i] * 1e6) : -1;
+    }
     if (k == "total_launches") return idx->st_total_launches;
     if (k == "total_searches") return idx->st_total_searches;
     return -1;

@@ -37,6 +37,7 @@ struct SelectArgs {
     uint32_t cap;
     int k;
     int final_pass;       // 1: also write D / I
+    int dense_count;      // >= 0: every list holds exactly this many entries (after a dense phase)
     float* out_d;         // [nq, k]
     int64_t* out_i;       // [nq, k]
     int64_t id_base;      // global id of local row 0
@@ -44,37 +45,143 @@ struct SelectArgs {
     uint32_t* overflow;   // [1 + nq]: [0] = any overflow, [1+q] = query q overflowed
 };
 
-// One CTA per query.  Dynamic smem: next_pow2(cap) * 8 bytes.
-__global__ void select_topk_kernel(SelectArgs a) {
+constexpr int kSelectThreads = 256;
+
+// k-th largest of the c distinct keys in s_keys (1 <= k <= c) by most-significant-digit radix
+// select, 8 bits per round, starting at the highest bit in which the keys differ at all.  Keys are
+// distinct (the low word encodes the row), so the answer is unique.  Whole CTA; returns the key.
+__device__ __forceinline__ uint64_t kth_largest_key(const uint64_t* s_keys, int c, int k,
+                                                    uint32_t* s_hist /*[256]*/, uint64_t* s_red /*[20]*/) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kSelectThreads / 32;
+    // CTA-wide min / max -> the bits above `hi` are common to every key
+    uint64_t mn = ~0ull, mx = 0ull;
+    for (int i = tid; i < c; i += kSelectThreads) { uint64_t x = s_keys[i]; mn = min(mn, x); mx = max(mx, x); }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, off));
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
+    }
+    if (lane == 0) { s_red[warp] = mn; s_red[kWarps + warp] = mx; }
+    __syncthreads();
+    mn = s_red[0]; mx = s_red[kWarps];
+#pragma unroll
+    for (int w = 1; w < kWarps; ++w) { mn = min(mn, s_red[w]); mx = max(mx, s_red[kWarps + w]); }
+    __syncthreads();
+    if (k == 1) return mx;
+    if (k == c) return mn;
+    int undecided = 64 - __clzll((long long)(mn ^ mx));  // low bits not yet fixed (>= 1: keys differ)
+    uint64_t prefix = undecided >= 64 ? 0ull : (mx >> undecided);
+    int kk = k;                                          // rank among the keys matching `prefix`
+    while (true) {
+        const int shift = undecided > 8 ? undecided - 8 : 0;
+        const int nbits = undecided - shift;             // 1..8 bits decided this round
+        s_hist[tid] = 0u;                                // kSelectThreads == 256 bins
+        __syncthreads();
+        for (int i = tid; i < c; i += kSelectThreads) {
+            const uint64_t x = s_keys[i];
+            const bool match = undecided >= 64 || (x >> undecided) == prefix;
+            if (match) atomicAdd(&s_hist[(uint32_t)(x >> shift) & ((1u << nbits) - 1u)], 1u);
+        }
+        __syncthreads();
+        if (warp == 0) {  // bin holding the kk-th largest: walk bins from the top
+            uint32_t h[8], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { h[j] = s_hist[lane * 8 + j]; sum += h[j]; }
+            uint32_t suf = sum;  // inclusive suffix sum over lanes (lane 31 = highest bins)
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                uint32_t t = __shfl_down_sync(0xFFFFFFFFu, suf, off);
+                if (lane + off < 32) suf += t;
+            }
+            if (suf >= (uint32_t)kk && suf - sum < (uint32_t)kk) {
+                uint32_t above = suf - sum;
+                int b = lane * 8;
+#pragma unroll
+                for (int j = 7; j >= 0; --j) {
+                    if (above + h[j] >= (uint32_t)kk) { b = lane * 8 + j; sum = h[j]; break; }
+                    above += h[j];
+                }
+                s_red[0] = (uint64_t)b; s_red[1] = above; s_red[2] = sum;
+            }
+        }
+        __syncthreads();
+        const uint32_t b = (uint32_t)s_red[0], above = (uint32_t)s_red[1], in_bin = (uint32_t)s_red[2];
+        __syncthreads();
+        prefix = (prefix << nbits) | b;
+        kk -= (int)above;
+        undecided = shift;
+        if (undecided == 0) return prefix;
+        if (in_bin == 1u) {  // a single key carries this prefix: it is the answer
+            for (int i = tid; i < c; i += kSelectThreads)
+                if ((s_keys[i] >> undecided) == prefix) s_red[3] = s_keys[i];
+            __syncthreads();
+            const uint64_t r = s_red[3];
+            __syncthreads();
+            return r;
+        }
+    }
+}
+
+// One CTA (kSelectThreads threads) per query.  Dynamic smem: (cap + next_pow2(k)) * 8 bytes.
+// Intermediate passes only need the k best as a SET (any order) and the new threshold: radix
+// select + compaction.  The final pass sorts those k (bitonic over next_pow2(k) keys) and emits.
+__global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs a) {
     extern __shared__ __align__(16) uint64_t s_keys[];
-    const int q = blockIdx.x;
-    uint32_t c = a.cnt[q];
+    __shared__ uint32_t s_hist[256];
+    __shared__ uint64_t s_red[20];
+    __shared__ uint32_t s_count;
+    const int q = blockIdx.x, tid = threadIdx.x;
+    uint32_t c = a.dense_count >= 0 ? (uint32_t)a.dense_count : a.cnt[q];
     if (c > a.cap) {  // the scan dropped candidates: this query must be redone (host fallback)
-        if (threadIdx.x == 0) { a.overflow[0] = 1u; a.overflow[1 + q] = 1u; }
+        if (tid == 0) { a.overflow[0] = 1u; a.overflow[1 + q] = 1u; }
         c = a.cap;
     }
-    int n = 1;
-    while (n < (int)c) n <<= 1;
-    const uint64_t* src = a.cand + (size_t)q * a.cap;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = i < (int)c ? src[i] : 0ull;
+    uint64_t* list = a.cand + (size_t)q * a.cap;
+    for (int i = tid; i < (int)c; i += kSelectThreads) s_keys[i] = raw_to_key(list[i]);
+    if (tid == 0) s_count = 0u;
     __syncthreads();
-    bitonic_sort_desc(s_keys, n);
     const int keep = min((int)c, a.k);
+    uint64_t kth = 0ull;  // every key >= kth is kept (all of them when c <= k)
+    if ((int)c > a.k) kth = kth_largest_key(s_keys, (int)c, a.k, s_hist, s_red);
     if (!a.final_pass) {
-        uint64_t* dst = a.cand + (size_t)q * a.cap;
-        for (int i = threadIdx.x; i < keep; i += blockDim.x) dst[i] = s_keys[i];
-        if (threadIdx.x == 0) {
+        if ((int)c > a.k) {
+            for (int i = tid; i < (int)c; i += kSelectThreads) {
+                const uint64_t x = s_keys[i];
+                if (x >= kth) list[atomicAdd(&s_count, 1u)] = key_to_raw(x);
+            }
+        }
+        if (tid == 0) {
             a.cnt[q] = (uint32_t)keep;
-            a.thr[q] = keep >= a.k ? key_score(s_keys[a.k - 1]) : kNegInf;
+            float t = kNegInf;
+            if ((int)c > a.k) t = key_score(kth);
+            else if ((int)c == a.k) {  // exactly k: threshold = the smallest key's score
+                uint64_t mn = ~0ull;
+                for (int i = 0; i < (int)c; ++i) mn = min(mn, s_keys[i]);
+                t = key_score(mn);
+            }
+            a.thr[q] = t;
         }
-    } else {
-        const float scale = a.out_scale ? a.out_scale[q] : 1.0f;
-        for (int i = threadIdx.x; i < a.k; i += blockDim.x) {
-            uint64_t key = i < keep ? s_keys[i] : 0ull;
-            bool valid = key != 0ull;
-            a.out_d[(size_t)q * a.k + i] = valid ? key_score(key) * scale : kLowestF32;
-            a.out_i[(size_t)q * a.k + i] = valid ? a.id_base + (int64_t)key_row(key) : -1;
-        }
+        return;
+    }
+    // final pass: gather the survivors, sort them, emit
+    int n = 1;
+    while (n < keep) n <<= 1;
+    uint64_t* s_out = s_keys + a.cap;
+    for (int i = tid; i < n; i += kSelectThreads) s_out[i] = 0ull;
+    __syncthreads();
+    for (int i = tid; i < (int)c; i += kSelectThreads) {
+        const uint64_t x = s_keys[i];
+        if (x >= kth) s_out[atomicAdd(&s_count, 1u)] = x;
+    }
+    __syncthreads();
+    bitonic_sort_desc(s_out, n);
+    const float scale = a.out_scale ? a.out_scale[q] : 1.0f;
+    for (int i = tid; i < a.k; i += kSelectThreads) {
+        uint64_t key = i < keep ? s_out[i] : 0ull;
+        bool valid = key != 0ull;
+        a.out_d[(size_t)q * a.k + i] = valid ? key_score(key) * scale : kLowestF32;
+        a.out_i[(size_t)q * a.k + i] = valid ? a.id_base + (int64_t)key_row(key) : -1;
     }
 }
 
@@ -116,7 +223,7 @@ __global__ void rescore_kernel(uint64_t* __restrict__ cand, const uint32_t* __re
         }
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);
-        if (lane == 0) cand[(size_t)q * cap + slot] = make_key(acc, row);
+        if (lane == 0) cand[(size_t)q * cap + slot] = make_raw_key(acc, row);
     }
 }
 

@@ -156,7 +156,7 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0) {
                 if (row < a.row_end && q < a.nq) {
                     const float s = acc[t];
                     if (a.dense) {
-                        a.cand[(size_t)q * a.cap + (row - a.row_begin)] = make_key(s, row);
+                        a.cand[(size_t)q * a.cap + (row - a.row_begin)] = make_raw_key(s, row);
                     } else if (s > s_thr[j]) {
                         append_candidate(a, q, s, row);
                     }

@@ -225,12 +225,34 @@ __host__ __device__ constexpr uint32_t make_idesc(int fmt_a, int fmt_b, int m, i
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-// Predicated 8-byte global store (no branch): the epilogue's survivor writes.
+// Predicated 8-byte global store (no branch): the dense phase's writes.
 __device__ __forceinline__ void st_global_v2_pred(uint64_t* ptr, uint32_t lo, uint32_t hi, bool p) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t@p st.global.v2.u32 [%0], {%1, %2};\n\t}" ::"l"(ptr),
         "r"(lo), "r"(hi), "r"((uint32_t)p)
         : "memory");
+}
+// One step of the epilogue's branch-free compaction into the thread's shared-memory strip:
+// if (v > thr) { *saddr = v; saddr += stride; mask |= bit; }  -- four 32-bit SASS instructions per
+// score, the only loop-carried dependencies are the predicated updates of `saddr` and `mask`.
+__device__ __forceinline__ void strip_append(uint32_t& saddr, uint32_t& mask, float v, float thr,
+                                             uint32_t bit, uint32_t stride) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.gt.f32 p, %2, %3;\n\t"
+        "@p st.shared.f32 [%0], %2;\n\t"
+        "@p add.u32 %0, %0, %5;\n\t"
+        "@p or.b32 %1, %1, %4;\n\t"
+        "}"
+        : "+r"(saddr), "+r"(mask)
+        : "f"(v), "f"(thr), "r"(bit), "r"(stride)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
 }
 
 }  // namespace tc

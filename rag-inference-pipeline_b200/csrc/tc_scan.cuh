@@ -18,9 +18,9 @@
 // CTA's TMEM.  Per tile and CTA the L2 -> smem traffic drops from A + B to A + B/2 and a stage
 // shrinks from 48 KB to 32 KB, so the ring is 6 deep instead of 4.
 //
-// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader
-// CTA only), warp 2 = TMEM allocator, warps 4..7 = epilogue (warp % 4 selects the TMEM lane
-// quarter).  Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
+// Warp roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader
+// CTA only), warp 2 = TMEM allocator, warps 4..11 = epilogue (warp % 4 selects the TMEM
+// lane quarter, the two warps of a quarter split the 256 columns).  Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
 // (MMA <-> epilogue), persistent static tile schedule (corpus tile major, query tile minor, so the
 // query tiles of one corpus tile run back to back and re-read it from L2; HBM sees it once).
 #pragma once
@@ -41,8 +41,9 @@ constexpr int BOX_ROWS = 128;    // rows per TMA box (both operands)
 constexpr int A_BYTES = BM * BK_BYTES;         // one query operand tile (per split term)
 constexpr int B_BYTES = BN * BK_BYTES;         // full corpus tile
 constexpr int TMEM_COLS = 512;   // two 256-column fp32 accumulators
-constexpr int NUM_THREADS = 256;
 constexpr int EPI_WARP0 = 4;
+constexpr int EPI_WARPS = 8;     // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int NUM_THREADS = (EPI_WARP0 + EPI_WARPS) * 32;
 
 // kFmt: 0 = fp16, 1 = bf16 (kind::f16), 2 = fp32 storage read as tf32 (kind::tf32).
 // kSplit = number of terms the fp32 queries are split into (q = q0 + q1): 1 for fp16 / fp32
@@ -55,19 +56,29 @@ template <int kFmt, int kSplit, int kCtas> struct Cfg {
     static constexpr int MMAS_PER_STAGE = 4;               // 32 bytes of K per instruction
     static constexpr int B_LOCAL_BYTES = B_BYTES / kCtas;  // this CTA's share of the corpus tile
     static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_LOCAL_BYTES;
-    static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
+    // operand ring + the epilogue's compaction strip + barriers
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 32 * 1024 + 1024 /*align slack*/ + 256;
 };
 
-// Epilogue of one 128 x 256 accumulator for one thread (= one query): filter against `thr`.
-// Two passes over TMEM, both guarded by a per-chunk max so the common "nothing passes" case costs
-// ~0.6 instructions per score: pass 1 counts the survivors, ONE atomic per thread reserves their
-// slots, pass 2 writes them with predicated (branch-free) stores.
-__device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t taddr, int q, bool active,
-                                                float thr, uint32_t tile_row0) {
-    uint32_t npass = 0;
+// Epilogue of one thread (= one query) over EPI_CHUNKS chunks of 32 accumulator columns starting
+// at chunk c0: filter against `thr` in ONE pass over TMEM.
+//   * Every group of 8 scores is guarded by its max, so "nothing passes" (the common case: ~1e-4 of
+//     the scores survive in the main phase) costs ~0.75 instructions per score.
+//   * A group with a survivor is compacted branch-free into the thread's strip in shared memory
+//     (values only; which columns passed is kept as a 32-bit mask in a register).
+//   * After a chunk with survivors ONE atomic reserves the list slots and the strip is written out
+//     as raw keys.
+constexpr int STRIP_SLOTS = 32;                              // one chunk's worth per thread
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr uint32_t STRIP_STRIDE = EPI_THREADS * 4;           // bytes between a thread's slots
+constexpr int STRIP_BYTES = STRIP_SLOTS * EPI_THREADS * 4;   // 32 KB
+constexpr int EPI_CHUNKS = BN / 32 / (EPI_WARPS / 4);        // chunks per epilogue warp and tile
+
+__device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t sbase, uint32_t taddr, int q,
+                                                float thr, uint32_t tile_row0, int c0) {
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = c0; c < c0 + EPI_CHUNKS; ++c) {
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
         if (row_base >= a.row_end) break;  // warp-uniform
         float v[32];
@@ -77,39 +88,34 @@ __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t tadd
             for (int j = 0; j < 32; ++j)
                 if (row_base + j >= a.row_end) v[j] = kNegInf;
         }
-        float mx = v[0];
+        uint32_t saddr = sbase, mask = 0u;
 #pragma unroll
-        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
-        if (mx > thr) {
+        for (int g = 0; g < 4; ++g) {
+            float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
+            mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+            if (mx > thr) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) npass += v[j] > thr ? 1u : 0u;
+                for (int j = 0; j < 8; ++j)
+                    strip_append(saddr, mask, v[8 * g + j], thr, 1u << (8 * g + j), STRIP_STRIDE);
+            }
         }
-    }
-    if (!__any_sync(0xFFFFFFFFu, npass != 0)) return;
-    uint32_t slot = (npass && active) ? atomicAdd(a.cnt + q, npass) : 0u;
-    uint64_t* dst = a.cand + (size_t)q * a.cap;
-#pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-        if (row_base >= a.row_end) break;
-        float v[32];
-        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-        if (row_base + 32 > a.row_end) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (row_base + j >= a.row_end) v[j] = kNegInf;
-        }
-        float mx = v[0];
-#pragma unroll
-        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, v[j]);
-        if (mx > thr) {
-            const uint32_t inv_row = 0xFFFFFFFFu - row_base;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const bool pass = v[j] > thr;
-                st_global_v2_pred(dst + slot, inv_row - (uint32_t)j, orderable_f32(v[j]),
-                                  pass && slot < a.cap);
-                slot += pass ? 1u : 0u;
+        if (mask) {
+            // mask != 0 implies an active query (inactive lanes carry thr = +inf).  A reservation
+            // that does not fit writes nothing: cnt > cap makes the select kernel flag the query as
+            // overflowed and the host redoes it in safe mode.
+            const uint32_t n = (uint32_t)__popc(mask);
+            uint32_t slot = atomicAdd(a.cnt + q, n);
+            if (slot + n <= a.cap) {
+                uint64_t* list = a.cand + (size_t)q * a.cap;
+                const uint32_t inv_row0 = 0xFFFFFFFFu - row_base;
+                uint32_t rd = sbase;
+                while (mask) {
+                    const uint32_t j = (uint32_t)__ffs((int)mask) - 1u;
+                    mask &= mask - 1u;
+                    const uint32_t bits = ld_shared_u32(rd);
+                    rd += STRIP_STRIDE;
+                    list[slot++] = ((uint64_t)bits << 32) | (uint64_t)(inv_row0 - j);
+                }
             }
         }
     }
@@ -117,9 +123,9 @@ __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t tadd
 
 // Phase 0: every score of the tile is written at slot = row - row_begin (no threshold yet).
 __device__ __forceinline__ void epilogue_dense(const ScanArgs& a, uint32_t taddr, int q, bool active,
-                                               uint32_t tile_row0) {
+                                               uint32_t tile_row0, int c0, int c1) {
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = c0; c < c1; ++c) {
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
         if (row_base >= a.row_end) break;
         float v[32];
@@ -128,7 +134,7 @@ __device__ __forceinline__ void epilogue_dense(const ScanArgs& a, uint32_t taddr
         const uint32_t inv_row = 0xFFFFFFFFu - row_base;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            st_global_v2_pred(dst + j, inv_row - (uint32_t)j, orderable_f32(v[j]),
+            st_global_v2_pred(dst + j, inv_row - (uint32_t)j, __float_as_uint(v[j]),
                               active && row_base + j < a.row_end);
     }
 }
@@ -147,7 +153,8 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     constexpr int B_BOXES = C::B_LOCAL_BYTES / (BOX_ROWS * BK_BYTES);  // 2 (single CTA) or 1 (pair)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = base + STAGES * STAGE_BYTES;
+    const uint32_t strip_base = base + STAGES * STAGE_BYTES;
+    const uint32_t bar_base = strip_base + STRIP_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
@@ -168,7 +175,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         // tempty: one arrival per epilogue warp of every CTA of the group (lives in the leader)
-        for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 4 * kCtas); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), EPI_WARPS * kCtas); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<kCtas>(tmem_slot, TMEM_COLS);
@@ -258,7 +265,10 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             }
         }
     } else if (warp >= EPI_WARP0) {  // ========== epilogue: TMEM -> registers -> threshold filter
-        const int w = warp - EPI_WARP0;  // == warp % 4: TMEM lanes [32w, 32w+32)
+        // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the columns
+        const int w = (warp - EPI_WARP0) & 3;
+        const int c0 = ((warp - EPI_WARP0) >> 2) * EPI_CHUNKS;
+        const uint32_t sbase = strip_base + ((uint32_t)threadIdx.x - EPI_WARP0 * 32) * 4u;
         const uint32_t tempty0 = kCtas == 2 ? mapa_shared(tempty_bar(0), 0) : tempty_bar(0);
         int it = 0;
         for (int t = t_begin; t < t_end; ++t, ++it) {
@@ -273,8 +283,8 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             mbar_wait(tfull_bar(buf), aph);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
-            if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0);
-            else epilogue_filter(a, taddr, q, active, thr, tile_row0);
+            if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0, c0, c0 + EPI_CHUNKS);
+            else epilogue_filter(a, sbase, taddr, q, thr, tile_row0, c0);
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) {

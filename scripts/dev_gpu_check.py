@@ -62,6 +62,8 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
     idx.set_variant(variant)
     if os.environ.get("FIP_CTA_PAIR"):
         idx.set_option("cta_pair", int(os.environ["FIP_CTA_PAIR"]))
+    if os.environ.get("FIP_SPLIT"):
+        idx.set_option("query_split", int(os.environ["FIP_SPLIT"]))
     idx.set_option("profile_events", 1)
     q = torch.from_numpy(synthetic_queries(nq, dim)).cuda()
     D = torch.empty((nq, k), dtype=torch.float32, device="cuda")
@@ -83,6 +85,9 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
           f"{gbs:.0f} GB/s  {tfs:.1f} TFLOP/s  launches={idx.stat('launches')} phases={idx.stat('phases')} "
           f"overflow={idx.stat('overflow_queries')} cta_group={idx.stat('cta_group')} "
           f"scan_ms={idx.stat('scan_time_ns')/1e6:.3f}")
+    sc = [idx.stat(f"scan_ns_{i}") / 1e6 for i in range(16) if idx.stat(f"scan_ns_{i}") >= 0]
+    gp = [idx.stat(f"gap_ns_{i}") / 1e6 for i in range(16) if idx.stat(f"gap_ns_{i}") >= 0]
+    print("  scans(ms):", " ".join(f"{v:.3f}" for v in sc), "| gaps(ms):", " ".join(f"{v:.3f}" for v in gp))
     idx.close()
 
 
