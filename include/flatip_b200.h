@@ -100,10 +100,14 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel for 16-bit storage), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
- * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs), "profile_events" (0/1: time every scan launch with CUDA events),
+ * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),
+ * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant), "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback). */
 int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
+ * "uncertified_queries" (queries the tensor-core filter could not certify exact and that were redone
+ * with a tighter variant), "stream_redo_queries" (of those and the overflowed ones, how many ended
+ * on the exact streaming kernel), "query_split_used",
  * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_time_ns" / "scan_launches" (device time and count of the scan
  * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);

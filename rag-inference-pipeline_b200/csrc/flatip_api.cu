@@ -124,10 +124,11 @@ int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t r
     return FIP_OK;
 }
 
-__global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* overflow, int nq) {
+// flags: [0 .. nq] overflow (any, per query), [nq+1 .. 2nq+1] uncertified (any, per query)
+__global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* flags, int nq) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nq) { thr[i] = kNegInf; cnt[i] = 0u; }
-    if (i <= nq) overflow[i] = 0u;
+    if (i <= nq) { flags[i] = 0u; flags[nq + 1 + i] = 0u; }
 }
 __global__ void fill_padding_kernel(float* d, int64_t* id, int64_t n) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -177,7 +178,9 @@ struct fip_index {
     std::vector<float> st_scan_each, st_gap_each;  // per scan launch; gap = time to the next scan
 
     // per-search workspace
-    DevBuf<float> thr, q_scale, q32, out_d;
+    DevBuf<float> thr, q_scale, q_eps, q32, out_d;
+    DevBuf<float> max_norm2;  // [1] max squared row norm of the shard (certificate radius)
+    int certify = 1;          // 0: skip the exactness certificate of the tensor-core variant
     DevBuf<uint32_t> cnt, overflow;
     DevBuf<uint64_t> cand;
     DevBuf<uint8_t> qprep;  // prepared query terms in the MMA operand type
@@ -195,6 +198,7 @@ struct fip_index {
 
     // stats
     int64_t st_launches = 0, st_variant = 0, st_phases = 0, st_overflow = 0, st_cap = 0, st_pair = 0;
+    int64_t st_uncert = 0, st_split = 0, st_stream_redo = 0;
     int64_t st_total_launches = 0, st_total_searches = 0;
 
     size_t row_bytes() const { return (size_t)cfg.dim * dtype_size(cfg.dtype); }
@@ -227,7 +231,7 @@ int reserve_rows(fip_index* idx, int64_t want) {
 
 int cap_for_k(int k, bool safe) {
     if (safe) return kMaxCap;
-    int cap = std::max(4096, 16 * next_pow2(k));
+    int cap = std::max(4096, 32 * next_pow2(k));
     return std::min(cap, kMaxCap);
 }
 
@@ -332,12 +336,28 @@ int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, 
     }
 }
 
+// How a (sub-)search is run.  rigor 0 = the index's configured variant; 1 = a tighter filter
+// (two query terms for 16-bit storage, else the exact streaming kernel); 2 = streaming kernel.
+struct Mode {
+    bool safe = false;  // phases short enough that a candidate list can never overflow
+    int rigor = 0;
+};
+struct SearchInfo {
+    int variant = 0, phases = 0, cap = 0, split = 0;
+    bool certified_path = false;  // the run can raise "uncertified" flags
+};
+
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
-                  int64_t* out_i, const float* out_scale, int64_t dense_count = -1) {
+                  int64_t* out_i, const float* out_scale, int64_t dense_count = -1,
+                  int keep_max = 0 /* > 0: exactness window on (tensor-core variant) */) {
     SelectArgs s{};
     s.cand = idx->cand.p; s.cnt = idx->cnt.p; s.thr = idx->thr.p; s.cap = (uint32_t)cap; s.k = k;
     s.final_pass = final_pass ? 1 : 0; s.out_d = out_d; s.out_i = out_i; s.id_base = idx->cfg.id_base;
     s.out_scale = out_scale; s.overflow = idx->overflow.p; s.dense_count = (int)dense_count;
+    if (keep_max > 0) {
+        s.win_eps = idx->q_eps.p; s.win_scale = idx->q_scale.p; s.keep_max = keep_max;
+        s.uncert = idx->overflow.p + (nq + 1);
+    }
     size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
@@ -348,22 +368,25 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
 }
 
 // One complete search of `nq` device-resident fp32 queries; results to device out_d / out_i.
-// Does not synchronise.  safe: phases short enough that a list can never overflow.
+// Does not synchronise.
 int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
-               bool safe, int* variant_used, int* phases_used, int* cap_used) {
+               Mode mode, SearchInfo* info) {
     fip_index* idx = c.idx;
     const int64_t n = idx->n_rows;
     const int dim = idx->cfg.dim;
+    const int dtype = idx->cfg.dtype;
+    *info = SearchInfo{};
+    FIP_CUDA(idx->overflow.ensure(2 * ((size_t)nq + 1)));
     if (n == 0) {
         int64_t tot = (int64_t)nq * k;
         fill_padding_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c.stream>>>(out_d, out_i, tot);
         FIP_CUDA(cudaGetLastError());
+        FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, 2 * ((size_t)nq + 1) * sizeof(uint32_t), c.stream));
         c.launches++;
-        *variant_used = 0; *phases_used = 0; *cap_used = 0;
         return FIP_OK;
     }
     int variant = idx->variant;
-    const bool tc_ok = (dim * dtype_size(idx->cfg.dtype)) % tc::BK_BYTES == 0;
+    const bool tc_ok = (dim * dtype_size(dtype)) % tc::BK_BYTES == 0;
     if (variant == FIP_VARIANT_AUTO)
         // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
         // CUDA-core kernel stays HBM-bound only while nq * dim FMAs per row fit under the FP32 pipe
@@ -373,16 +396,32 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (variant == FIP_VARIANT_TENSOR && !tc_ok)
         return fail(FIP_ERR_INVALID, "tensor-core variant needs rows that are a multiple of 128 bytes "
                                      "(dim % 64 == 0 for fp16/bf16, dim % 32 == 0 for fp32)");
-    // The tensor-core scan filters on rounded operands (fp16 / bf16-pair queries, tf32 for fp32
-    // storage): keep a margin of extra candidates (k' = k + max(16, k/4)) and rescore the
-    // survivors exactly (fp32 FMA on the stored values) before the final selection.
+    // Query terms of the tensor-core filter: one term (fp16 / bf16 / tf32) by default; rigor 1
+    // adds a second 16-bit term (error 2^-17 instead of 2^-11 / 2^-9).
+    int split = dtype == kF32 ? 1 : (idx->query_split ? idx->query_split : 1);
+    if (variant == FIP_VARIANT_TENSOR && mode.rigor == 1) {
+        if (dtype != kF32 && split == 1) split = 2;
+        else variant = FIP_VARIANT_STREAM;
+    }
+    if (mode.rigor >= 2) variant = FIP_VARIANT_STREAM;
+    // The tensor-core scan filters on rounded operands, so its lists keep more than k candidates
+    // and the survivors are rescored exactly (fp32 FMA on the stored values) before the final
+    // selection.  With the certificate on (default) every candidate inside the query's exactness
+    // window stays (select.cuh): k_plan is only the size the phases are planned for and keep_max
+    // the truncation limit.  With it off a fixed margin of k_plan - k extra candidates is kept.
     const bool rescore = variant == FIP_VARIANT_TENSOR;
+    const bool certify = rescore && idx->certify != 0;
     const int k_out = k;
-    if (rescore) k = k + std::max(16, k / 4);
-    const int cap = cap_for_k(k, safe);
+    // (bf16 single-term filter: eps is ~6x that of fp16, its window holds ~0.65 k extra candidates
+    // on Gaussian data by the Cauchy-Schwarz bound)
+    const int k_plan = !rescore ? k
+                       : (dtype == kBF16 && split == 1) ? k + std::max(48, 3 * k / 4)
+                                                        : k + std::max(16, k / 4);
+    const int cap = cap_for_k(k_plan, mode.safe);
+    const int keep_max = certify ? std::min(cap / 2, k_out + 2 * (k_plan - k_out)) : 0;
+    const int k_sel = certify ? k_out : k_plan;   // what the intermediate selects look for
     FIP_CUDA(idx->thr.ensure(nq));
     FIP_CUDA(idx->cnt.ensure(nq));
-    FIP_CUDA(idx->overflow.ensure((size_t)nq + 1));
     FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
 
     init_lists_kernel<<<(nq + 256) / 256, 256, 0, c.stream>>>(idx->thr.p, idx->cnt.p, idx->overflow.p, nq);
@@ -390,7 +429,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     c.launches++;
 
     CUtensorMap tmap_q{};
-    int nq_pad = 0, split = 1, n_qtiles = 0;
+    int nq_pad = 0, n_qtiles = 0;
     bool pair = false;
     const float* out_scale = nullptr;
     if (variant == FIP_VARIANT_TENSOR) {
@@ -401,32 +440,34 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
                                       (n_qtiles % 2 == 0 || n_qtiles >= 7));
         if (pair) n_qtiles = (n_qtiles + 1) / 2 * 2;
         nq_pad = n_qtiles * tc::BM;
-        // fp16 / fp32 storage: one term; bf16 storage: bf16 hi + lo terms (see tc_scan.cuh).
-        split = idx->cfg.dtype == kF32 ? 1
-                : idx->query_split     ? idx->query_split
-                                       : (idx->cfg.dtype == kBF16 ? 2 : 1);
-        const size_t esize = dtype_size(idx->cfg.dtype);
+        const size_t esize = dtype_size(dtype);
         FIP_CUDA(idx->qprep.ensure((size_t)split * nq_pad * dim * esize));
         FIP_CUDA(idx->q_scale.ensure(nq));
+        FIP_CUDA(idx->q_eps.ensure(nq));
         const unsigned pgrid = (nq_pad + 7) / 8;
-        if (idx->cfg.dtype == kBF16) {
+        // what software cannot see: fp32 accumulation in the tensor core, tf32 operand truncation
+        const float rel = (float)dim * 1.1920929e-7f + (dtype == kF32 ? (1.0f / 512 + 1.0f / 1048576) : 0.f);
+        const float* mn2 = idx->max_norm2.p;
+        float* sc = idx->q_scale.p;
+        float* ep = idx->q_eps.p;
+        if (dtype == kBF16) {
             auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->qprep.p);
-            if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
-            else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
-        } else if (idx->cfg.dtype == kF16) {
+            if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
+            else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
+        } else if (dtype == kF16) {
             auto* dst = reinterpret_cast<__half*>(idx->qprep.p);
-            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
-            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, idx->q_scale.p, nq, nq_pad, dim);
+            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
+            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
         } else {
             tc::prepare_queries_kernel<float, 1><<<pgrid, 256, 0, c.stream>>>(
-                q32, reinterpret_cast<float*>(idx->qprep.p), idx->q_scale.p, nq, nq_pad, dim);
+                q32, reinterpret_cast<float*>(idx->qprep.p), sc, ep, mn2, rel, nq, nq_pad, dim);
         }
         FIP_CUDA(cudaGetLastError());
         c.launches++;
-        int rc = make_tmap(&tmap_q, idx->qprep.p, idx->cfg.dtype, dim, (uint64_t)split * nq_pad);
+        int rc = make_tmap(&tmap_q, idx->qprep.p, dtype, dim, (uint64_t)split * nq_pad);
         if (rc) return rc;
         if (!idx->tmap_x_valid) {
-            rc = make_tmap(&idx->tmap_x, idx->corpus, idx->cfg.dtype, dim, (uint64_t)n);
+            rc = make_tmap(&idx->tmap_x, idx->corpus, dtype, dim, (uint64_t)n);
             if (rc) return rc;
             idx->tmap_x_valid = true;
         }
@@ -435,12 +476,12 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     }
 
     ScanArgs a{};
-    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.dtype = idx->cfg.dtype; a.nq = nq;
+    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.dtype = dtype; a.nq = nq;
     a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
 
     auto scan_launch = [&]() -> int {
         if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, n_qtiles, split, pair);
-        switch (idx->cfg.dtype) {
+        switch (dtype) {
             case kF32: return launch_stream_phase<float>(c, a, q32);
             case kF16: return launch_stream_phase<__half>(c, a, q32);
             default: return launch_stream_phase<__nv_bfloat16>(c, a, q32);
@@ -461,7 +502,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         return FIP_OK;
     };
 
-    const int keff = std::max(k, 16);
+    const int keff = std::max(k_plan, 16);
     const double growth = std::max(2.0, ((double)cap / 2 - keff) / keff);
     int phases = 0;
     // phase 0: no threshold yet, every score of the first rows is written (slot = row)
@@ -470,87 +511,136 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (rc) return rc;
     int64_t pos = m;
     phases++;
-    rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale, m);
+    rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, m, keep_max);
     if (rc) return rc;
     while (pos < n) {
-        if (safe) m = std::max<int64_t>(256, (int64_t)(cap - k) / 256 * 256);
+        if (mode.safe) m = std::max<int64_t>(256, (int64_t)(cap - std::max(k_plan, keep_max)) / 256 * 256);
         else m = std::max<int64_t>(256, (int64_t)((double)pos * growth) / 256 * 256);
         m = std::min<int64_t>(m, n - pos);
         rc = scan(pos, pos + m, false);
         if (rc) return rc;
         pos += m;
         phases++;
-        rc = launch_select(c, idx, nq, k, cap, pos == n && !rescore, out_d, out_i, out_scale);
+        rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max);
         if (rc) return rc;
     }
     if (rescore) {
-        // lists now hold the k' best by 16-bit-query score: recompute them exactly, then select k.
-        const int64_t warps = (int64_t)nq * k;
+        // lists now hold the k' best by approximate score: recompute them exactly, then select k.
+        const int k_res = certify ? keep_max : k_plan;   // list slots that may hold a candidate
+        const int64_t warps = (int64_t)nq * k_res;
         const unsigned grid = (unsigned)std::min<int64_t>((warps + 7) / 8, (int64_t)idx->num_sms * 8);
-        if (idx->cfg.dtype == kBF16)
+        if (dtype == kBF16)
             rescore_kernel<__nv_bfloat16><<<grid, 256, 0, c.stream>>>(
-                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __nv_bfloat16*)idx->corpus, q32, dim);
-        else if (idx->cfg.dtype == kF32)
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k_res, (const __nv_bfloat16*)idx->corpus, q32, dim);
+        else if (dtype == kF32)
             rescore_kernel<float><<<grid, 256, 0, c.stream>>>(
-                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const float*)idx->corpus, q32, dim);
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k_res, (const float*)idx->corpus, q32, dim);
         else
             rescore_kernel<__half><<<grid, 256, 0, c.stream>>>(
-                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k, (const __half*)idx->corpus, q32, dim);
+                idx->cand.p, idx->cnt.p, (uint32_t)cap, nq, k_res, (const __half*)idx->corpus, q32, dim);
         FIP_CUDA(cudaGetLastError());
         c.launches++;
         rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr);
         if (rc) return rc;
     }
-    *variant_used = variant; *phases_used = phases; *cap_used = cap;
+    info->variant = variant; info->phases = phases; info->cap = cap; info->split = split;
+    info->certified_path = certify;
     return FIP_OK;
 }
 
-// Search + overflow check + safe-mode redo of overflowed queries.  Synchronises the stream.
+// Reads the flags of the search just enqueued (synchronises) and appends the flagged queries,
+// translated through `ids` (null = identity), to `over` / `uncert`.
+int collect_flags(fip_index* idx, cudaStream_t stream, int nq, const int* ids, std::vector<int>* over,
+                  std::vector<int>* uncert) {
+    const size_t nflags = 2 * ((size_t)nq + 1);
+    FIP_CUDA(idx->h_flags.ensure(nflags));
+    FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p, idx->overflow.p, sizeof(uint32_t) * nflags,
+                             cudaMemcpyDeviceToHost, stream));
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    const uint32_t* f = idx->h_flags.p;
+    const uint32_t* u = f + nq + 1;
+    if (!f[0] && !u[0]) return FIP_OK;
+    for (int q = 0; q < nq; ++q) {
+        const int id = ids ? ids[q] : q;
+        if (f[1 + q]) over->push_back(id);
+        else if (u[1 + q]) uncert->push_back(id);
+    }
+    return FIP_OK;
+}
+
+// Redo the queries `sel` (indices into q32 / out_*) under `mode`; flagged ones are appended to
+// over / uncert (as indices of the ORIGINAL batch).  Synchronises.
+int redo_subset(SearchCtx& c, const float* q32, const std::vector<int>& sel, int k, float* out_d,
+                int64_t* out_i, Mode mode, std::vector<int>* over, std::vector<int>* uncert, int* phases) {
+    fip_index* idx = c.idx;
+    const int ns = (int)sel.size();
+    if (ns == 0) return FIP_OK;
+    const int dim = idx->cfg.dim;
+    FIP_CUDA(idx->sel.ensure(sel.size()));
+    FIP_CUDA(idx->sub_q.ensure(sel.size() * (size_t)dim));
+    FIP_CUDA(idx->sub_d.ensure(sel.size() * (size_t)k));
+    FIP_CUDA(idx->sub_i.ensure(sel.size() * (size_t)k));
+    FIP_CUDA(cudaMemcpyAsync(idx->sel.p, sel.data(), sel.size() * sizeof(int), cudaMemcpyHostToDevice,
+                             c.stream));
+    int64_t tot = (int64_t)ns * dim;
+    gather_rows_f32_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c.stream>>>(q32, idx->sel.p,
+                                                                              idx->sub_q.p, ns, dim);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    SearchInfo info;
+    int rc = run_search(c, idx->sub_q.p, ns, k, idx->sub_d.p, idx->sub_i.p, mode, &info);
+    if (rc) return rc;
+    tot = (int64_t)ns * k;
+    scatter_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c.stream>>>(
+        idx->sub_d.p, idx->sub_i.p, idx->sel.p, out_d, out_i, ns, k);
+    FIP_CUDA(cudaGetLastError());
+    c.launches++;
+    *phases += info.phases;
+    return collect_flags(idx, c.stream, ns, sel.data(), over, uncert);  // also keeps `sel` alive
+}
+
+// Search + checks.  Level 0 runs the configured variant.  Queries whose candidate list overflowed
+// are redone in safe mode, queries whose result could not be CERTIFIED exact (tensor-core filter,
+// see select.cuh) are redone with a tighter filter; whatever is still flagged after that goes to
+// the exact streaming kernel in safe mode, which cannot fail.  Synchronises the stream.
 int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
                    cudaStream_t stream) {
     SearchCtx c{idx, stream};
-    int variant = 0, phases = 0, cap = 0;
     idx->ev_used = 0;
     idx->st_scan_launches = 0;
     if (idx->profile && idx->ev.empty()) {
         idx->ev.resize(128);
         for (auto& e : idx->ev) FIP_CUDA(cudaEventCreate(&e));
     }
-    int rc = run_search(c, q32, nq, k, out_d, out_i, idx->force_safe != 0, &variant, &phases, &cap);
+    Mode m0;
+    m0.safe = idx->force_safe != 0;
+    SearchInfo info;
+    int rc = run_search(c, q32, nq, k, out_d, out_i, m0, &info);
     if (rc) return rc;
-    int n_over = 0;
-    if (idx->n_rows > 0) {
-        FIP_CUDA(idx->h_flags.ensure((size_t)nq + 1));
-        FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p, idx->overflow.p, sizeof(uint32_t) * ((size_t)nq + 1),
-                                 cudaMemcpyDeviceToHost, stream));
-    }
-    FIP_CUDA(cudaStreamSynchronize(stream));
-    if (idx->n_rows > 0 && idx->h_flags.p[0]) {
-        std::vector<int> sel;
-        for (int q = 0; q < nq; ++q)
-            if (idx->h_flags.p[1 + q]) sel.push_back(q);
-        n_over = (int)sel.size();
-        FIP_CUDA(idx->sel.ensure(sel.size()));
-        FIP_CUDA(idx->sub_q.ensure(sel.size() * (size_t)idx->cfg.dim));
-        FIP_CUDA(idx->sub_d.ensure(sel.size() * (size_t)k));
-        FIP_CUDA(idx->sub_i.ensure(sel.size() * (size_t)k));
-        FIP_CUDA(cudaMemcpyAsync(idx->sel.p, sel.data(), sel.size() * sizeof(int),
-                                 cudaMemcpyHostToDevice, stream));
-        int64_t tot = (int64_t)n_over * idx->cfg.dim;
-        gather_rows_f32_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(
-            q32, idx->sel.p, idx->sub_q.p, n_over, idx->cfg.dim);
-        FIP_CUDA(cudaGetLastError());
-        c.launches++;
-        int v2, p2, c2;
-        rc = run_search(c, idx->sub_q.p, n_over, k, idx->sub_d.p, idx->sub_i.p, true, &v2, &p2, &c2);
+    std::vector<int> over, uncert, over2, uncert2;
+    rc = collect_flags(idx, stream, nq, nullptr, &over, &uncert);
+    if (rc) return rc;
+    int phases = info.phases;
+    const size_t n_over = over.size(), n_uncert = uncert.size();
+    if (!over.empty()) {
+        Mode m; m.safe = true; m.rigor = m0.rigor;
+        rc = redo_subset(c, q32, over, k, out_d, out_i, m, &over2, &uncert2, &phases);
         if (rc) return rc;
-        tot = (int64_t)n_over * k;
-        scatter_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(
-            idx->sub_d.p, idx->sub_i.p, idx->sel.p, out_d, out_i, n_over, k);
-        FIP_CUDA(cudaGetLastError());
-        c.launches++;
-        FIP_CUDA(cudaStreamSynchronize(stream));  // sel (host vector) must outlive the H2D copy
-        phases += p2;
+    }
+    if (!uncert.empty()) {
+        Mode m; m.safe = m0.safe; m.rigor = 1;
+        rc = redo_subset(c, q32, uncert, k, out_d, out_i, m, &over2, &uncert2, &phases);
+        if (rc) return rc;
+    }
+    over2.insert(over2.end(), uncert2.begin(), uncert2.end());
+    if (!over2.empty()) {
+        std::sort(over2.begin(), over2.end());
+        Mode m; m.safe = true; m.rigor = 2;
+        std::vector<int> o3, u3;
+        rc = redo_subset(c, q32, over2, k, out_d, out_i, m, &o3, &u3, &phases);
+        if (rc) return rc;
+        if (!o3.empty() || !u3.empty())
+            return fail(FIP_ERR_STATE, "internal error: the exact fallback path raised a flag");
     }
     idx->st_scan_ms = 0.0;
     idx->st_scan_each.clear();
@@ -565,8 +655,9 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
             idx->st_gap_each.push_back(ms);
         }
     }
-    idx->st_launches = c.launches; idx->st_variant = variant; idx->st_phases = phases;
-    idx->st_overflow = n_over; idx->st_cap = cap;
+    idx->st_launches = c.launches; idx->st_variant = info.variant; idx->st_phases = phases;
+    idx->st_overflow = (int64_t)n_over; idx->st_uncert = (int64_t)n_uncert;
+    idx->st_stream_redo = (int64_t)over2.size(); idx->st_cap = info.cap; idx->st_split = info.split;
     idx->st_total_launches += c.launches; idx->st_total_searches++;
     return FIP_OK;
 }
@@ -612,6 +703,9 @@ int fip_create(const fip_config* cfg, fip_index** out) {
     idx->num_sms = prop.multiProcessorCount;
     cudaError_t e = cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete idx; FIP_CUDA(e); }
+    e = idx->max_norm2.ensure(1);
+    if (e == cudaSuccess) e = cudaMemset(idx->max_norm2.p, 0, sizeof(float));
+    if (e != cudaSuccess) { fip_destroy(idx); FIP_CUDA(e); }
     if (cfg->capacity_rows > 0) {
         int rc = reserve_rows(idx, cfg->capacity_rows);
         if (rc) { fip_destroy(idx); return rc; }
@@ -625,7 +719,7 @@ void fip_destroy(fip_index* idx) {
     cudaSetDevice(idx->cfg.device);
     if (idx->stream) cudaStreamSynchronize(idx->stream);
     if (idx->corpus) cudaFree(idx->corpus);
-    idx->thr.release(); idx->q_scale.release(); idx->q32.release(); idx->out_d.release();
+    idx->thr.release(); idx->q_scale.release(); idx->q_eps.release(); idx->max_norm2.release(); idx->q32.release(); idx->out_d.release();
     idx->cnt.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
@@ -633,6 +727,19 @@ void fip_destroy(fip_index* idx) {
     for (auto& e : idx->ev) cudaEventDestroy(e);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
+}
+
+// Folds the squared norms of stored rows [row0, row0 + n) into idx->max_norm2 (enqueue only).
+static int update_row_norms(fip_index* idx, int64_t row0, int64_t n) {
+    const char* src = (const char*)idx->corpus + (size_t)row0 * idx->row_bytes();
+    const unsigned grid = (unsigned)std::min<int64_t>((n + 7) / 8, (int64_t)idx->num_sms * 16);
+    switch (idx->cfg.dtype) {
+        case kF32: row_norm_max_kernel<float><<<grid, 256, 0, idx->stream>>>((const float*)src, n, idx->cfg.dim, idx->max_norm2.p); break;
+        case kF16: row_norm_max_kernel<__half><<<grid, 256, 0, idx->stream>>>((const __half*)src, n, idx->cfg.dim, idx->max_norm2.p); break;
+        default: row_norm_max_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((const __nv_bfloat16*)src, n, idx->cfg.dim, idx->max_norm2.p); break;
+    }
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
 }
 
 static int convert_append(fip_index* idx, const float* src_dev, int64_t n) {
@@ -671,6 +778,8 @@ int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n) {
                                  cudaMemcpyHostToDevice, idx->stream));
         rc = convert_append(idx, idx->add_stage.p, m);
         if (rc) return rc;
+        rc = update_row_norms(idx, idx->n_rows, m);
+        if (rc) return rc;
         FIP_CUDA(cudaStreamSynchronize(idx->stream));
         idx->n_rows += m;
     }
@@ -696,6 +805,8 @@ int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtyp
     } else {
         return fail(FIP_ERR_INVALID, "fip_add_device: rows must be fp32 or the index's storage dtype");
     }
+    rc = update_row_norms(idx, idx->n_rows, n);
+    if (rc) return rc;
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows += n;
     idx->tmap_x_valid = false;
@@ -719,6 +830,8 @@ int fip_add_synthetic(fip_index* idx, int64_t n, uint64_t seed, int64_t global_r
         default: synthetic_fill_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((__nv_bfloat16*)dst, n, idx->cfg.dim, global_row0, seed, 0u); break;
     }
     FIP_CUDA(cudaGetLastError());
+    rc = update_row_norms(idx, idx->n_rows, n);
+    if (rc) return rc;
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows += n;
     idx->tmap_x_valid = false;
@@ -728,6 +841,10 @@ int fip_add_synthetic(fip_index* idx, int64_t n, uint64_t seed, int64_t global_r
 int fip_reset(fip_index* idx) {
     if (!idx) return fail(FIP_ERR_INVALID, "null index");
     std::lock_guard<std::mutex> lock(idx->mu);
+    int rc = use_device(idx);
+    if (rc) return rc;
+    FIP_CUDA(cudaMemsetAsync(idx->max_norm2.p, 0, sizeof(float), idx->stream));
+    FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows = 0;
     idx->tmap_x_valid = false;
     return FIP_OK;
@@ -833,6 +950,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
     } else if (k == "cta_pair") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "cta_pair must be 0 (auto), 1 or 2");
         idx->cta_pair = (int)value;
+    } else if (k == "certify") {
+        idx->certify = value != 0;
     } else if (k == "profile_events") {
         idx->profile = value != 0;
     } else if (k == "force_safe_mode") {
@@ -850,6 +969,9 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "variant") return idx->st_variant;
     if (k == "phases") return idx->st_phases;
     if (k == "overflow_queries") return idx->st_overflow;
+    if (k == "uncertified_queries") return idx->st_uncert;
+    if (k == "stream_redo_queries") return idx->st_stream_redo;
+    if (k == "query_split_used") return idx->st_split;
     if (k == "candidate_capacity") return idx->st_cap;
     if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);

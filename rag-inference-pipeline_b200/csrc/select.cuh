@@ -43,6 +43,20 @@ struct SelectArgs {
     int64_t id_base;      // global id of local row 0
     const float* out_scale;  // [nq] or null: multiply reported scores (undoes the query scaling)
     uint32_t* overflow;   // [1 + nq]: [0] = any overflow, [1+q] = query q overflowed
+    // Exactness window (tensor-core variant only; null = exact scores, keep exactly k).
+    // The scan's scores are APPROXIMATE: |approx - exact| <= eps[q] for every stored row (see
+    // prepare_queries_kernel).  Let A be the k-th best approximate score so far.  The k-th best
+    // exact score T is >= A - eps, so a row can only belong to the exact top-k if its approximate
+    // score exceeds A - 2 eps.  Intermediate passes therefore keep EVERY candidate above
+    // A - 2 eps (not a fixed count) and publish that as the filter threshold; after exact
+    // rescoring the final pass picks the k best of them.  The result is exact by construction.
+    // Only when more than keep_max candidates crowd that window (a cluster of near-ties tighter
+    // than the filter's resolution) is the list truncated and the query flagged "uncertified";
+    // the host redoes it with a tighter variant.
+    const float* win_eps;     // [nq] eps in unscaled score units
+    const float* win_scale;   // [nq] approx-score scale (out_scale of the scan)
+    int keep_max;             // truncation limit for the window (<= cap)
+    uint32_t* uncert;         // [1 + nq] like `overflow`
 };
 
 constexpr int kSelectThreads = 256;
@@ -145,21 +159,57 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
     uint64_t kth = 0ull;  // every key >= kth is kept (all of them when c <= k)
     if ((int)c > a.k) kth = kth_largest_key(s_keys, (int)c, a.k, s_hist, s_red);
     if (!a.final_pass) {
-        if ((int)c > a.k) {
+        // threshold and the limit key: candidates with key > lim stay in the list
+        float t = kNegInf;
+        uint64_t lim = 0ull;      // key 0 is below every real key: keep everything
+        uint32_t kept = c;
+        if ((int)c >= a.k) {
+            if ((int)c == a.k) {  // exactly k: the k-th best is the smallest key
+                uint64_t mn = ~0ull;
+                for (int i = tid; i < (int)c; i += kSelectThreads) mn = min(mn, s_keys[i]);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, off));
+                if ((tid & 31) == 0) s_red[tid >> 5] = mn;
+                __syncthreads();
+                mn = s_red[0];
+                for (int w = 1; w < kSelectThreads / 32; ++w) mn = min(mn, s_red[w]);
+                __syncthreads();
+                kth = mn;
+            }
+            t = key_score(kth);
+            lim = kth - 1ull;
+            kept = (uint32_t)a.k;
+            if (a.win_eps) {
+                const float win = 2.0f * a.win_eps[q] / a.win_scale[q];
+                if (win > 0.f && t > kNegInf) {
+                    t = nextafterf(t - win, kNegInf);
+                    lim = ((uint64_t)orderable_f32(t) << 32) | 0xFFFFFFFFull;  // keep score > t
+                    kept = 0xFFFFFFFFu;                                         // counted below
+                }
+            }
+        }
+        if ((int)c > a.k || kept == 0xFFFFFFFFu) {
             for (int i = tid; i < (int)c; i += kSelectThreads) {
                 const uint64_t x = s_keys[i];
-                if (x >= kth) list[atomicAdd(&s_count, 1u)] = key_to_raw(x);
+                if (x > lim) list[atomicAdd(&s_count, 1u)] = key_to_raw(x);
+            }
+            __syncthreads();
+            kept = s_count;
+            if ((int)kept > a.keep_max && a.win_eps) {
+                // the window is crowded: truncate to the keep_max best and flag the query
+                __syncthreads();
+                if (tid == 0) { s_count = 0u; a.uncert[0] = 1u; a.uncert[1 + q] = 1u; }
+                const uint64_t kth2 = kth_largest_key(s_keys, (int)c, a.keep_max, s_hist, s_red);
+                for (int i = tid; i < (int)c; i += kSelectThreads) {
+                    const uint64_t x = s_keys[i];
+                    if (x >= kth2) list[atomicAdd(&s_count, 1u)] = key_to_raw(x);
+                }
+                t = key_score(kth2);
+                kept = (uint32_t)a.keep_max;
             }
         }
         if (tid == 0) {
-            a.cnt[q] = (uint32_t)keep;
-            float t = kNegInf;
-            if ((int)c > a.k) t = key_score(kth);
-            else if ((int)c == a.k) {  // exactly k: threshold = the smallest key's score
-                uint64_t mn = ~0ull;
-                for (int i = 0; i < (int)c; ++i) mn = min(mn, s_keys[i]);
-                t = key_score(mn);
-            }
+            a.cnt[q] = kept;
             a.thr[q] = t;
         }
         return;

@@ -67,6 +67,30 @@ template <> __device__ __forceinline__ float from_storage<__nv_bfloat16>(__nv_bf
     return __bfloat162float(v);
 }
 
+// max over rows of ||x_r||^2 (fp32, from the stored values): the exactness certificate of the
+// tensor-core variant bounds |<dq, x_r>| by ||dq|| * max ||x_r||.  One warp per row; squared norms
+// are non-negative, so their bit patterns order like unsigned integers (atomicMax on the bits).
+template <typename T>
+__global__ void row_norm_max_kernel(const T* __restrict__ rows, int64_t n, int dim,
+                                    float* __restrict__ max_norm2) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    float best = 0.f;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const T* x = rows + r * (int64_t)dim;
+        float acc = 0.f;
+        for (int c = lane; c < dim; c += 32) {
+            const float v = from_storage<T>(x[c]);
+            acc = fmaf(v, v, acc);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);
+        best = fmaxf(best, acc);
+    }
+    if (lane == 0 && best > 0.f) atomicMax(reinterpret_cast<unsigned int*>(max_norm2), __float_as_uint(best));
+}
+
 template <typename T>
 __global__ void widen_rows_kernel(const T* __restrict__ in, float* __restrict__ out, int64_t n) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;

@@ -307,9 +307,17 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
 // into [0.5, 1) so the fp16 range is never an issue (exact to undo: out_scale[q] = 2^e); bf16 and
 // fp32 (tf32 operand: the tensor core ignores the low 13 mantissa bits) keep scale 1.
 // Rows >= nq are zero.  One warp per query row.
+//
+// Also emits the query's certificate radius eps[q]: a rigorous bound on |approx - exact| score for
+// ANY stored row, in unscaled score units:
+//     eps = ( ||q - sum(terms)|| + rel * ||q|| ) * max_r ||x_r||
+// where `rel` covers what software cannot see: fp32 accumulation inside the tensor core
+// (dim * 2^-23) and, for tf32, the truncation of BOTH operands to 10 mantissa bits (2^-9 + 2^-20).
 template <typename T, int kSplit>
 __global__ void prepare_queries_kernel(const float* __restrict__ q32, T* __restrict__ qt,
-                                       float* __restrict__ out_scale, int nq, int nq_pad, int dim) {
+                                       float* __restrict__ out_scale, float* __restrict__ out_eps,
+                                       const float* __restrict__ max_norm2, float rel, int nq,
+                                       int nq_pad, int dim) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= nq_pad) return;
@@ -332,16 +340,28 @@ __global__ void prepare_queries_kernel(const float* __restrict__ q32, T* __restr
         up = ldexpf(1.0f, -e);
         down = ldexpf(1.0f, e);
     }
+    float res2 = 0.f, q2 = 0.f;
     for (int c = lane; c < dim; c += 32) {
         float rem = src[c] * up;
+        q2 = fmaf(rem, rem, q2);
 #pragma unroll
         for (int t = 0; t < kSplit; ++t) {
             T h = to_storage<T>(rem);
             qt[((size_t)t * nq_pad + row) * dim + c] = h;
             rem -= from_storage<T>(h);
         }
+        res2 = fmaf(rem, rem, res2);
     }
-    if (lane == 0) out_scale[row] = down;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        res2 += __shfl_xor_sync(0xFFFFFFFFu, res2, off);
+        q2 += __shfl_xor_sync(0xFFFFFFFFu, q2, off);
+    }
+    if (lane == 0) {
+        out_scale[row] = down;
+        // 1.01: slack for the fp32 rounding of the norms themselves
+        out_eps[row] = 1.01f * (sqrtf(res2) + rel * sqrtf(q2)) * down * sqrtf(*max_norm2);
+    }
 }
 
 }  // namespace tc

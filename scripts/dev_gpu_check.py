@@ -83,7 +83,7 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
     tfs = 2.0 * nq * n * dim / ms / 1e9
     print(f"TIME {variant} {dtype} n={n} d={dim} nq={nq} k={k}: {ms:.3f} ms/search  {nq/ms*1e3:.0f} QPS  "
           f"{gbs:.0f} GB/s  {tfs:.1f} TFLOP/s  launches={idx.stat('launches')} phases={idx.stat('phases')} "
-          f"overflow={idx.stat('overflow_queries')} cta_group={idx.stat('cta_group')} "
+          f"overflow={idx.stat('overflow_queries')} uncert={idx.stat('uncertified_queries')} split={idx.stat('query_split_used')} cta_group={idx.stat('cta_group')} "
           f"scan_ms={idx.stat('scan_time_ns')/1e6:.3f}")
     sc = [idx.stat(f"scan_ns_{i}") / 1e6 for i in range(16) if idx.stat(f"scan_ns_{i}") >= 0]
     gp = [idx.stat(f"gap_ns_{i}") / 1e6 for i in range(16) if idx.stat(f"gap_ns_{i}") >= 0]

@@ -226,6 +226,67 @@ def test_adversarial_order_overflow_fallback(variant, dtype):
     idx.close()
 
 
+@pytest.mark.parametrize("dtype", ["f16", "bf16", "f32"])
+def test_exactness_certificate_redoes_near_tie_clusters(dtype):
+    """300 planted rows score within ~1e-4 of each other for query 0 -- closer than the error bound
+    of the rounded tensor-core filter -- so that query cannot be certified and must be redone with
+    a tighter variant; the other queries stay on the fast path.  Results are exact either way."""
+    dim, n, k = 128, 30000, 10
+    rng = np.random.default_rng(11)
+    corpus = synthetic.synthetic_corpus(0, n, dim, "f32").copy()
+    queries = synthetic.synthetic_queries(40, dim)
+    where = rng.choice(n, size=300, replace=False)
+    corpus[where] = 9.0 * queries[0][None, :] + 2e-5 * rng.standard_normal((300, dim)).astype(np.float32)
+    corpus = synthetic.round_to_storage(corpus, dtype)
+    idx = _index(dim, dtype)
+    idx.add(corpus)
+    idx.set_variant("tensor")
+    D, I = idx.search(queries, k)
+    assert idx.stat("uncertified_queries") >= 1
+    assert idx.stat("uncertified_queries") < 40          # ordinary queries certify on the fast path
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k + 1)
+    _check(D, I, Dr[:, :k], Ir[:, :k], dtype, Dr[:, k])
+    assert set(I[0].tolist()) <= set(where.tolist())
+    # exact scores: the k best of the planted rows, recomputed in fp64
+    ref0 = np.sort(corpus[where].astype(np.float64) @ queries[0].astype(np.float64))[::-1][:k]
+    np.testing.assert_allclose(D[0], ref0, rtol=2e-6 if dtype == "f32" else 1e-5)
+    # with the certificate off the flags are never raised
+    idx.set_option("certify", 0)
+    idx.search(queries, k)
+    assert idx.stat("uncertified_queries") == 0
+    idx.close()
+
+
+@pytest.mark.parametrize("dtype", ["f32", "f16"])
+def test_certificate_falls_back_on_norm_outlier(dtype):
+    """One row with a huge norm inflates the (Cauchy-Schwarz) error bound so much that the exactness
+    window of the tensor-core filter swallows the whole list: every query is flagged and redone
+    (fp32 storage: straight on the exact streaming kernel).  Results stay exact."""
+    dim, n, k = 64, 9000, 5
+    corpus = synthetic.synthetic_corpus(0, n, dim, dtype).copy()
+    corpus[1234] *= 4000.0
+    corpus = synthetic.round_to_storage(corpus, dtype)
+    queries = synthetic.synthetic_queries(6, dim)
+    idx = _index(dim, dtype)
+    idx.add(corpus)
+    idx.set_variant("tensor")
+    D, I = idx.search(queries, k)
+    assert idx.stat("uncertified_queries") == 6
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k)
+    _check(D, I, Dr, Ir, dtype)
+    idx.close()
+
+
+def test_default_query_terms():
+    for dtype in ("f16", "bf16", "f32"):
+        idx = _index(128, dtype)
+        idx.add_synthetic(20000, 3, 0)
+        idx.search(synthetic.synthetic_queries(64, 128), 10)
+        assert idx.last_variant() == "tensor" and idx.stat("query_split_used") == 1
+        assert idx.stat("uncertified_queries") == 0
+        idx.close()
+
+
 def test_forced_safe_mode_matches():
     dim, n, k = 128, 50000, 20
     corpus = c_oracle.synthetic_corpus(0, n, dim, "f16")
