@@ -24,6 +24,10 @@ import sys
 import threading
 import time
 
+# Must be set before ANY OpenMP runtime starts (torch loads one): spinning libgomp workers starve
+# the BLAS threads of the CPU baseline (same policy as the reference, src/pipeline/runtime.py:51).
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -202,6 +206,11 @@ def run_b200(args, rank, local_rank, world):
     from rag_inference_pipeline_b200.synthetic import CORPUS_SEED, synthetic_queries
 
     total_rows, dim, dtype, batch, k = workload(args)
+    # stdout carries exactly ONE JSON line: anything libraries print while we set up and run (NCCL
+    # prints its version on stdout) is diverted to stderr until the line is ready.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -236,13 +245,21 @@ def run_b200(args, rank, local_rank, world):
     launches = 0
     scan_ns = 0
     scan_launches = 0
+    per_scan = {}   # scan launch index -> [rows, total ns, count]
     barrier()
     e0.record()
     for _ in range(args.steps):
         D, I = searcher.search_tensor(q_dev, k)
-        launches += searcher.index.stat("launches") + (1 if world > 1 else 0)
+        launches += searcher.index.stat("launches") + (2 if world > 1 else 0)
         scan_ns += searcher.index.stat("scan_time_ns")
         scan_launches += searcher.index.stat("scan_launches")
+        for i in range(64):
+            ns = searcher.index.stat(f"scan_ns_{i}")
+            if ns < 0:
+                break
+            rec = per_scan.setdefault(i, [searcher.index.stat(f"scan_rows_{i}"), 0, 0])
+            rec[1] += ns
+            rec[2] += 1
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -300,21 +317,36 @@ def run_b200(args, rank, local_rank, world):
         esize = 4 if dtype == "f32" else 2
         scan_s = scan_ns_max * 1e-9
         scans = max(1, scan_launches)
-        if variant == "tensor" and batch > 210:
-            flops_per_search = 2.0 * batch * n_local * dim   # algorithmic: no padding / split credit
-            achieved = flops_per_search * args.steps / scan_s / 1e12 if scan_s > 0 else None
+        # dominant kernel = the scan launch that takes the longest (the last, geometrically
+        # largest phase); its algorithmic work is that phase's rows only.
+        dom = max(per_scan, key=lambda i: per_scan[i][1]) if per_scan else None
+        dom_rows = per_scan[dom][0] if dom is not None else n_local
+        dom_s = per_scan[dom][1] * 1e-9 / per_scan[dom][2] if dom is not None else scan_s / scans
+        tensor_bound = variant == "tensor" and batch * (4 / esize) > 420   # 2*B/esize > P/BW ~ 210
+        if tensor_bound:
+            flops = 2.0 * batch * dom_rows * dim            # algorithmic: no padding / split credit
+            achieved = flops / dom_s / 1e12 if dom_s > 0 else None
             roof = {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops_sustained"],
                     "unit": "TFLOP/s",
                     "peak_source": f"{peaks['source']} (sustained cuBLAS bf16, kernel timed inside a long step)"}
         else:
-            bytes_per_search = float(n_local) * dim * esize + batch * dim * 4 + batch * k * 12
-            achieved = bytes_per_search * args.steps / scan_s / 1e9 if scan_s > 0 else None
+            nbytes = float(dom_rows) * dim * esize + batch * dim * 4
+            achieved = nbytes / dom_s / 1e9 if dom_s > 0 else None
             roof = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                     "peak_source": f"{peaks['source']} (copy bandwidth)"}
         roof["frac"] = (roof["achieved"] / roof["peak"]) if roof["achieved"] else None
         roof["kernel"] = "tc_scan_kernel" if variant == "tensor" else "stream_scan_kernel"
+        roof["launch"] = {"phase": dom, "rows": dom_rows, "avg_ms": dom_s * 1e3,
+                          "phases_per_search": len(per_scan)}
         roof["launches_timed"] = scan_launches
-        roof["avg_launch_ms"] = scan_s * 1e3 / scans
+        roof["all_scan_launches_ms_per_step"] = scan_s * 1e3 / args.steps
+        roof["whole_search_frac"] = None
+        if tensor_bound and ms_per_step > 0:
+            roof["whole_search_frac"] = (2.0 * batch * n_local * dim / (ms_per_step * 1e-3) / 1e12
+                                         / peaks["tflops_sustained"])
+        elif ms_per_step > 0:
+            roof["whole_search_frac"] = ((float(n_local) * dim * esize) / (ms_per_step * 1e-3) / 1e9
+                                         / peaks["hbm_gbs"])
         roof["kernel_share_of_step"] = scan_s * 1e3 / ms_max if ms_max > 0 else None
         traffic_path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         roof["traffic"] = None
@@ -336,9 +368,14 @@ def run_b200(args, rank, local_rank, world):
             "roofline": roof,
             "cpu_baseline": cpu_baseline,
             "variant": variant, "phases_per_search": phases, "overflow_queries": overflow,
+            "uncertified_queries": searcher.index.stat("uncertified_queries"),
+            "cta_group": searcher.index.stat("cta_group"),
             "corpus_load_s": load_s, "verify": verify,
         }
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
     searcher.close()
     if world > 1:
         dist.barrier()

@@ -108,7 +108,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value);
  * "uncertified_queries" (queries the tensor-core filter could not certify exact and that were redone
  * with a tighter variant), "stream_redo_queries" (of those and the overflowed ones, how many ended
  * on the exact streaming kernel), "query_split_used",
- * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_time_ns" / "scan_launches" (device time and count of the scan
+ * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_ns_<i>" / "scan_rows_<i>" / "gap_ns_<i>" (per scan launch i: device time, corpus rows, time to the
+ * next scan), "scan_time_ns" / "scan_launches" (device time and count of the scan
  * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);
 

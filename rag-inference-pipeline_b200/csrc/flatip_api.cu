@@ -176,6 +176,7 @@ struct fip_index {
     double st_scan_ms = 0.0;      // device time of the scan kernels of the last search
     int64_t st_scan_launches = 0;
     std::vector<float> st_scan_each, st_gap_each;  // per scan launch; gap = time to the next scan
+    std::vector<int64_t> st_scan_rows, st_scan_rows_pending;  // corpus rows of each timed scan
 
     // per-search workspace
     DevBuf<float> thr, q_scale, q_eps, q32, out_d;
@@ -498,6 +499,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
             FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_used + 1], c.stream));
             idx->ev_used += 2;
             idx->st_scan_launches += c.launches - before;
+            idx->st_scan_rows_pending.push_back(r1 - r0);
         }
         return FIP_OK;
     };
@@ -608,6 +610,7 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
     SearchCtx c{idx, stream};
     idx->ev_used = 0;
     idx->st_scan_launches = 0;
+    idx->st_scan_rows_pending.clear();
     if (idx->profile && idx->ev.empty()) {
         idx->ev.resize(128);
         for (auto& e : idx->ev) FIP_CUDA(cudaEventCreate(&e));
@@ -645,6 +648,7 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
     idx->st_scan_ms = 0.0;
     idx->st_scan_each.clear();
     idx->st_gap_each.clear();
+    idx->st_scan_rows = idx->st_scan_rows_pending;
     for (int i = 0; i + 1 < idx->ev_used; i += 2) {
         float ms = 0.f;
         FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i], idx->ev[i + 1]));
@@ -976,6 +980,10 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
     if (k == "scan_launches") return idx->st_scan_launches;
+    if (k.rfind("scan_rows_", 0) == 0) {
+        const size_t i = (size_t)atoi(k.c_str() + 10);
+        return i < idx->st_scan_rows.size() ? idx->st_scan_rows[i] : -1;
+    }
     if (k.rfind("scan_ns_", 0) == 0 || k.rfind("gap_ns_", 0) == 0) {
         const bool gap = k[0] == 'g';
         const auto& v = gap ? idx->st_gap_each : idx->st_scan_each;
