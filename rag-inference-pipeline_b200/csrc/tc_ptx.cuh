@@ -39,12 +39,19 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                  : "memory");
 }
+// The two "accumulator drained" arrivals below are RELAXED on purpose.  What they order is the
+// epilogue's TMEM reads before the next MMA into the same accumulator, and that is already done:
+// tcgen05.wait::ld has completed (the values are in registers) and tcgen05.fence::before_thread_sync
+// precedes the arrive.  A release arrive would additionally drain the thread's outstanding GLOBAL
+// stores (the survivors just appended to the candidate lists) -- MEMBAR.ALL.GPU + ERRBAR in SASS,
+// 22 % of all stall samples in the k = 1024 profile -- although nobody reads those lists before
+// the kernel ends.
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+    asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 // arrive on a barrier given by a shared::cluster address (own or peer CTA)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar)
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar)
                  : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
@@ -232,27 +239,29 @@ __device__ __forceinline__ void st_global_v2_pred(uint64_t* ptr, uint32_t lo, ui
         "r"(lo), "r"(hi), "r"((uint32_t)p)
         : "memory");
 }
-// One step of the epilogue's branch-free compaction into the thread's shared-memory strip:
-// if (v > thr) { *saddr = v; saddr += stride; mask |= bit; }  -- four 32-bit SASS instructions per
-// score, the only loop-carried dependencies are the predicated updates of `saddr` and `mask`.
-__device__ __forceinline__ void strip_append(uint32_t& saddr, uint32_t& mask, float v, float thr,
-                                             uint32_t bit, uint32_t stride) {
+// Epilogue pass 1, one score: if (v > thr) mask |= bit;   (two SASS instructions, no branch)
+__device__ __forceinline__ void mask_or_if_gt(uint32_t& mask, float v, float thr, uint32_t bit) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "setp.gt.f32 p, %2, %3;\n\t"
-        "@p st.shared.f32 [%0], %2;\n\t"
-        "@p add.u32 %0, %0, %5;\n\t"
-        "@p or.b32 %1, %1, %4;\n\t"
+        "setp.gt.f32 p, %1, %2;\n\t"
+        "@p or.b32 %0, %0, %3;\n\t"
         "}"
-        : "+r"(saddr), "+r"(mask)
-        : "f"(v), "f"(thr), "r"(bit), "r"(stride)
-        : "memory");
+        : "+r"(mask)
+        : "f"(v), "f"(thr), "r"(bit));
 }
-__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
-    return v;
+// Epilogue pass 2, one score: if (take) { *list = {lo, hi}; ++list; }   (predicated, no branch)
+__device__ __forceinline__ void list_append_if(uint64_t*& list, uint32_t lo, uint32_t hi, uint32_t take) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t"
+        "@p st.global.v2.u32 [%0], {%1, %2};\n\t"
+        "@p add.u64 %0, %0, 8;\n\t"
+        "}"
+        : "+l"(list)
+        : "r"(lo), "r"(hi), "r"(take)
+        : "memory");
 }
 
 }  // namespace tc

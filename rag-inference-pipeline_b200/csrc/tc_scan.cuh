@@ -56,66 +56,82 @@ template <int kFmt, int kSplit, int kCtas> struct Cfg {
     static constexpr int MMAS_PER_STAGE = 4;               // 32 bytes of K per instruction
     static constexpr int B_LOCAL_BYTES = B_BYTES / kCtas;  // this CTA's share of the corpus tile
     static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_LOCAL_BYTES;
-    static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
-    // operand ring + the epilogue's compaction strip + barriers
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 32 * 1024 + 1024 /*align slack*/ + 256;
+    static constexpr int STAGES = (225 * 1024) / STAGE_BYTES > 8 ? 8 : (225 * 1024) / STAGE_BYTES;
+    // operand ring + barriers (the epilogue works out of TMEM and registers)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256;
 };
 
-// Epilogue of one thread (= one query) over EPI_CHUNKS chunks of 32 accumulator columns starting
-// at chunk c0: filter against `thr` in ONE pass over TMEM.
-//   * Every group of 8 scores is guarded by its max, so "nothing passes" (the common case: ~1e-4 of
-//     the scores survive in the main phase) costs ~0.75 instructions per score.
-//   * A group with a survivor is compacted branch-free into the thread's strip in shared memory
-//     (values only; which columns passed is kept as a 32-bit mask in a register).
-//   * After a chunk with survivors ONE atomic reserves the list slots and the strip is written out
-//     as raw keys.
-constexpr int STRIP_SLOTS = 32;                              // one chunk's worth per thread
+// Epilogue of one thread (= one query) over its EPI_CHUNKS chunks of 32 accumulator columns starting
+// at chunk c0: filter against `thr`, two passes over TMEM, no shared memory.
+//   pass 1  every chunk is read once; each group of 8 scores is guarded by its max, so "nothing
+//           passes" (the common case: ~1e-4 of the scores survive in the main phase) costs ~0.75
+//           instructions per score.  A group with a survivor records which columns passed in the
+//           chunk's 32-bit mask (registers only).
+//   reserve ONE atomicAdd per thread and tile reserves the list slots of all its survivors (the
+//           round trip to L2 is paid once per tile, not once per chunk, and overlaps pass 2's TMEM
+//           reads).
+//   pass 2  chunks in which some lane of the warp had a survivor are read from TMEM again (the
+//           accumulator is still live) and the survivors are stored straight from registers as raw
+//           keys with predicated stores.
 constexpr int EPI_THREADS = EPI_WARPS * 32;
-constexpr uint32_t STRIP_STRIDE = EPI_THREADS * 4;           // bytes between a thread's slots
-constexpr int STRIP_BYTES = STRIP_SLOTS * EPI_THREADS * 4;   // 32 KB
 constexpr int EPI_CHUNKS = BN / 32 / (EPI_WARPS / 4);        // chunks per epilogue warp and tile
 
-__device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t sbase, uint32_t taddr, int q,
-                                                float thr, uint32_t tile_row0, int c0) {
-#pragma unroll 1
-    for (int c = c0; c < c0 + EPI_CHUNKS; ++c) {
+__device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t taddr, int q, float thr,
+                                                uint32_t tile_row0, int c0) {
+    uint32_t masks[EPI_CHUNKS];
+    uint32_t n = 0;
+#pragma unroll
+    for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
+        const int c = c0 + ci;
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
-        if (row_base >= a.row_end) break;  // warp-uniform
-        float v[32];
-        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-        if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
+        uint32_t mask = 0u;
+        if (row_base < a.row_end) {  // warp-uniform
+            float v[32];
+            tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+            if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (row_base + j >= a.row_end) v[j] = kNegInf;
-        }
-        uint32_t saddr = sbase, mask = 0u;
+                for (int j = 0; j < 32; ++j)
+                    if (row_base + j >= a.row_end) v[j] = kNegInf;
+            }
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
-            mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
-            if (mx > thr) {
+            for (int g = 0; g < 4; ++g) {
+                float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
+                mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+                if (mx > thr) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    strip_append(saddr, mask, v[8 * g + j], thr, 1u << (8 * g + j), STRIP_STRIDE);
+                    for (int j = 0; j < 8; ++j) mask_or_if_gt(mask, v[8 * g + j], thr, 1u << (8 * g + j));
+                }
             }
         }
-        if (mask) {
-            // mask != 0 implies an active query (inactive lanes carry thr = +inf).  A reservation
-            // that does not fit writes nothing: cnt > cap makes the select kernel flag the query as
-            // overflowed and the host redoes it in safe mode.
-            const uint32_t n = (uint32_t)__popc(mask);
-            uint32_t slot = atomicAdd(a.cnt + q, n);
-            if (slot + n <= a.cap) {
-                uint64_t* list = a.cand + (size_t)q * a.cap;
-                const uint32_t inv_row0 = 0xFFFFFFFFu - row_base;
-                uint32_t rd = sbase;
-                while (mask) {
-                    const uint32_t j = (uint32_t)__ffs((int)mask) - 1u;
-                    mask &= mask - 1u;
-                    const uint32_t bits = ld_shared_u32(rd);
-                    rd += STRIP_STRIDE;
-                    list[slot++] = ((uint64_t)bits << 32) | (uint64_t)(inv_row0 - j);
-                }
+        masks[ci] = mask;
+        n += (uint32_t)__popc(mask);
+    }
+    // n != 0 implies an active query (inactive lanes carry thr = +inf).  A reservation that does
+    // not fit writes nothing: cnt > cap makes the select kernel flag the query as overflowed and
+    // the host redoes it in safe mode.
+    uint32_t slot = 0u;
+    bool fits = false;
+    if (n) {
+        slot = atomicAdd(a.cnt + q, n);
+        fits = slot + n <= a.cap;
+    }
+    if (!__any_sync(0xFFFFFFFFu, n != 0u)) return;
+    uint64_t* list = a.cand + (size_t)q * a.cap + slot;
+#pragma unroll
+    for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
+        const uint32_t mask = fits ? masks[ci] : 0u;
+        if (!__any_sync(0xFFFFFFFFu, masks[ci] != 0u)) continue;  // warp-uniform
+        const int c = c0 + ci;
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        const uint32_t inv_row0 = 0xFFFFFFFFu - (tile_row0 + (uint32_t)c * 32);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if ((mask >> (8 * g)) & 0xFFu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    list_append_if(list, inv_row0 - (uint32_t)(8 * g + j), __float_as_uint(v[8 * g + j]),
+                                   mask & (1u << (8 * g + j)));
             }
         }
     }
@@ -153,8 +169,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     constexpr int B_BOXES = C::B_LOCAL_BYTES / (BOX_ROWS * BK_BYTES);  // 2 (single CTA) or 1 (pair)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t strip_base = base + STAGES * STAGE_BYTES;
-    const uint32_t bar_base = strip_base + STRIP_BYTES;
+    const uint32_t bar_base = base + STAGES * STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
@@ -268,7 +283,6 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the columns
         const int w = (warp - EPI_WARP0) & 3;
         const int c0 = ((warp - EPI_WARP0) >> 2) * EPI_CHUNKS;
-        const uint32_t sbase = strip_base + ((uint32_t)threadIdx.x - EPI_WARP0 * 32) * 4u;
         const uint32_t tempty0 = kCtas == 2 ? mapa_shared(tempty_bar(0), 0) : tempty_bar(0);
         int it = 0;
         for (int t = t_begin; t < t_end; ++t, ++it) {
@@ -284,7 +298,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
             if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0, c0, c0 + EPI_CHUNKS);
-            else epilogue_filter(a, sbase, taddr, q, thr, tile_row0, c0);
+            else epilogue_filter(a, taddr, q, thr, tile_row0, c0);
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) {
