@@ -99,7 +99,7 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
                      int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream);
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
- * streaming kernel for 16-bit storage), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
+ * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
  * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),
  * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant), "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback). */

@@ -165,7 +165,7 @@ struct fip_index {
 
     // options
     int variant = FIP_VARIANT_AUTO;
-    int stream_max_batch = 4;
+    int stream_max_batch = 0;  // 0 = by arithmetic intensity (nq <= sizeof(storage))
     int force_safe = 0;
     int query_split = 0;  // 0 = auto (1 for fp16 / fp32 storage, 2 for bf16)
     int cta_pair = 0;     // 0 = auto, 1 = single-CTA MMAs, 2 = CTA pairs (cta_group::2)
@@ -246,35 +246,36 @@ template <typename T, int QB, int R>
 int launch_stream_pass(SearchCtx& c, const ScanArgs& a, const float* q32, int q0) {
     fip_index* idx = c.idx;
     auto kern = stream_scan_kernel<T, QB, R>;
-    size_t smem = (size_t)QB * a.dim * sizeof(float);
-    FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    FIP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
-    per_sm = std::max(1, std::min(per_sm, 4));
-    int64_t groups = ((int64_t)(a.row_end - a.row_begin) + R - 1) / R;
-    int grid = (int)std::min<int64_t>((int64_t)idx->num_sms * per_sm, (groups + 7) / 8);
+    const StreamPlan plan = plan_stream(QB, R, (size_t)a.dim * sizeof(T), a.dim);
+    if (plan.warps == 0 || plan.slots < 2)
+        return fail(FIP_ERR_INVALID, "dim too large for the streaming kernel (a row block does not fit "
+                                     "in shared memory twice)");
+    FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
+    const int64_t blocks = ((int64_t)(a.row_end - a.row_begin) + R - 1) / R;
+    int grid = (int)std::min<int64_t>((int64_t)idx->num_sms, (blocks + plan.warps - 1) / plan.warps);
     grid = std::max(grid, 1);
-    kern<<<grid, 256, smem, c.stream>>>(a, q32, q0);
+    kern<<<grid, plan.warps * 32, plan.smem, c.stream>>>(a, q32, q0, plan.slots);
     FIP_CUDA(cudaGetLastError());
     c.launches++;
     return FIP_OK;
 }
 
+// Rows per block: 4 for 16-bit storage, 2 for fp32 (same bytes per block); 16-query passes halve
+// it to stay inside the register budget.
 template <typename T>
 int launch_stream_phase(SearchCtx& c, const ScanArgs& a, const float* q32) {
-    const int max_qb_smem = (int)((220 * 1024) / ((size_t)a.dim * sizeof(float)));
-    if (max_qb_smem < 1) return fail(FIP_ERR_INVALID, "dim too large for the streaming kernel");
+    constexpr int R = sizeof(T) == 4 ? 2 : 4;
     for (int q0 = 0; q0 < a.nq;) {
         int rem = a.nq - q0;
         int qb = rem >= 16 ? 16 : next_pow2(rem);
-        while (qb > max_qb_smem) qb >>= 1;
+        while (qb > 1 && plan_stream(qb, qb == 16 ? R / 2 : R, (size_t)a.dim * sizeof(T), a.dim).slots < 2) qb >>= 1;
         int rc;
         switch (qb) {
-            case 1: rc = launch_stream_pass<T, 1, 8>(c, a, q32, q0); break;
-            case 2: rc = launch_stream_pass<T, 2, 8>(c, a, q32, q0); break;
-            case 4: rc = launch_stream_pass<T, 4, 8>(c, a, q32, q0); break;
-            case 8: rc = launch_stream_pass<T, 8, 4>(c, a, q32, q0); break;
-            default: rc = launch_stream_pass<T, 16, 4>(c, a, q32, q0); qb = 16; break;
+            case 1: rc = launch_stream_pass<T, 1, R>(c, a, q32, q0); break;
+            case 2: rc = launch_stream_pass<T, 2, R>(c, a, q32, q0); break;
+            case 4: rc = launch_stream_pass<T, 4, R>(c, a, q32, q0); break;
+            case 8: rc = launch_stream_pass<T, 8, R>(c, a, q32, q0); break;
+            default: rc = launch_stream_pass<T, 16, R / 2>(c, a, q32, q0); qb = 16; break;
         }
         if (rc) return rc;
         q0 += qb;
@@ -388,12 +389,21 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     }
     int variant = idx->variant;
     const bool tc_ok = (dim * dtype_size(dtype)) % tc::BK_BYTES == 0;
-    if (variant == FIP_VARIANT_AUTO)
+    if (variant == FIP_VARIANT_AUTO) {
         // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
-        // CUDA-core kernel stays HBM-bound only while nq * dim FMAs per row fit under the FP32 pipe
-        // (nq <= ~4); above that the tensor pipe is needed to stay on the HBM roof, and above
-        // ~210 flop/byte (nq > ~210 for 16-bit storage) the tensor pipe itself is the roof.
-        variant = (tc_ok && nq > idx->stream_max_batch) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
+        // CUDA-core kernel (FMA + unpack + LDS per element) keeps up with HBM up to ~2 flop/byte
+        // (measured: 0.94-0.98 of the copy bandwidth at nq = 2 for 16-bit and nq = 4 for fp32
+        // storage, 0.73 at twice that); above it the tensor pipe is needed to stay on the HBM
+        // roof, and above ~210 flop/byte (nq > ~210 for 16-bit storage) the tensor pipe itself is
+        // the roof.  The streaming kernel maps the 32 lanes of a warp onto the 16-byte vectors of a
+        // row, so rows shorter than 1 KB (2 x 512 bytes) leave lanes idle (0.68-0.83 measured at
+        // 256 / 768-byte rows): those go to the tensor-core kernel at any batch size.
+        // stream_max_batch > 0 overrides the rule.
+        const bool long_rows = (size_t)dim * dtype_size(dtype) >= 1024;
+        const int stream_max = idx->stream_max_batch > 0 ? idx->stream_max_batch
+                                                         : (long_rows ? dtype_size(dtype) : 0);
+        variant = (tc_ok && nq > stream_max) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
+    }
     if (variant == FIP_VARIANT_TENSOR && !tc_ok)
         return fail(FIP_ERR_INVALID, "tensor-core variant needs rows that are a multiple of 128 bytes "
                                      "(dim % 64 == 0 for fp16/bf16, dim % 32 == 0 for fp32)");

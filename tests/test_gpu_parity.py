@@ -108,18 +108,33 @@ def test_parity_with_oracle(variant, dtype, n, dim, nq, k):
 
 
 def test_auto_variant_follows_arithmetic_intensity():
-    idx = _index(128, "f16")
+    idx = _index(512, "f16")                   # 1 KB rows
     idx.add_synthetic(5000, 1, 0)
-    idx.search(synthetic.synthetic_queries(2, 128), 5)
-    assert idx.last_variant() == "stream"      # tiny batch: HBM-bound on CUDA cores
-    idx.search(synthetic.synthetic_queries(64, 128), 5)
+    idx.search(synthetic.synthetic_queries(2, 512), 5)
+    assert idx.last_variant() == "stream"      # 2 flop/byte: HBM-bound on CUDA cores
+    idx.search(synthetic.synthetic_queries(3, 512), 5)
+    assert idx.last_variant() == "tensor"      # 3 flop/byte: past what FMA + unpack sustain
+    idx.search(synthetic.synthetic_queries(64, 512), 5)
     assert idx.last_variant() == "tensor"      # needs the tensor pipe to stay on the HBM roof
     idx.close()
-    idx = _index(128, "f32")
+    idx = _index(256, "f32")                   # 1 KB rows
     idx.add_synthetic(5000, 1, 0)
-    idx.search(synthetic.synthetic_queries(64, 128), 5)
+    idx.search(synthetic.synthetic_queries(64, 256), 5)
     assert idx.last_variant() == "tensor"      # fp32 storage: tf32 filter + exact fp32 rescoring
-    idx.search(synthetic.synthetic_queries(3, 128), 5)
+    idx.search(synthetic.synthetic_queries(3, 256), 5)
+    assert idx.last_variant() == "stream"
+    idx.close()
+    idx = _index(128, "f16")                   # 256-byte rows: half a warp per row -> tensor
+    idx.add_synthetic(5000, 1, 0)
+    idx.search(synthetic.synthetic_queries(1, 128), 5)
+    assert idx.last_variant() == "tensor"
+    idx.set_option("stream_max_batch", 4)      # explicit override
+    idx.search(synthetic.synthetic_queries(4, 128), 5)
+    assert idx.last_variant() == "stream"
+    idx.close()
+    idx = _index(40, "f16")                    # rows not a multiple of 128 bytes: no TMA tiles
+    idx.add_synthetic(5000, 1, 0)
+    idx.search(synthetic.synthetic_queries(64, 40), 5)
     assert idx.last_variant() == "stream"
     idx.close()
 
