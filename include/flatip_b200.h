@@ -97,6 +97,12 @@ int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int3
  */
 int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int32_t g, int64_t nq,
                      int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream);
+/* Same merge over a PACKED exchange buffer: shard r's distances start at in_d + r * stride_d and its
+ * ids at in_i + r * stride_i (strides in elements).  Lets a rank ship distances and ids in ONE
+ * all-gather (one buffer per rank: [nq * k_in fp32 | pad to 16 bytes | nq * k_in int64]). */
+int fip_merge_strided_device(int32_t device, const float* in_d, const int64_t* in_i, int64_t stride_d,
+                             int64_t stride_i, int32_t g, int64_t nq, int32_t k_in, int32_t k_out,
+                             float* out_d, int64_t* out_i, void* cuda_stream);
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query

@@ -9,12 +9,12 @@ Public surface:
 """
 
 from .factory import COMPONENT_TYPE, create_b200_flat_ip_store, install
-from .index import FlatIPIndex, merge_device
+from .index import FlatIPIndex, merge_device, merge_strided_device
 from .store import B200FlatIPStore
 
 __all__ = [
     "B200FlatIPStore", "FlatIPIndex", "ShardedFlatIPSearcher", "COMPONENT_TYPE",
-    "create_b200_flat_ip_store", "install", "merge_device",
+    "create_b200_flat_ip_store", "install", "merge_device", "merge_strided_device",
 ]
 
 

@@ -33,7 +33,7 @@ FIP_ERR_STATE = -5
 EXPORTED_SYMBOLS = (
     "fip_create", "fip_destroy", "fip_add_host_f32", "fip_add_device", "fip_add_synthetic",
     "fip_reset", "fip_reconstruct", "fip_ntotal", "fip_dim", "fip_dtype_of", "fip_search",
-    "fip_search_device", "fip_merge_device", "fip_set_option", "fip_get_stat", "fip_last_error",
+    "fip_search_device", "fip_merge_device", "fip_merge_strided_device", "fip_set_option", "fip_get_stat", "fip_last_error",
     "fip_abi_version", "fip_compiled_sm",
 )
 
@@ -102,6 +102,9 @@ def load_library():
         lib.fip_merge_device.argtypes = [c.c_int32, P, P, c.c_int32, c.c_int64, c.c_int32,
                                          c.c_int32, P, P, P]
         lib.fip_merge_device.restype = c.c_int
+        lib.fip_merge_strided_device.argtypes = [c.c_int32, P, P, c.c_int64, c.c_int64, c.c_int32,
+                                                 c.c_int64, c.c_int32, c.c_int32, P, P, P]
+        lib.fip_merge_strided_device.restype = c.c_int
         lib.fip_set_option.argtypes = [P, c.c_char_p, c.c_int64]
         lib.fip_set_option.restype = c.c_int
         lib.fip_get_stat.argtypes = [P, c.c_char_p]

@@ -932,14 +932,17 @@ int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int3
     return search_checked(idx, queries_dev, (int)nq, k, distances_dev, ids_dev, s);
 }
 
-int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int32_t g, int64_t nq,
-                     int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream) {
+int fip_merge_strided_device(int32_t device, const float* in_d, const int64_t* in_i, int64_t stride_d,
+                             int64_t stride_i, int32_t g, int64_t nq, int32_t k_in, int32_t k_out,
+                             float* out_d, int64_t* out_i, void* cuda_stream) {
     if (!in_d || !in_i || !out_d || !out_i || g < 1 || nq < 0 || k_in < 1 || k_out < 1)
         return fail(FIP_ERR_INVALID, "bad argument");
     if ((int64_t)g * k_in > kMaxCap) return fail(FIP_ERR_INVALID, "g * k_in must be <= 16384");
+    if (stride_d < nq * k_in || stride_i < nq * k_in)
+        return fail(FIP_ERR_INVALID, "shard stride smaller than one shard's result");
     if (nq == 0) return FIP_OK;
     FIP_CUDA(cudaSetDevice(device));
-    MergeArgs m{in_d, in_i, g, (int)nq, k_in, k_out, out_d, out_i};
+    MergeArgs m{in_d, in_i, g, (int)nq, k_in, k_out, stride_d, stride_i, out_d, out_i};
     int n = next_pow2(g * k_in);
     size_t smem = (size_t)n * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 1024)));
@@ -947,6 +950,12 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
     merge_topk_kernel<<<(unsigned)nq, threads, smem, (cudaStream_t)cuda_stream>>>(m);
     FIP_CUDA(cudaGetLastError());
     return FIP_OK;
+}
+
+int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int32_t g, int64_t nq,
+                     int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream) {
+    return fip_merge_strided_device(device, in_d, in_i, nq * (int64_t)k_in, nq * (int64_t)k_in, g, nq, k_in,
+                                    k_out, out_d, out_i, cuda_stream);
 }
 
 int fip_set_option(fip_index* idx, const char* key, int64_t value) {

@@ -284,6 +284,7 @@ struct MergeArgs {
     const float* in_d;
     const int64_t* in_i;
     int g, nq, k_in, k_out;
+    int64_t stride_d, stride_i;  // elements between shard r and shard r+1 (nq * k_in when packed)
     float* out_d;      // [nq, k_out]
     int64_t* out_i;    // [nq, k_out]
 };
@@ -298,8 +299,9 @@ __global__ void merge_topk_kernel(MergeArgs a) {
         uint64_t key = 0ull;
         if (i < total) {
             int r = i / a.k_in, p = i - r * a.k_in;
-            size_t off = ((size_t)r * a.nq + q) * a.k_in + p;
-            if (a.in_i[off] >= 0) key = make_key(a.in_d[off], (uint32_t)i);
+            size_t off = (size_t)q * a.k_in + p;
+            if (a.in_i[(size_t)r * a.stride_i + off] >= 0)
+                key = make_key(a.in_d[(size_t)r * a.stride_d + off], (uint32_t)i);
         }
         s_keys[i] = key;
     }
@@ -312,9 +314,9 @@ __global__ void merge_topk_kernel(MergeArgs a) {
         if (key != 0ull) {
             int src = (int)key_row(key);
             int r = src / a.k_in, p = src - r * a.k_in;
-            size_t off = ((size_t)r * a.nq + q) * a.k_in + p;
-            d = a.in_d[off];
-            id = a.in_i[off];
+            size_t off = (size_t)q * a.k_in + p;
+            d = a.in_d[(size_t)r * a.stride_d + off];
+            id = a.in_i[(size_t)r * a.stride_i + off];
         }
         a.out_d[(size_t)q * a.k_out + i] = d;
         a.out_i[(size_t)q * a.k_out + i] = id;

@@ -116,3 +116,14 @@ def merge_device(device: int, in_d_ptr: int, in_i_ptr: int, g: int, nq: int, k_i
     _native.check(lib.fip_merge_device(int(device), P(in_d_ptr), P(in_i_ptr), int(g), int(nq),
                                        int(k_in), int(k_out), P(out_d_ptr), P(out_i_ptr),
                                        P(stream)))
+
+
+def merge_strided_device(device: int, in_d_ptr: int, in_i_ptr: int, stride_d: int, stride_i: int,
+                         g: int, nq: int, k_in: int, k_out: int, out_d_ptr: int, out_i_ptr: int,
+                         stream: int = 0) -> None:
+    """K3 merge over a packed exchange buffer (shard strides in elements)."""
+    lib = _native.load_library()
+    P = ctypes.c_void_p
+    _native.check(lib.fip_merge_strided_device(
+        int(device), P(in_d_ptr), P(in_i_ptr), int(stride_d), int(stride_i), int(g), int(nq),
+        int(k_in), int(k_out), P(out_d_ptr), P(out_i_ptr), P(stream)))

@@ -2,9 +2,9 @@
 
 The corpus is split into contiguous row shards (rank r owns global rows
 ``[r * ceil(N/g), min(N, (r+1) * ceil(N/g)))``); every rank runs the local search on its shard
-(queries replicated), the per-shard ``[B, k]`` results are exchanged with ONE NCCL all-gather over
-NVLink (12 * B * k bytes per rank -- latency-bound), and every rank merges the g sorted lists with
-the K3 kernel.  Because shards are contiguous and ordered, "shard index, then position" equals
+(queries replicated) straight into a packed ``[distances | ids]`` buffer, the per-shard results are
+exchanged with ONE NCCL all-gather over NVLink (12 * B * k bytes per rank -- latency-bound, so one
+collective instead of two), and every rank merges the g sorted lists with the K3 kernel.  Because shards are contiguous and ordered, "shard index, then position" equals
 "id ascending", so the global tie-break (score desc, id asc) is preserved.
 
 The reference has no counterpart (faiss-cpu in one process,
@@ -16,7 +16,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from .index import FlatIPIndex, merge_device
+from .index import FlatIPIndex, merge_strided_device
 
 
 def shard_range(total_rows: int, rank: int, world_size: int) -> tuple[int, int]:
@@ -29,15 +29,25 @@ def shard_range(total_rows: int, rank: int, world_size: int) -> tuple[int, int]:
     return begin, end
 
 
-def gather_and_merge(local_d, local_i, k: int, *, world_size: int, all_gather, merge):
-    """The exchange step, backend-agnostic: ``all_gather(t) -> [g, ...]`` stacked in rank order,
-    ``merge(all_d, all_i, k) -> (D, I)``.  Split out so the world_size > 1 plumbing can be
-    exercised on CPU with gloo (tests) while production passes the NCCL / K3 callables."""
+def pack_layout(nq: int, k: int) -> tuple[int, int]:
+    """Byte layout of one rank's exchange buffer: ``[nq*k fp32 | pad to 16 B | nq*k int64]``.
+    Returns (offset of the ids, total bytes); total is a multiple of 16 so that the ids of every
+    rank stay 8-byte aligned inside the gathered ``[g, total]`` buffer."""
+    off_i = (int(nq) * int(k) * 4 + 15) // 16 * 16
+    total = (off_i + int(nq) * int(k) * 8 + 15) // 16 * 16
+    return off_i, total
+
+
+def gather_and_merge(pack, nq: int, k: int, *, world_size: int, all_gather, merge):
+    """The exchange step, backend-agnostic.  ``pack`` is this rank's packed result (pack_layout);
+    ``all_gather(pack) -> [g, total]`` stacks the ranks' buffers in rank order (ONE collective for
+    distances and ids); ``merge(all_pack, off_i, total) -> (D, I)``.  Split out so the
+    world_size > 1 plumbing can be exercised on CPU with gloo (tests) while production passes the
+    NCCL / K3 callables."""
+    off_i, total = pack_layout(nq, k)
     if world_size == 1:
-        return local_d, local_i
-    all_d = all_gather(local_d)
-    all_i = all_gather(local_i)
-    return merge(all_d, all_i, k)
+        return merge(pack.reshape(1, total), off_i, total)
+    return merge(all_gather(pack), off_i, total)
 
 
 class ShardedFlatIPSearcher:
@@ -83,28 +93,33 @@ class ShardedFlatIPSearcher:
         queries = queries.contiguous()
         B = queries.shape[0]
         stream = torch.cuda.current_stream(queries.device).cuda_stream
-        d_loc = torch.empty((B, k), dtype=torch.float32, device=queries.device)
-        i_loc = torch.empty((B, k), dtype=torch.int64, device=queries.device)
+        off_i, total = pack_layout(B, k)
+        pack = torch.empty((total,), dtype=torch.uint8, device=queries.device)
+        d_loc = pack[:B * k * 4].view(torch.float32).view(B, k)
+        i_loc = pack[off_i:off_i + B * k * 8].view(torch.int64).view(B, k)
         self.index.search_device(queries.data_ptr(), B, k, d_loc.data_ptr(), i_loc.data_ptr(),
                                  stream)
+        if self.world_size == 1:
+            return d_loc, i_loc
 
         def all_gather(t):
             import torch.distributed as dist
 
-            out = torch.empty((self.world_size,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+            out = torch.empty((self.world_size, t.numel()), dtype=t.dtype, device=t.device)
             dist.all_gather_into_tensor(out, t, group=self.group)
             return out
 
-        def merge(all_d, all_i, kk):
-            d_out = torch.empty((B, kk), dtype=torch.float32, device=queries.device)
-            i_out = torch.empty((B, kk), dtype=torch.int64, device=queries.device)
-            merge_device(self.device, all_d.data_ptr(), all_i.data_ptr(), self.world_size, B, kk,
-                         kk, d_out.data_ptr(), i_out.data_ptr(),
-                         torch.cuda.current_stream(queries.device).cuda_stream)
+        def merge(all_pack, off, tot):
+            d_out = torch.empty((B, k), dtype=torch.float32, device=queries.device)
+            i_out = torch.empty((B, k), dtype=torch.int64, device=queries.device)
+            merge_strided_device(self.device, all_pack.data_ptr(), all_pack.data_ptr() + off,
+                                 tot // 4, tot // 8, self.world_size, B, k, k,
+                                 d_out.data_ptr(), i_out.data_ptr(),
+                                 torch.cuda.current_stream(queries.device).cuda_stream)
             return d_out, i_out
 
-        return gather_and_merge(d_loc, i_loc, k, world_size=self.world_size,
-                                all_gather=all_gather, merge=merge)
+        return gather_and_merge(pack, B, k, world_size=self.world_size, all_gather=all_gather,
+                                merge=merge)
 
     # ------------------------------------------------------------------ host-buffer path
     def search(self, queries: np.ndarray, k: int):

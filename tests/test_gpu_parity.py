@@ -382,6 +382,49 @@ def test_merge_kernel_matches_oracle():
     assert np.array_equal(oi.cpu().numpy(), Ir)
 
 
+def test_packed_exchange_buffer_merge():
+    """The packed [distances | pad | ids] per-rank buffer of sharded.py, gathered as [g, total]
+    bytes, merged by the strided K3 entry point == the oracle merge."""
+    import torch
+    from rag_inference_pipeline_b200 import merge_strided_device
+    from rag_inference_pipeline_b200.sharded import pack_layout
+
+    rng = np.random.default_rng(11)
+    g, nq, k = 4, 5, 33                               # nq * k odd: the ids need the padding
+    d = np.sort(rng.standard_normal((g, nq, k)).astype(np.float32), axis=2)[:, :, ::-1].copy()
+    ids = (np.sort(rng.integers(0, 500, (g, nq, k)), axis=2) + (np.arange(g) * 500)[:, None, None]).astype(np.int64)
+    off_i, total = pack_layout(nq, k)
+    packed = np.zeros((g, total), dtype=np.uint8)
+    for r in range(g):
+        packed[r, :nq * k * 4] = d[r].view(np.uint8).ravel()
+        packed[r, off_i:off_i + nq * k * 8] = ids[r].view(np.uint8).ravel()
+    Dr, Ir = flatip_oracle.merge_sorted_lists(d, ids, k)
+    tp = torch.from_numpy(packed).cuda()
+    od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    oi = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    merge_strided_device(0, tp.data_ptr(), tp.data_ptr() + off_i, total // 4, total // 8, g, nq, k, k,
+                         od.data_ptr(), oi.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(od.cpu().numpy(), Dr)
+    assert np.array_equal(oi.cpu().numpy(), Ir)
+
+
+def test_sharded_searcher_single_rank_matches_oracle():
+    import torch
+    from rag_inference_pipeline_b200 import ShardedFlatIPSearcher
+
+    dim, n, nq, k = 128, 30_001, 9, 7
+    s = ShardedFlatIPSearcher(dim, "f16", n, rank=0, world_size=1, device=0)
+    s.load_synthetic(synthetic.CORPUS_SEED)
+    q = synthetic.synthetic_queries(nq, dim)
+    D, I = s.search_tensor(torch.from_numpy(q).cuda(), k)
+    torch.cuda.synchronize()
+    corpus = synthetic.synthetic_corpus(0, n, dim, "f16")
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
+    _check(D.cpu().numpy(), I.cpu().numpy(), Dr, Ir, "f16")
+    s.close()
+
+
 def test_sharded_search_equals_single_index():
     """Row-shard emulation on one GPU: g shard indexes searched one after the other, results
     stacked like an all-gather leaves them, merged by K3 == one index over the whole corpus."""

@@ -10,7 +10,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from rag_inference_pipeline_b200.sharded import gather_and_merge, shard_range
+from rag_inference_pipeline_b200.sharded import gather_and_merge, pack_layout, shard_range
 
 
 def test_shard_ranges_cover_exactly():
@@ -25,6 +25,13 @@ def test_shard_ranges_cover_exactly():
             assert e0 == b1
     with pytest.raises(ValueError):
         shard_range(10, 2, 2)
+
+
+def test_pack_layout_alignment():
+    for nq, k in [(1, 1), (3, 5), (7, 30), (1024, 100), (256, 1024)]:
+        off_i, total = pack_layout(nq, k)
+        assert off_i >= nq * k * 4 and off_i % 16 == 0
+        assert total >= off_i + nq * k * 8 and total % 16 == 0
 
 
 def _free_port():
@@ -51,14 +58,28 @@ def _worker(rank, world, port, total, dim, nq, k, out_dir):
     q = synthetic.synthetic_queries(nq, dim)
     d_loc, i_loc = flatip_oracle.flat_ip_search(q, corpus, k, id_base=b)
 
+    # this rank's packed exchange buffer, laid out exactly like the CUDA path's
+    off_i, total = pack_layout(nq, k)
+    pack = np.zeros(total, dtype=np.uint8)
+    pack[:nq * k * 4] = np.ascontiguousarray(d_loc).view(np.uint8).ravel()
+    pack[off_i:off_i + nq * k * 8] = np.ascontiguousarray(i_loc).view(np.uint8).ravel()
+    calls = []
+
     def all_gather(t):
-        t = torch.from_numpy(np.ascontiguousarray(t))
+        calls.append(1)
+        t = torch.from_numpy(t)
         out = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(out, t)
         return torch.stack(out).numpy()
 
-    D, I = gather_and_merge(d_loc, i_loc, k, world_size=world, all_gather=all_gather,
-                            merge=flatip_oracle.merge_sorted_lists)
+    def merge(all_pack, off, tot):
+        assert all_pack.shape == (world, tot) and off == off_i
+        all_d = np.stack([all_pack[r, :nq * k * 4].view(np.float32).reshape(nq, k) for r in range(world)])
+        all_i = np.stack([all_pack[r, off:off + nq * k * 8].view(np.int64).reshape(nq, k) for r in range(world)])
+        return flatip_oracle.merge_sorted_lists(all_d, all_i, k)
+
+    D, I = gather_and_merge(pack, nq, k, world_size=world, all_gather=all_gather, merge=merge)
+    assert len(calls) == 1          # distances and ids travel in ONE collective
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), D=D, I=I)
     dist.barrier()
     dist.destroy_process_group()
