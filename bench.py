@@ -222,7 +222,7 @@ def run_b200(args, rank, local_rank, world):
         torch.cuda.synchronize()
 
     searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=rank, world_size=world,
-                                     device=local_rank)
+                                     device=local_rank, exchange=args.exchange)
     t0 = time.time()
     searcher.load_synthetic(CORPUS_SEED)
     load_s = time.time() - t0
@@ -250,7 +250,7 @@ def run_b200(args, rank, local_rank, world):
     e0.record()
     for _ in range(args.steps):
         D, I = searcher.search_tensor(q_dev, k)
-        launches += searcher.index.stat("launches") + (2 if world > 1 else 0)
+        launches += searcher.index.stat("launches") + (1 if world > 1 else 0)   # + exchange/merge kernel
         scan_ns += searcher.index.stat("scan_time_ns")
         scan_launches += searcher.index.stat("scan_launches")
         for i in range(64):
@@ -370,6 +370,7 @@ def run_b200(args, rank, local_rank, world):
             "variant": variant, "phases_per_search": phases, "overflow_queries": overflow,
             "uncertified_queries": searcher.index.stat("uncertified_queries"),
             "cta_group": searcher.index.stat("cta_group"),
+            "exchange": searcher.exchange_used,
             "corpus_load_s": load_s, "verify": verify,
         }
         sys.stdout.flush()
@@ -394,6 +395,8 @@ def main():
     ap.add_argument("--k", type=int, default=0)
     ap.add_argument("--variant", choices=["auto", "stream", "tensor"], default="auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", choices=["auto", "p2p", "nccl"], default="auto",
+                    help="N > 1: fused peer-memory exchange + merge kernel, or NCCL all-gather + merge")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", 0))

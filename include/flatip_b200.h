@@ -104,6 +104,32 @@ int fip_merge_strided_device(int32_t device, const float* in_d, const int64_t* i
                              int64_t stride_i, int32_t g, int64_t nq, int32_t k_in, int32_t k_out,
                              float* out_d, int64_t* out_i, void* cuda_stream);
 
+/*
+ * Fused exchange + merge over NVLink peer memory (K4, csrc/exchange.cuh): the one-kernel
+ * replacement for "all-gather, then fip_merge_device".  One fip_exchange per rank; every rank
+ * allocates a buffer its peers can write (CUDA IPC between processes, peer access inside one
+ * process), and fip_exchange_merge launches ONE kernel that stores this rank's local [nq, k]
+ * result into every rank's buffer, waits per query for the other ranks' rows and merges them.
+ * Like a collective, every rank of the group must make the same sequence of fip_exchange_merge
+ * calls (same nq, k).  No counterpart in the reference (single process).
+ *   create        allocate for up to nq_max queries x k_max results, world <= 16 ranks
+ *   ipc_handle    64-byte handle of the local buffer (to be all-gathered by the host runtime)
+ *   connect_ipc   map the peers' buffers from `world` concatenated handles (own slot ignored)
+ *   connect_local same for exchanges living in THIS process (one per device, or several on one
+ *                 device for tests): all[r] is rank r's exchange
+ *   merge         asynchronous on `cuda_stream`; d_loc / i_loc / out_* are device buffers [nq, k]
+ */
+#define FIP_IPC_HANDLE_BYTES 64
+typedef struct fip_exchange fip_exchange;
+int fip_exchange_create(int32_t device, int32_t world, int32_t rank, int64_t nq_max, int32_t k_max,
+                        fip_exchange** out);
+int fip_exchange_ipc_handle(fip_exchange* x, void* handle_out);
+int fip_exchange_connect_ipc(fip_exchange* x, const void* all_handles);
+int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all);
+int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
+                       float* out_d, int64_t* out_i, void* cuda_stream);
+void fip_exchange_destroy(fip_exchange* x);
+
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
  * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),

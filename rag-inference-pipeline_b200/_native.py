@@ -35,7 +35,10 @@ EXPORTED_SYMBOLS = (
     "fip_reset", "fip_reconstruct", "fip_ntotal", "fip_dim", "fip_dtype_of", "fip_search",
     "fip_search_device", "fip_merge_device", "fip_merge_strided_device", "fip_set_option", "fip_get_stat", "fip_last_error",
     "fip_abi_version", "fip_compiled_sm",
+    "fip_exchange_create", "fip_exchange_ipc_handle", "fip_exchange_connect_ipc",
+    "fip_exchange_connect_local", "fip_exchange_merge", "fip_exchange_destroy",
 )
+IPC_HANDLE_BYTES = 64
 
 
 class FipConfig(ctypes.Structure):
@@ -105,6 +108,19 @@ def load_library():
         lib.fip_merge_strided_device.argtypes = [c.c_int32, P, P, c.c_int64, c.c_int64, c.c_int32,
                                                  c.c_int64, c.c_int32, c.c_int32, P, P, P]
         lib.fip_merge_strided_device.restype = c.c_int
+        lib.fip_exchange_create.argtypes = [c.c_int32, c.c_int32, c.c_int32, c.c_int64, c.c_int32,
+                                            c.POINTER(P)]
+        lib.fip_exchange_create.restype = c.c_int
+        lib.fip_exchange_ipc_handle.argtypes = [P, P]
+        lib.fip_exchange_ipc_handle.restype = c.c_int
+        lib.fip_exchange_connect_ipc.argtypes = [P, P]
+        lib.fip_exchange_connect_ipc.restype = c.c_int
+        lib.fip_exchange_connect_local.argtypes = [P, c.POINTER(P)]
+        lib.fip_exchange_connect_local.restype = c.c_int
+        lib.fip_exchange_merge.argtypes = [P, P, P, c.c_int64, c.c_int32, P, P, P]
+        lib.fip_exchange_merge.restype = c.c_int
+        lib.fip_exchange_destroy.argtypes = [P]
+        lib.fip_exchange_destroy.restype = None
         lib.fip_set_option.argtypes = [P, c.c_char_p, c.c_int64]
         lib.fip_set_option.restype = c.c_int
         lib.fip_get_stat.argtypes = [P, c.c_char_p]

@@ -18,6 +18,7 @@
 
 #include "../../include/flatip_b200.h"
 #include "common.cuh"
+#include "exchange.cuh"
 #include "select.cuh"
 #include "stream_scan.cuh"
 #include "synthetic.cuh"
@@ -230,10 +231,35 @@ int reserve_rows(fip_index* idx, int64_t want) {
     return FIP_OK;
 }
 
-int cap_for_k(int k, bool safe) {
+double phase_growth(int cap, int k_plan) {
+    const int keff = std::max(k_plan, 16);
+    return std::max(2.0, ((double)cap / 2 - keff) / keff);
+}
+int count_phases(int64_t n, int cap, int k_plan) {
+    const double growth = phase_growth(cap, k_plan);
+    int64_t pos = std::min<int64_t>(n, cap);
+    int phases = 1;
+    while (pos < n) {
+        pos += std::max<int64_t>(256, (int64_t)((double)pos * growth) / 256 * 256);
+        phases++;
+    }
+    return phases;
+}
+// Candidate-list capacity per query.  The floor (4096, or 32 x k for large k) keeps the lists of a
+// big batch small; every phase boundary costs a select pass and a scan launch (~50 us), so a small
+// batch -- whose lists are cheap and whose select passes fit one wave of CTAs -- takes a larger
+// capacity when that saves a phase (3 instead of 4 phases for shards between 1.1 M and 70 M rows
+// at k = 100).
+int cap_for_k(int k, bool safe, int nq, int64_t n) {
     if (safe) return kMaxCap;
-    int cap = std::max(4096, 32 * next_pow2(k));
-    return std::min(cap, kMaxCap);
+    int cap = std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
+    int best_phases = count_phases(n, cap, k);
+    for (int c = cap * 2; c <= kMaxCap; c *= 2) {
+        if ((int64_t)nq * c > (int64_t)148 * kMaxCap) break;
+        const int ph = count_phases(n, c, k);
+        if (ph < best_phases) { best_phases = ph; cap = c; }
+    }
+    return cap;
 }
 
 struct SearchCtx {
@@ -428,7 +454,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     const int k_plan = !rescore ? k
                        : (dtype == kBF16 && split == 1) ? k + std::max(48, 3 * k / 4)
                                                         : k + std::max(16, k / 4);
-    const int cap = cap_for_k(k_plan, mode.safe);
+    const int cap = cap_for_k(k_plan, mode.safe, nq, n);
     const int keep_max = certify ? std::min(cap / 2, k_out + 2 * (k_plan - k_out)) : 0;
     const int k_sel = certify ? k_out : k_plan;   // what the intermediate selects look for
     FIP_CUDA(idx->thr.ensure(nq));
@@ -514,8 +540,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         return FIP_OK;
     };
 
-    const int keff = std::max(k_plan, 16);
-    const double growth = std::max(2.0, ((double)cap / 2 - keff) / keff);
+    const double growth = phase_growth(cap, k_plan);
     int phases = 0;
     // phase 0: no threshold yet, every score of the first rows is written (slot = row)
     int64_t m = std::min<int64_t>(n, cap);
@@ -956,6 +981,135 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
                      int32_t k_in, int32_t k_out, float* out_d, int64_t* out_i, void* cuda_stream) {
     return fip_merge_strided_device(device, in_d, in_i, nq * (int64_t)k_in, nq * (int64_t)k_in, g, nq, k_in,
                                     k_out, out_d, out_i, cuda_stream);
+}
+
+// ------------------------------------------------------------------ fused exchange + merge (K4)
+struct fip_exchange {
+    int device = 0, world = 1, rank = 0, nq_max = 0, k_max = 0;
+    int64_t slot_bytes = 0, flags_off = 0, total_bytes = 0;
+    uint8_t* local = nullptr;
+    uint8_t* peer[kMaxRanks] = {};
+    bool ipc_opened[kMaxRanks] = {};
+    bool connected = false;
+    uint32_t epoch = 0;
+    std::mutex mu;
+};
+
+static int64_t round_up16(int64_t v) { return (v + 15) / 16 * 16; }
+
+int fip_exchange_create(int32_t device, int32_t world, int32_t rank, int64_t nq_max, int32_t k_max,
+                        fip_exchange** out) {
+    if (!out) return fail(FIP_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world)
+        return fail(FIP_ERR_INVALID, "world must be in [1, 16] and 0 <= rank < world");
+    if (nq_max < 1 || nq_max > (1 << 20) || k_max < 1 || k_max > kMaxK)
+        return fail(FIP_ERR_INVALID, "nq_max / k_max out of range");
+    if ((int64_t)world * k_max > kMaxCap) return fail(FIP_ERR_INVALID, "world * k_max must be <= 16384");
+    FIP_CUDA(cudaSetDevice(device));
+    fip_exchange* x = new (std::nothrow) fip_exchange();
+    if (!x) return fail(FIP_ERR_NOMEM, "host allocation failed");
+    x->device = device; x->world = world; x->rank = rank; x->nq_max = (int)nq_max; x->k_max = k_max;
+    x->slot_bytes = round_up16(round_up16(nq_max * k_max * 4) + nq_max * k_max * 8);
+    x->flags_off = 2 * (int64_t)world * x->slot_bytes;
+    x->total_bytes = x->flags_off + round_up16(2 * (int64_t)world * nq_max * 4);
+    cudaError_t e = cudaMalloc((void**)&x->local, (size_t)x->total_bytes);
+    if (e == cudaSuccess) e = cudaMemset(x->local, 0, (size_t)x->total_bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { if (x->local) cudaFree(x->local); delete x; FIP_CUDA(e); }
+    x->peer[rank] = x->local;
+    *out = x;
+    return FIP_OK;
+}
+
+int fip_exchange_ipc_handle(fip_exchange* x, void* handle_out) {
+    if (!x || !handle_out) return fail(FIP_ERR_INVALID, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == FIP_IPC_HANDLE_BYTES, "handle size");
+    FIP_CUDA(cudaSetDevice(x->device));
+    cudaIpcMemHandle_t h;
+    FIP_CUDA(cudaIpcGetMemHandle(&h, x->local));
+    memcpy(handle_out, &h, sizeof(h));
+    return FIP_OK;
+}
+
+int fip_exchange_connect_ipc(fip_exchange* x, const void* all_handles) {
+    if (!x || !all_handles) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lock(x->mu);
+    FIP_CUDA(cudaSetDevice(x->device));
+    for (int r = 0; r < x->world; ++r) {
+        if (r == x->rank || x->peer[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)all_handles + (size_t)r * sizeof(h), sizeof(h));
+        void* p = nullptr;
+        FIP_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        x->peer[r] = (uint8_t*)p;
+        x->ipc_opened[r] = true;
+    }
+    x->connected = true;
+    return FIP_OK;
+}
+
+int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all) {
+    if (!x || !all) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lock(x->mu);
+    FIP_CUDA(cudaSetDevice(x->device));
+    for (int r = 0; r < x->world; ++r) {
+        if (r == x->rank) continue;
+        const fip_exchange* o = all[r];
+        if (!o || o->world != x->world || o->rank != r || o->slot_bytes != x->slot_bytes || o->nq_max != x->nq_max)
+            return fail(FIP_ERR_INVALID, "exchange objects do not describe the same group");
+        if (o->device != x->device) {
+            int can = 0;
+            FIP_CUDA(cudaDeviceCanAccessPeer(&can, x->device, o->device));
+            if (!can) return fail(FIP_ERR_STATE, "no peer access between the two devices");
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) FIP_CUDA(e);
+            cudaGetLastError();
+        }
+        x->peer[r] = o->local;
+    }
+    x->connected = true;
+    return FIP_OK;
+}
+
+int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
+                       float* out_d, int64_t* out_i, void* cuda_stream) {
+    if (!x || (nq > 0 && (!d_loc || !i_loc || !out_d || !out_i))) return fail(FIP_ERR_INVALID, "null argument");
+    if (nq < 0 || nq > x->nq_max || k < 1 || k > x->k_max)
+        return fail(FIP_ERR_INVALID, "nq / k exceed what the exchange was created for");
+    if (!x->connected && x->world > 1) return fail(FIP_ERR_STATE, "exchange is not connected to its peers");
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(x->mu);
+    // every rank makes the same sequence of calls (like a collective), so the epoch advances in
+    // lock-step and consecutive launches alternate buffer parity
+    x->epoch++;
+    if (x->epoch == 0) x->epoch = 2;  // wrapped (0xFFFFFFFF -> 2 keeps the parity alternating); 0 = "never written"
+    FIP_CUDA(cudaSetDevice(x->device));
+    ExchangeArgs a{};
+    for (int r = 0; r < x->world; ++r) a.peer[r] = x->peer[r];
+    a.g = x->world; a.rank = x->rank; a.nq = (int)nq; a.k = k; a.epoch = x->epoch;
+    a.slot_bytes = x->slot_bytes; a.flags_off = x->flags_off; a.nq_max = x->nq_max;
+    a.off_i = (int)round_up16(nq * k * 4);
+    a.d_loc = d_loc; a.i_loc = i_loc; a.out_d = out_d; a.out_i = out_i;
+    const int n = next_pow2(x->world * k);
+    const size_t smem = (size_t)n * sizeof(uint64_t);
+    FIP_CUDA(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)std::max<size_t>(smem, 1024)));
+    const int threads = std::min(1024, std::max(64, n / 2));
+    exchange_merge_kernel<<<(unsigned)nq, threads, smem, (cudaStream_t)cuda_stream>>>(a);
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+
+void fip_exchange_destroy(fip_exchange* x) {
+    if (!x) return;
+    cudaSetDevice(x->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < x->world; ++r)
+        if (x->ipc_opened[r] && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
+    if (x->local) cudaFree(x->local);
+    cudaGetLastError();
+    delete x;
 }
 
 int fip_set_option(fip_index* idx, const char* key, int64_t value) {

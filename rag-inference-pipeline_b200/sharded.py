@@ -54,7 +54,15 @@ class ShardedFlatIPSearcher:
     """One instance per rank.  ``search_tensor`` is the device-resident hot path."""
 
     def __init__(self, dim: int, dtype: str, total_rows: int, *, rank: int = 0,
-                 world_size: int = 1, device: int = 0, group=None):
+                 world_size: int = 1, device: int = 0, group=None, exchange: str = "auto"):
+        """exchange: how the per-shard results meet.  "p2p" = the fused exchange + merge kernel
+        over NVLink peer memory (K4), "nccl" = one packed all-gather + the K3 merge kernel,
+        "auto" = p2p when the peers' buffers can be mapped (CUDA IPC), else nccl."""
+        if exchange not in ("auto", "p2p", "nccl"):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        self.exchange_mode = exchange
+        self._xchg = None
+        self.exchange_used = "none"
         self.dim = int(dim)
         self.dtype = dtype
         self.total_rows = int(total_rows)
@@ -101,6 +109,16 @@ class ShardedFlatIPSearcher:
                                  stream)
         if self.world_size == 1:
             return d_loc, i_loc
+        xchg = self._ensure_exchange(B, k)
+        if xchg is not None:
+            d_out = torch.empty((B, k), dtype=torch.float32, device=queries.device)
+            i_out = torch.empty((B, k), dtype=torch.int64, device=queries.device)
+            xchg.merge(d_loc.data_ptr(), i_loc.data_ptr(), B, k, d_out.data_ptr(), i_out.data_ptr(),
+                       stream)
+            pack.record_stream(torch.cuda.current_stream(queries.device))
+            self.exchange_used = "p2p"
+            return d_out, i_out
+        self.exchange_used = "nccl"
 
         def all_gather(t):
             import torch.distributed as dist
@@ -121,6 +139,60 @@ class ShardedFlatIPSearcher:
         return gather_and_merge(pack, B, k, world_size=self.world_size, all_gather=all_gather,
                                 merge=merge)
 
+    # ------------------------------------------------------------------ peer-memory exchange
+    def _ensure_exchange(self, nq: int, k: int):
+        """Collective: (re)creates the K4 exchange when this search does not fit the current one.
+        Every rank sees the same (nq, k), so every rank takes the same branch."""
+        if self.exchange_mode == "nccl":
+            return None
+        if self._xchg is not None and self._xchg.fits(nq, k):
+            return self._xchg
+        if self._xchg is False:          # an earlier attempt failed on some rank: stay on NCCL
+            return None
+        import torch
+        import torch.distributed as dist
+
+        from .exchange import PeerExchange
+
+        if self._xchg is not None:
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)   # nobody still writes into the old buffers
+            self._xchg.close()
+            self._xchg = None
+        nq_max = max(1024, 1 << (int(nq) - 1).bit_length())
+        k_max = max(128, 1 << (int(k) - 1).bit_length())
+        k_max = min(k_max, 16384 // self.world_size)
+        # Every rank walks the same collective sequence (all_gather_object, all_reduce) whether or
+        # not its own steps succeed, so a failure on one rank cannot strand the others.
+        x, err, handle = None, "", b""
+        try:
+            if k > k_max:
+                raise ValueError("world_size * k exceeds the merge capacity")
+            x = PeerExchange(self.device, self.world_size, self.rank, nq_max, k_max)
+            handle = x.ipc_handle()
+        except Exception as e:  # noqa: BLE001 - any failure means "no peer mapping on this box"
+            err = f"{type(e).__name__}: {e}"
+        handles = [None] * self.world_size
+        dist.all_gather_object(handles, handle, group=self.group)
+        if not err:
+            try:
+                if any(not h for h in handles):
+                    raise RuntimeError("a peer could not allocate its exchange buffer")
+                x.connect_ipc(handles)
+            except Exception as e:  # noqa: BLE001
+                err = f"{type(e).__name__}: {e}"
+        ok = torch.tensor([0 if err else 1], dtype=torch.int32, device=torch.device("cuda", self.device))
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 0:
+            if x is not None:
+                x.close()
+            self._xchg = False
+            if self.exchange_mode == "p2p":
+                raise RuntimeError(f"peer-memory exchange unavailable on rank {self.rank}: {err or 'a peer failed'}")
+            return None
+        self._xchg = x
+        return x
+
     # ------------------------------------------------------------------ host-buffer path
     def search(self, queries: np.ndarray, k: int):
         """numpy in, numpy out (H2D / D2H inside), same contract as FAISSStore.search."""
@@ -132,4 +204,13 @@ class ShardedFlatIPSearcher:
         return d.cpu().numpy(), i.cpu().numpy()
 
     def close(self) -> None:
+        if self._xchg:
+            import torch
+            import torch.distributed as dist
+
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)   # peers may still be reading / writing our buffer
+            self._xchg.close()
+        self._xchg = None
         self.index.close()

@@ -382,6 +382,46 @@ def test_merge_kernel_matches_oracle():
     assert np.array_equal(oi.cpu().numpy(), Ir)
 
 
+def test_fused_exchange_merge_kernel_in_process():
+    """K4 with all ranks inside this process (several exchanges on one device, one stream each):
+    every rank must end up with the oracle's merge of all ranks' lists, over several epochs with
+    changing (nq, k) so that both buffer parities and layout changes are exercised."""
+    import torch
+    from rag_inference_pipeline_b200.exchange import PeerExchange
+
+    g = 4
+    group = [PeerExchange(0, g, r, 64, 128) for r in range(g)]
+    PeerExchange.connect_local(group)
+    streams = [torch.cuda.Stream() for _ in range(g)]
+    rng = np.random.default_rng(5)
+    for nq, k in [(37, 100), (64, 128), (1, 1), (5, 33), (37, 100)]:
+        d = np.sort(rng.standard_normal((g, nq, k)).astype(np.float32), axis=2)[:, :, ::-1].copy()
+        if k > 60:
+            d[:, :, 40:60] = d[:, :, 40:41]
+            d[3] = d[2]
+        ids = (np.sort(rng.integers(0, 1000, (g, nq, k)), axis=2) + (np.arange(g) * 1000)[:, None, None]).astype(np.int64)
+        if k > 10:
+            ids[1, :, k - 5:] = -1
+            d[1, :, k - 5:] = np.finfo(np.float32).min
+        Dr, Ir = flatip_oracle.merge_sorted_lists(d, ids, k)
+        td = [torch.from_numpy(d[r]).cuda() for r in range(g)]
+        ti = [torch.from_numpy(ids[r]).cuda() for r in range(g)]
+        od = [torch.empty((nq, k), dtype=torch.float32, device="cuda") for _ in range(g)]
+        oi = [torch.empty((nq, k), dtype=torch.int64, device="cuda") for _ in range(g)]
+        torch.cuda.synchronize()
+        for r in range(g):   # rank r's kernel spins until the other ranks' kernels have published
+            group[r].merge(td[r].data_ptr(), ti[r].data_ptr(), nq, k, od[r].data_ptr(), oi[r].data_ptr(),
+                           streams[r].cuda_stream)
+        torch.cuda.synchronize()
+        for r in range(g):
+            assert np.array_equal(od[r].cpu().numpy(), Dr), (r, nq, k)
+            assert np.array_equal(oi[r].cpu().numpy(), Ir), (r, nq, k)
+    with pytest.raises(Exception):
+        group[0].merge(td[0].data_ptr(), ti[0].data_ptr(), 65, 10, od[0].data_ptr(), oi[0].data_ptr(), 0)
+    for x in group:
+        x.close()
+
+
 def test_packed_exchange_buffer_merge():
     """The packed [distances | pad | ids] per-rank buffer of sharded.py, gathered as [g, total]
     bytes, merged by the strided K3 entry point == the oracle merge."""
