@@ -133,7 +133,9 @@ void fip_exchange_destroy(fip_exchange* x);
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
  * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),
- * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant), "profile_events" (0/1: time every scan launch with CUDA events),
+ * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant),
+ * "coalesce" (1 default / 0) and "coalesce_max_batch" (default 4096): fip_search calls that arrive
+ * from other threads while a search is running are queued and served together as ONE batch, "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback). */
 int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
@@ -142,7 +144,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value);
  * on the exact streaming kernel), "query_split_used",
  * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_ns_<i>" / "scan_rows_<i>" / "gap_ns_<i>" (per scan launch i: device time, corpus rows, time to the
  * next scan), "scan_time_ns" / "scan_launches" (device time and count of the scan
- * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches". */
+ * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches",
+ * "host_calls" / "host_batches" (fip_search calls and the batches they were served in),
+ * "coalesced_calls" (calls that shared a batch with another call); "last_batch_calls". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);
 
 const char* fip_last_error(void);

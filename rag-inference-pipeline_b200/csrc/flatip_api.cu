@@ -13,6 +13,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <vector>
 
@@ -163,6 +165,22 @@ struct fip_index {
     int64_t n_rows = 0;
     int64_t cap_rows = 0;
     std::mutex mu;
+
+    // Request coalescing (fip_search): host callers that arrive while a search is running are
+    // queued; whoever finds no leader becomes one, takes every queued request with the same k (up
+    // to coalesce_max queries) and runs them as ONE batch.  Below ~210 queries a flat scan is
+    // HBM-bound -- its cost does not depend on the batch size -- so riding along is free.
+    struct Pending {
+        const float* q; int64_t nq; int k; float* d; int64_t* i;
+        int rc = 0; bool done = false; std::string err;
+    };
+    std::mutex qmu;
+    std::condition_variable qcv;
+    std::deque<Pending*> pending;
+    bool leader_active = false;
+    int coalesce = 1;
+    int64_t coalesce_max = 4096;
+    int64_t st_batches = 0, st_calls = 0, st_coalesced_calls = 0, st_last_batch_calls = 0;
 
     // options
     int variant = FIP_VARIANT_AUTO;
@@ -918,31 +936,91 @@ int64_t fip_ntotal(const fip_index* idx) { return idx ? idx->n_rows : 0; }
 int32_t fip_dim(const fip_index* idx) { return idx ? idx->cfg.dim : 0; }
 int32_t fip_dtype_of(const fip_index* idx) { return idx ? idx->cfg.dtype : -1; }
 
-int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, float* distances,
-               int64_t* ids) {
-    int rc = check_search_args(idx, queries, nq, k, distances, ids);
-    if (rc) return rc;
-    if (nq == 0) return FIP_OK;
+// One host-buffer search over the concatenation of `batch` (all with the same k): pinned staging,
+// H2D, search, D2H, scatter back to every caller's buffers.
+static int run_host_batch(fip_index* idx, const std::vector<fip_index::Pending*>& batch) {
     std::lock_guard<std::mutex> lock(idx->mu);
-    rc = use_device(idx);
+    int rc = use_device(idx);
     if (rc) return rc;
-    const size_t qn = (size_t)nq * idx->cfg.dim, on = (size_t)nq * k;
+    const int k = batch[0]->k;
+    int64_t nq = 0;
+    for (auto* b : batch) nq += b->nq;
+    const size_t dim = (size_t)idx->cfg.dim;
+    const size_t qn = (size_t)nq * dim, on = (size_t)nq * k;
     FIP_CUDA(idx->h_q.ensure(qn));
     FIP_CUDA(idx->h_d.ensure(on));
     FIP_CUDA(idx->h_i.ensure(on));
     FIP_CUDA(idx->q32.ensure(qn));
     FIP_CUDA(idx->out_d.ensure(on));
     FIP_CUDA(idx->out_i.ensure(on));
-    memcpy(idx->h_q.p, queries, qn * sizeof(float));
+    size_t off = 0;
+    for (auto* b : batch) {
+        memcpy(idx->h_q.p + off * dim, b->q, (size_t)b->nq * dim * sizeof(float));
+        off += (size_t)b->nq;
+    }
     FIP_CUDA(cudaMemcpyAsync(idx->q32.p, idx->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, idx->stream));
     rc = search_checked(idx, idx->q32.p, (int)nq, k, idx->out_d.p, idx->out_i.p, idx->stream);
     if (rc) return rc;
     FIP_CUDA(cudaMemcpyAsync(idx->h_d.p, idx->out_d.p, on * sizeof(float), cudaMemcpyDeviceToHost, idx->stream));
     FIP_CUDA(cudaMemcpyAsync(idx->h_i.p, idx->out_i.p, on * sizeof(int64_t), cudaMemcpyDeviceToHost, idx->stream));
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
-    memcpy(distances, idx->h_d.p, on * sizeof(float));
-    memcpy(ids, idx->h_i.p, on * sizeof(int64_t));
+    off = 0;
+    for (auto* b : batch) {
+        memcpy(b->d, idx->h_d.p + off * k, (size_t)b->nq * k * sizeof(float));
+        memcpy(b->i, idx->h_i.p + off * k, (size_t)b->nq * k * sizeof(int64_t));
+        off += (size_t)b->nq;
+    }
+    idx->st_batches++;
+    idx->st_calls += (int64_t)batch.size();
+    idx->st_last_batch_calls = (int64_t)batch.size();
+    if (batch.size() > 1) idx->st_coalesced_calls += (int64_t)batch.size();
     return FIP_OK;
+}
+
+int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, float* distances,
+               int64_t* ids) {
+    int rc = check_search_args(idx, queries, nq, k, distances, ids);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    fip_index::Pending me{queries, nq, k, distances, ids};
+    if (!idx->coalesce) {
+        std::vector<fip_index::Pending*> one{&me};
+        return run_host_batch(idx, one);
+    }
+    std::unique_lock<std::mutex> lk(idx->qmu);
+    idx->pending.push_back(&me);
+    while (!me.done) {
+        if (idx->leader_active) {
+            idx->qcv.wait(lk);
+            continue;
+        }
+        // become the leader for one batch: the oldest request sets k; every queued request with
+        // that k rides along, in arrival order, while the batch stays within coalesce_max queries
+        idx->leader_active = true;
+        std::vector<fip_index::Pending*> batch;
+        const int bk = idx->pending.front()->k;
+        int64_t total = 0;
+        for (auto it = idx->pending.begin(); it != idx->pending.end();) {
+            fip_index::Pending* p = *it;
+            if (p->k == bk && (batch.empty() || total + p->nq <= idx->coalesce_max)) {
+                batch.push_back(p);
+                total += p->nq;
+                it = idx->pending.erase(it);
+            } else {
+                ++it;
+            }
+        }
+        lk.unlock();
+        const int brc = run_host_batch(idx, batch);
+        const std::string berr = brc ? g_last_error : std::string();
+        lk.lock();
+        for (auto* p : batch) { p->rc = brc; p->err = berr; p->done = true; }
+        idx->leader_active = false;
+        idx->qcv.notify_all();
+    }
+    lk.unlock();
+    if (me.rc) g_last_error = me.err;
+    return me.rc;
 }
 
 int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
@@ -1127,6 +1205,11 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
     } else if (k == "cta_pair") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "cta_pair must be 0 (auto), 1 or 2");
         idx->cta_pair = (int)value;
+    } else if (k == "coalesce") {
+        idx->coalesce = value != 0;
+    } else if (k == "coalesce_max_batch") {
+        if (value < 1) return fail(FIP_ERR_INVALID, "coalesce_max_batch must be >= 1");
+        idx->coalesce_max = value;
     } else if (k == "certify") {
         idx->certify = value != 0;
     } else if (k == "profile_events") {
@@ -1163,6 +1246,10 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
         const size_t i = (size_t)atoi(k.c_str() + (gap ? 7 : 8));
         return i < v.size() ? (int64_t)(v[i] * 1e6) : -1;
     }
+    if (k == "host_batches") return idx->st_batches;
+    if (k == "host_calls") return idx->st_calls;
+    if (k == "coalesced_calls") return idx->st_coalesced_calls;
+    if (k == "last_batch_calls") return idx->st_last_batch_calls;
     if (k == "total_launches") return idx->st_total_launches;
     if (k == "total_searches") return idx->st_total_searches;
     return -1;

@@ -147,6 +147,43 @@ class B200FlatIPStore:
         else:
             return distances, indices
 
+    def search_device(self, embeddings, k: int):
+        """Embedding hand-off fast path: a co-located embedder passes its output as a
+        torch CUDA tensor ``[batch, dim]`` on this store's device (any float dtype) and gets torch
+        CUDA tensors back -- no ``list[float]`` -> ``np.array`` -> ``astype`` copies
+        (``/root/reference/src/pipeline/services/retrieval/api.py:69-84``, ``faiss_store.py:147``)
+        and no host round trip.  Same validation, errors and (distances, indices) contract as
+        ``search``; the call is ordered on the tensor's current stream and blocks until done."""
+        import torch
+
+        if not self._is_loaded or self._index is None:
+            msg = "FAISS index not loaded. Call load() first."
+            raise RuntimeError(msg)
+        if embeddings.dim() != 2:
+            msg = f"Embeddings must be 2D array, got shape {tuple(embeddings.shape)}"
+            raise ValueError(msg)
+        if embeddings.shape[1] != self.settings.faiss_dim:
+            msg = (
+                f"Embedding dimension mismatch: expected {self.settings.faiss_dim}, "
+                f"got {embeddings.shape[1]}"
+            )
+            raise ValueError(msg)
+        if not embeddings.is_cuda or embeddings.device.index != self.device:
+            msg = f"search_device needs a CUDA tensor on device {self.device}"
+            raise ValueError(msg)
+        q = embeddings.to(torch.float32).contiguous()
+        batch = q.shape[0]
+        distances = torch.empty((batch, int(k)), dtype=torch.float32, device=q.device)
+        indices = torch.empty((batch, int(k)), dtype=torch.int64, device=q.device)
+        try:
+            self._index.search_device(q.data_ptr(), batch, int(k), distances.data_ptr(),
+                                      indices.data_ptr(),
+                                      torch.cuda.current_stream(q.device).cuda_stream)
+        except Exception:
+            logger.exception("FAISS search failed")
+            raise
+        return distances, indices
+
     # ----------------------------------------------------------------------------- teardown
     def unload(self) -> None:
         if self._is_loaded:

@@ -422,6 +422,45 @@ def test_fused_exchange_merge_kernel_in_process():
         x.close()
 
 
+def test_concurrent_callers_are_coalesced_into_one_batch():
+    """The retrieval service calls search() from a thread pool with several batches in flight
+    (/root/reference/src/pipeline/services/retrieval/api.py:348-349).  Calls that arrive while a
+    search is running are served together; every caller still gets exactly its own rows."""
+    import threading
+
+    dim, n, k, nthreads, rounds, nq = 256, 3_000_000, 10, 8, 12, 8
+    idx = _index(dim, "f16")
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    qs = [synthetic.synthetic_queries(nq, dim, seed=100 + t) for t in range(nthreads)]
+    idx.set_option("coalesce", 0)
+    serial = [idx.search(q, k) for q in qs]
+    assert idx.stat("coalesced_calls") == 0
+    idx.set_option("coalesce", 1)
+    errors = []
+    start = threading.Barrier(nthreads)
+
+    def worker(t):
+        try:
+            start.wait()
+            for _ in range(rounds):
+                kk = k if t % 4 else k + 3          # one caller in four asks for a different k
+                D, I = idx.search(qs[t], kk)
+                assert np.array_equal(I[:, :k], serial[t][1]) and np.array_equal(D[:, :k], serial[t][0])
+        except Exception as e:  # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(nthreads)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    calls, batches = idx.stat("host_calls"), idx.stat("host_batches")
+    assert calls == nthreads + nthreads * rounds
+    assert idx.stat("coalesced_calls") > 0 and batches < calls, (calls, batches)
+    idx.close()
+
+
 def test_packed_exchange_buffer_merge():
     """The packed [distances | pad | ids] per-rank buffer of sharded.py, gathered as [g, total]
     bytes, merged by the strided K3 entry point == the oracle merge."""
@@ -526,7 +565,21 @@ def test_store_dropin_on_gpu(tmp_path):
     D2, I2 = st2.search(q, k)
     Dr2, Ir2 = flatip_oracle.flat_ip_search(q, synthetic.synthetic_corpus(0, n, dim, "f16"), k)
     _check(D2, I2, Dr2, Ir2, "f16")
+    # embedding hand-off fast path: torch CUDA tensor in (fp16, as an embedder would emit),
+    # torch CUDA tensors out, same answer as the host path on the same (rounded) queries
+    import torch
+    q16 = torch.from_numpy(q).cuda().half()
+    D3, I3 = st2.search_device(q16, k)
+    assert D3.is_cuda and I3.dtype == torch.int64 and tuple(D3.shape) == (32, k)
+    D4, I4 = st2.search(q16.float().cpu().numpy(), k)
+    assert np.array_equal(I3.cpu().numpy(), I4) and np.array_equal(D3.cpu().numpy(), D4)
+    with pytest.raises(ValueError, match="Embedding dimension mismatch"):
+        st2.search_device(torch.zeros((2, dim + 8), device="cuda"), k)
+    with pytest.raises(ValueError, match="CUDA tensor"):
+        st2.search_device(torch.zeros((2, dim)), k)
     st2.unload()
+    with pytest.raises(RuntimeError, match="not loaded"):
+        st2.search_device(q16, k)
 
 
 def test_large_scale_properties():
