@@ -134,6 +134,8 @@ void fip_exchange_destroy(fip_exchange* x);
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
  * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),
  * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant),
+ * "live_thresholds" (1 default: a filter launch raises its own per-query thresholds from a score
+ * histogram, so one launch covers the shard; 0: thresholds move only between geometric phases),
  * "coalesce" (1 default / 0) and "coalesce_max_batch" (default 4096): fip_search calls that arrive
  * from other threads while a search is running are queued and served together as ONE batch, "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback). */

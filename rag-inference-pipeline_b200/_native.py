@@ -13,7 +13,8 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_NAME = "libflatip_b200.so"
-LIB_PATH = os.path.join(_HERE, LIB_NAME)
+# FLATIP_B200_LIBRARY: developer override (A/B builds of the kernels)
+LIB_PATH = os.environ.get("FLATIP_B200_LIBRARY") or os.path.join(_HERE, LIB_NAME)
 
 FIP_F32, FIP_F16, FIP_BF16 = 0, 1, 2
 DTYPE_CODES = {"f32": FIP_F32, "f16": FIP_F16, "bf16": FIP_BF16,

@@ -88,17 +88,95 @@ struct ScanArgs {
     uint32_t row_begin;        // phase row range [row_begin, row_end)
     uint32_t row_end;
     int dense;                 // 1: phase 0, every score is written at slot = row - row_begin
-    const float* thr;          // [nq] running k-th best score per query (strict > passes)
+    float* thr;                // [nq] running threshold per query (strict > passes); raised live
     uint32_t* cnt;             // [nq] candidates currently in each list
     uint64_t* cand;            // [nq, cap] candidate keys
     uint32_t cap;
+    // Live thresholds (null hist = off).  Every candidate in a list is also counted in
+    // hist[q][bucket], bucket = min(255, (orderable(score) - hbase[q]) >> 16), hbase[q] = the
+    // orderable bits of the threshold the select pass published.  Whenever a list grows past a
+    // multiple of kRefreshEvery entries the appending warp walks the histogram from the top: if
+    // k_thr candidates sit in buckets >= b, the k_thr-th best score so far is >= the lower edge of
+    // bucket b, so everything below that edge (minus the exactness window 2 eps / scale of the
+    // tensor-core filter) can be dropped from now on.  Counts only grow and thresholds are only
+    // raised, so a stale read of either is merely conservative.  This is what lets ONE filter
+    // launch cover the whole shard: survivors grow like k log(N / m0) instead of k N / m0.
+    uint32_t* hist;            // [nq, 256]
+    const uint32_t* hbase;     // [nq]
+    const float* win_eps;      // [nq] or null (exact scores)
+    const float* win_scale;    // [nq] or null
+    int k_thr;
 };
+constexpr uint32_t kRefreshEvery = 128;   // list entries between two threshold refreshes
+constexpr int kHistBins = 256;
+constexpr int kHistShift = 16;            // 2^16 ulps per bucket = 2^-7 relative score resolution
 
-// Append one candidate (common tail of every scan kernel's epilogue).
-__device__ __forceinline__ void append_candidate(const ScanArgs& a, int q, float score,
+__device__ __forceinline__ uint32_t hist_bucket(uint32_t score_bits, uint32_t hbase) {
+    const uint32_t o = (score_bits & 0x80000000u) ? ~score_bits : (score_bits | 0x80000000u);
+    const uint32_t d = (o - hbase) >> kHistShift;   // o > hbase for every candidate (score > threshold)
+    return d < (uint32_t)(kHistBins - 1) ? d : (uint32_t)(kHistBins - 1);
+}
+// Monotone raise of a float in global memory (works across signs: positive floats order like
+// signed ints, negative floats inversely like unsigned ints).
+__device__ __forceinline__ void raise_threshold(float* addr, float v) {
+    if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+// New threshold implied by "at least k_thr candidates in buckets >= b" (b >= 1).
+__device__ __forceinline__ float threshold_from_bucket(const ScanArgs& a, int q, uint32_t b) {
+    const uint32_t base = a.hbase[q];
+    const uint32_t add = b << kHistShift;
+    uint32_t edge = base + add;
+    if (edge < base) edge = 0xFFFFFFFFu;          // saturate
+    // edge - 1: a score EQUAL to the bucket edge still passes the strict compare (ties are broken
+    // by id, and rows scanned concurrently may carry lower ids than the counted candidates)
+    float t = from_orderable_f32(edge - 1u);
+    if (a.win_eps) t -= 2.0f * a.win_eps[q] / a.win_scale[q];
+    return t;
+}
+// Whole-warp refresh for every lane with `need` set (all 32 lanes must call this converged).
+__device__ __forceinline__ void refresh_thresholds_warp(const ScanArgs& a, bool need, int q, int lane) {
+    uint32_t trig = __ballot_sync(0xFFFFFFFFu, need);
+    while (trig) {
+        const int src = __ffs((int)trig) - 1;
+        trig &= trig - 1u;
+        const int qq = __shfl_sync(0xFFFFFFFFu, q, src);
+        const uint4* h = reinterpret_cast<const uint4*>(a.hist + (size_t)qq * kHistBins + lane * 8);
+        const uint4 h0 = __ldcg(h), h1 = __ldcg(h + 1);
+        const uint32_t c[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        uint32_t sum = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum += c[j];
+        uint32_t suf = sum;  // inclusive suffix sum over lanes (lane 31 holds the top buckets)
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_down_sync(0xFFFFFFFFu, suf, off);
+            if (lane + off < 32) suf += t;
+        }
+        const uint32_t k = (uint32_t)a.k_thr;
+        if (suf >= k && suf - sum < k) {
+            uint32_t above = suf - sum;
+            int b = lane * 8;
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {
+                if (above + c[j] >= k) { b = lane * 8 + j; break; }
+                above += c[j];
+            }
+            if (b > 0) raise_threshold(a.thr + qq, threshold_from_bucket(a, qq, (uint32_t)b));
+        }
+    }
+}
+// Append one candidate (tail of the streaming kernel's epilogue).  Returns true when the list just
+// grew past a multiple of kRefreshEvery entries: the caller then refreshes the query's threshold
+// (refresh_thresholds_warp, once the warp has reconverged).
+__device__ __forceinline__ bool append_candidate(const ScanArgs& a, int q, float score,
                                                  uint32_t row) {
     uint32_t slot = atomicAdd(a.cnt + q, 1u);
-    if (slot < a.cap) a.cand[(size_t)q * a.cap + slot] = make_raw_key(score, row);
+    if (slot >= a.cap) return false;
+    a.cand[(size_t)q * a.cap + slot] = make_raw_key(score, row);
+    if (!a.hist) return false;
+    atomicAdd(a.hist + (size_t)q * kHistBins + hist_bucket(__float_as_uint(score), a.hbase[q]), 1u);
+    return ((slot + 1u) & (kRefreshEvery - 1u)) == 0u;
 }
 
 inline int next_pow2(int v) {

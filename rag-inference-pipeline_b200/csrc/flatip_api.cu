@@ -201,6 +201,8 @@ struct fip_index {
     DevBuf<float> thr, q_scale, q_eps, q32, out_d;
     DevBuf<float> max_norm2;  // [1] max squared row norm of the shard (certificate radius)
     int certify = 1;          // 0: skip the exactness certificate of the tensor-core variant
+    int live_thr = 1;         // 0: thresholds only move between scan launches (geometric phases)
+    DevBuf<uint32_t> hist, hbase;   // live thresholds: [nq, 256] score histogram, [nq] bucket origin
     DevBuf<uint32_t> cnt, overflow;
     DevBuf<uint64_t> cand;
     DevBuf<uint8_t> qprep;  // prepared query terms in the MMA operand type
@@ -249,16 +251,36 @@ int reserve_rows(fip_index* idx, int64_t want) {
     return FIP_OK;
 }
 
-double phase_growth(int cap, int k_plan) {
-    const int keff = std::max(k_plan, 16);
-    return std::max(2.0, ((double)cap / 2 - keff) / keff);
+// How many times the scanned row count may grow in ONE filter launch so that a query's candidate
+// list is expected to stay within its capacity.
+//   fixed thresholds (live = false): a launch over m rows after n rows leaves ~k m / n survivors,
+//     so growth is limited to (cap/2 - k) / k  (lists half full on average data);
+//   live thresholds: the launch raises its own thresholds (common.cuh), survivors grow like
+//     k log(ratio).  A refresh happens every kRefreshEvery appended entries, i.e. with
+//     x = kRefreshEvery / k the threshold lags by a factor (1 + x) in rows: x / log(1 + x) more
+//     survivors than ideal, plus ~20 % for the bucket resolution; the expected list is kept below
+//     3/4 of the capacity.
+// Overflow means "redo in safe mode", so these are performance bounds, not correctness ones.
+double phase_ratio(int cap, int k_plan, int keep_max, bool live) {
+    const double keff = std::max(k_plan, 16);
+    const double fixed = 1.0 + std::max(2.0, ((double)cap / 2 - keff) / keff);
+    if (!live) return fixed;
+    const double x = (double)kRefreshEvery / keff;
+    const double lag = 1.2 * x / std::log1p(x);
+    const double budget = 0.75 * cap - std::max(k_plan, keep_max) - (double)kRefreshEvery;
+    return std::max(fixed, std::exp(std::min(40.0, std::max(0.0, budget) / (lag * keff))));
 }
-int count_phases(int64_t n, int cap, int k_plan) {
-    const double growth = phase_growth(cap, k_plan);
+int keep_max_for(int cap, int k_out, int k_plan, bool certify) {
+    return certify ? std::min(cap / 2, k_out + 2 * (k_plan - k_out)) : 0;
+}
+int64_t phase_rows(int64_t pos, double ratio) {
+    return std::max<int64_t>(256, (int64_t)std::min((double)pos * (ratio - 1.0), 4.0e9) / 256 * 256);
+}
+int count_phases(int64_t n, int cap, double ratio) {
     int64_t pos = std::min<int64_t>(n, cap);
     int phases = 1;
     while (pos < n) {
-        pos += std::max<int64_t>(256, (int64_t)((double)pos * growth) / 256 * 256);
+        pos += phase_rows(pos, ratio);
         phases++;
     }
     return phases;
@@ -266,16 +288,15 @@ int count_phases(int64_t n, int cap, int k_plan) {
 // Candidate-list capacity per query.  The floor (4096, or 32 x k for large k) keeps the lists of a
 // big batch small; every phase boundary costs a select pass and a scan launch (~50 us), so a small
 // batch -- whose lists are cheap and whose select passes fit one wave of CTAs -- takes a larger
-// capacity when that saves a phase (3 instead of 4 phases for shards between 1.1 M and 70 M rows
-// at k = 100).
-int cap_for_k(int k, bool safe, int nq, int64_t n) {
+// capacity when that saves a phase.
+int cap_for_k(int k_out, int k_plan, bool certify, bool live, bool safe, int nq, int64_t n) {
     if (safe) return kMaxCap;
-    int cap = std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
-    int best_phases = count_phases(n, cap, k);
+    int cap = std::min(std::max(4096, 32 * next_pow2(k_plan)), kMaxCap);
+    int best = count_phases(n, cap, phase_ratio(cap, k_plan, keep_max_for(cap, k_out, k_plan, certify), live));
     for (int c = cap * 2; c <= kMaxCap; c *= 2) {
         if ((int64_t)nq * c > (int64_t)148 * kMaxCap) break;
-        const int ph = count_phases(n, c, k);
-        if (ph < best_phases) { best_phases = ph; cap = c; }
+        const int ph = count_phases(n, c, phase_ratio(c, k_plan, keep_max_for(c, k_out, k_plan, certify), live));
+        if (ph < best) { best = ph; cap = c; }
     }
     return cap;
 }
@@ -395,7 +416,8 @@ struct SearchInfo {
 
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
                   int64_t* out_i, const float* out_scale, int64_t dense_count = -1,
-                  int keep_max = 0 /* > 0: exactness window on (tensor-core variant) */) {
+                  int keep_max = 0 /* > 0: exactness window on (tensor-core variant) */,
+                  bool live = false /* seed the live-threshold histogram */) {
     SelectArgs s{};
     s.cand = idx->cand.p; s.cnt = idx->cnt.p; s.thr = idx->thr.p; s.cap = (uint32_t)cap; s.k = k;
     s.final_pass = final_pass ? 1 : 0; s.out_d = out_d; s.out_i = out_i; s.id_base = idx->cfg.id_base;
@@ -404,6 +426,7 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
         s.win_eps = idx->q_eps.p; s.win_scale = idx->q_scale.p; s.keep_max = keep_max;
         s.uncert = idx->overflow.p + (nq + 1);
     }
+    if (live && !final_pass) { s.hist = idx->hist.p; s.hbase = idx->hbase.p; }
     size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
@@ -472,8 +495,9 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     const int k_plan = !rescore ? k
                        : (dtype == kBF16 && split == 1) ? k + std::max(48, 3 * k / 4)
                                                         : k + std::max(16, k / 4);
-    const int cap = cap_for_k(k_plan, mode.safe, nq, n);
-    const int keep_max = certify ? std::min(cap / 2, k_out + 2 * (k_plan - k_out)) : 0;
+    const bool live = idx->live_thr && !mode.safe;
+    const int cap = cap_for_k(k_out, k_plan, certify, live, mode.safe, nq, n);
+    const int keep_max = keep_max_for(cap, k_out, k_plan, certify);
     const int k_sel = certify ? k_out : k_plan;   // what the intermediate selects look for
     FIP_CUDA(idx->thr.ensure(nq));
     FIP_CUDA(idx->cnt.ensure(nq));
@@ -558,7 +582,13 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         return FIP_OK;
     };
 
-    const double growth = phase_growth(cap, k_plan);
+    const double ratio = phase_ratio(cap, k_plan, keep_max, live);
+    if (live) {
+        FIP_CUDA(idx->hist.ensure((size_t)nq * kHistBins));
+        FIP_CUDA(idx->hbase.ensure(nq));
+        a.hist = idx->hist.p; a.hbase = idx->hbase.p; a.k_thr = k_sel;
+        if (keep_max > 0) { a.win_eps = idx->q_eps.p; a.win_scale = idx->q_scale.p; }
+    }
     int phases = 0;
     // phase 0: no threshold yet, every score of the first rows is written (slot = row)
     int64_t m = std::min<int64_t>(n, cap);
@@ -566,17 +596,17 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (rc) return rc;
     int64_t pos = m;
     phases++;
-    rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, m, keep_max);
+    rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, m, keep_max, live);
     if (rc) return rc;
     while (pos < n) {
         if (mode.safe) m = std::max<int64_t>(256, (int64_t)(cap - std::max(k_plan, keep_max)) / 256 * 256);
-        else m = std::max<int64_t>(256, (int64_t)((double)pos * growth) / 256 * 256);
+        else m = phase_rows(pos, ratio);
         m = std::min<int64_t>(m, n - pos);
         rc = scan(pos, pos + m, false);
         if (rc) return rc;
         pos += m;
         phases++;
-        rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max);
+        rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max, live);
         if (rc) return rc;
     }
     if (rescore) {
@@ -777,7 +807,7 @@ void fip_destroy(fip_index* idx) {
     if (idx->stream) cudaStreamSynchronize(idx->stream);
     if (idx->corpus) cudaFree(idx->corpus);
     idx->thr.release(); idx->q_scale.release(); idx->q_eps.release(); idx->max_norm2.release(); idx->q32.release(); idx->out_d.release();
-    idx->cnt.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
+    idx->cnt.release(); idx->hist.release(); idx->hbase.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
     idx->h_flags.release(); idx->add_stage.release();
@@ -1210,6 +1240,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
     } else if (k == "coalesce_max_batch") {
         if (value < 1) return fail(FIP_ERR_INVALID, "coalesce_max_batch must be >= 1");
         idx->coalesce_max = value;
+    } else if (k == "live_thresholds") {
+        idx->live_thr = value != 0;
     } else if (k == "certify") {
         idx->certify = value != 0;
     } else if (k == "profile_events") {

@@ -57,6 +57,10 @@ struct SelectArgs {
     const float* win_scale;   // [nq] approx-score scale (out_scale of the scan)
     int keep_max;             // truncation limit for the window (<= cap)
     uint32_t* uncert;         // [1 + nq] like `overflow`
+    // Live thresholds (common.cuh, ScanArgs::hist): an intermediate pass re-seeds the query's score
+    // histogram with the candidates it keeps and publishes the bucket origin.  Null = off.
+    uint32_t* hist;           // [nq, 256]
+    uint32_t* hbase;          // [nq]
 };
 
 constexpr int kSelectThreads = 256;
@@ -188,6 +192,7 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
                 }
             }
         }
+        uint64_t keep_from = lim + 1ull;   // every key >= keep_from stays in the list
         if ((int)c > a.k || kept == 0xFFFFFFFFu) {
             for (int i = tid; i < (int)c; i += kSelectThreads) {
                 const uint64_t x = s_keys[i];
@@ -206,7 +211,24 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
                 }
                 t = key_score(kth2);
                 kept = (uint32_t)a.keep_max;
+                keep_from = kth2;
             }
+        }
+        if (a.hist) {
+            __syncthreads();
+            s_hist[tid] = 0u;                 // kSelectThreads == kHistBins
+            __syncthreads();
+            const uint32_t hb = orderable_f32(t);
+            for (int i = tid; i < (int)c; i += kSelectThreads) {
+                const uint64_t x = s_keys[i];
+                if (x >= keep_from) {
+                    const uint32_t d = ((uint32_t)(x >> 32) - hb) >> kHistShift;
+                    atomicAdd(&s_hist[d < (uint32_t)(kHistBins - 1) ? d : (uint32_t)(kHistBins - 1)], 1u);
+                }
+            }
+            __syncthreads();
+            a.hist[(size_t)q * kHistBins + tid] = s_hist[tid];
+            if (tid == 0) a.hbase[q] = hb;
         }
         if (tid == 0) {
             a.cnt[q] = kept;

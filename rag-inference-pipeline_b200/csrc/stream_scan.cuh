@@ -154,7 +154,6 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0, int sl
     constexpr int PER = V >= 32 ? V / 32 : 1;
     constexpr int REP = V >= 32 ? 1 : 32 / V;
     extern __shared__ __align__(128) uint8_t s_raw[];
-    __shared__ float s_thr[QB];
 
     const int dim = a.dim;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -171,8 +170,6 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0, int sl
         int j = i / dim, c = i - j * dim;
         s_q[i] = (q0 + j < a.nq) ? queries[(size_t)(q0 + j) * dim + c] : 0.f;
     }
-    if (threadIdx.x < QB)
-        s_thr[threadIdx.x] = (q0 + (int)threadIdx.x < a.nq) ? a.thr[q0 + threadIdx.x] : 0.f;
     if (lane == 0)
         for (int s = 0; s < slots; ++s) ss_mbar_init(bar0 + 8u * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -204,6 +201,15 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0, int sl
         const int slot = (int)(i % slots);
         const uint32_t parity = (uint32_t)((i / slots) & 1);
         const uint32_t r0 = a.row_begin + (uint32_t)((gwarp + i * nwarps) * R);
+        // this lane's (row, query) pairs are fixed: fetch their thresholds now (L2: they are
+        // raised live by whoever appends candidates), the latency hides behind the block's FMAs
+        float thr_reg[PER];
+#pragma unroll
+        for (int t = 0; t < PER; ++t) {
+            const int flat = (V >= 32) ? lane * PER + t : lane / REP;
+            const int q = q0 + flat % QB;
+            thr_reg[t] = (q < a.nq && !a.dense) ? __ldcg(a.thr + q) : 0.f;
+        }
         ss_mbar_wait(bar0 + 8u * slot, parity);
         const uint32_t src = ring0 + (uint32_t)slot * blk;
 
@@ -245,6 +251,8 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0, int sl
         }
         warp_reduce_scatter<V>(acc, lane);
 
+        bool need = false;   // one of this lane's appends crossed a refresh boundary
+        int need_q = 0;
         if (lane % REP == 0) {
 #pragma unroll
             for (int t = 0; t < PER; ++t) {
@@ -256,12 +264,14 @@ stream_scan_kernel(ScanArgs a, const float* __restrict__ queries, int q0, int sl
                     const float s = acc[t];
                     if (a.dense) {
                         a.cand[(size_t)q * a.cap + (row - a.row_begin)] = make_raw_key(s, row);
-                    } else if (s > s_thr[j]) {
-                        append_candidate(a, q, s, row);
+                    } else if (s > thr_reg[t]) {
+                        if (append_candidate(a, q, s, row)) { need = true; need_q = q; }
                     }
                 }
             }
         }
+        __syncwarp();
+        if (a.hist) refresh_thresholds_warp(a, need, need_q, lane);
     }
 }
 

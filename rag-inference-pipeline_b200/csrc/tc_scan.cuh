@@ -18,9 +18,9 @@
 // CTA's TMEM.  Per tile and CTA the L2 -> smem traffic drops from A + B to A + B/2 and a stage
 // shrinks from 48 KB to 32 KB, so the ring is 6 deep instead of 4.
 //
-// Warp roles (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader
-// CTA only), warp 2 = TMEM allocator, warps 4..11 = epilogue (warp % 4 selects the TMEM
-// lane quarter, the two warps of a quarter split the 256 columns).  Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
+// Warp roles (640 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader
+// CTA only), warp 2 = TMEM allocator, warps 4..19 = epilogue (warp % 4 selects the TMEM
+// lane quarter, the four warps of a quarter split the 256 columns).  Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
 // (MMA <-> epilogue), persistent static tile schedule (corpus tile major, query tile minor, so the
 // query tiles of one corpus tile run back to back and re-read it from L2; HBM sees it once).
 #pragma once
@@ -42,7 +42,10 @@ constexpr int A_BYTES = BM * BK_BYTES;         // one query operand tile (per sp
 constexpr int B_BYTES = BN * BK_BYTES;         // full corpus tile
 constexpr int TMEM_COLS = 512;   // two 256-column fp32 accumulators
 constexpr int EPI_WARP0 = 4;
-constexpr int EPI_WARPS = 8;     // two warps per TMEM lane quarter, each takes half of the columns
+#ifndef FIP_EPI_WARPS
+#define FIP_EPI_WARPS 16   // 8 -> 16: the per-tile latency chain (TMEM reads, list reservation) halves; cfg5 2.43 -> 2.24 ms
+#endif
+constexpr int EPI_WARPS = FIP_EPI_WARPS;   // EPI_WARPS / 4 warps per TMEM lane quarter split the columns
 constexpr int NUM_THREADS = (EPI_WARP0 + EPI_WARPS) * 32;
 
 // kFmt: 0 = fp16, 1 = bf16 (kind::f16), 2 = fp32 storage read as tf32 (kind::tf32).
@@ -76,34 +79,38 @@ template <int kFmt, int kSplit, int kCtas> struct Cfg {
 constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int EPI_CHUNKS = BN / 32 / (EPI_WARPS / 4);        // chunks per epilogue warp and tile
 
+// The chunk loops are NOT unrolled: one copy of each pass keeps the kernel inside the instruction
+// cache (a fully unrolled version lost 2x on `no_inst` fetch stalls); the per-chunk masks live in
+// two 64-bit registers addressed with shifts.
 __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t taddr, int q, float thr,
-                                                uint32_t tile_row0, int c0) {
-    uint32_t masks[EPI_CHUNKS];
+                                                uint32_t hb, uint32_t tile_row0, int c0) {
+    static_assert(EPI_CHUNKS <= 4, "masks are packed into two 64-bit registers");
+    uint64_t m01 = 0ull, m23 = 0ull;   // masks of chunks 0,1 and 2,3
     uint32_t n = 0;
-#pragma unroll
+#pragma unroll 1
     for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
         const int c = c0 + ci;
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+        if (row_base >= a.row_end) break;  // warp-uniform
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (row_base + j >= a.row_end) v[j] = kNegInf;
+        }
         uint32_t mask = 0u;
-        if (row_base < a.row_end) {  // warp-uniform
-            float v[32];
-            tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
-            if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (row_base + j >= a.row_end) v[j] = kNegInf;
-            }
+        for (int g = 0; g < 4; ++g) {
+            float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
+            mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+            if (mx > thr) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
-                mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
-                if (mx > thr) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) mask_or_if_gt(mask, v[8 * g + j], thr, 1u << (8 * g + j));
-                }
+                for (int j = 0; j < 8; ++j) mask_or_if_gt(mask, v[8 * g + j], thr, 1u << (8 * g + j));
             }
         }
-        masks[ci] = mask;
+        const uint64_t shifted = (uint64_t)mask << (32 * (ci & 1));
+        if (ci & 2) m23 |= shifted; else m01 |= shifted;
         n += (uint32_t)__popc(mask);
     }
     // n != 0 implies an active query (inactive lanes carry thr = +inf).  A reservation that does
@@ -117,10 +124,12 @@ __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t tadd
     }
     if (!__any_sync(0xFFFFFFFFu, n != 0u)) return;
     uint64_t* list = a.cand + (size_t)q * a.cap + slot;
-#pragma unroll
+    uint32_t* hrow = a.hist ? a.hist + (size_t)q * kHistBins : nullptr;
+#pragma unroll 1
     for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
-        const uint32_t mask = fits ? masks[ci] : 0u;
-        if (!__any_sync(0xFFFFFFFFu, masks[ci] != 0u)) continue;  // warp-uniform
+        const uint32_t cmask = (uint32_t)(((ci & 2) ? m23 : m01) >> (32 * (ci & 1)));
+        if (!__any_sync(0xFFFFFFFFu, cmask != 0u)) continue;  // warp-uniform
+        const uint32_t mask = fits ? cmask : 0u;
         const int c = c0 + ci;
         float v[32];
         tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
@@ -129,12 +138,19 @@ __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t tadd
         for (int g = 0; g < 4; ++g) {
             if ((mask >> (8 * g)) & 0xFFu) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    list_append_if(list, inv_row0 - (uint32_t)(8 * g + j), __float_as_uint(v[8 * g + j]),
-                                   mask & (1u << (8 * g + j)));
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t bits = __float_as_uint(v[8 * g + j]);
+                    const uint32_t take = mask & (1u << (8 * g + j));
+                    list_append_if(list, inv_row0 - (uint32_t)(8 * g + j), bits, take);
+                    if (take && hrow) atomicAdd(hrow + hist_bucket(bits, hb), 1u);
+                }
             }
         }
     }
+    // live threshold: a list that just grew past a multiple of kRefreshEvery entries is re-read
+    if (a.hist)
+        refresh_thresholds_warp(a, fits && ((slot + n) / kRefreshEvery != slot / kRefreshEvery), q,
+                                (int)(threadIdx.x & 31));
 }
 
 // Phase 0: every score of the tile is written at slot = row - row_begin (no threshold yet).
@@ -284,6 +300,15 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         const int w = (warp - EPI_WARP0) & 3;
         const int c0 = ((warp - EPI_WARP0) >> 2) * EPI_CHUNKS;
         const uint32_t tempty0 = kCtas == 2 ? mapa_shared(tempty_bar(0), 0) : tempty_bar(0);
+        // Threshold and histogram origin of a thread's query come from L2 (thresholds are raised
+        // live by whoever appends candidates) and are fetched ONE TILE AHEAD, so the round trip is
+        // never on the epilogue's critical path.
+        auto query_of = [&](int t) { return ((t % n_qgroups) * kCtas + (int)cta_rank) * BM + w * 32 + lane; };
+        auto load_thr = [&](int qq) { return qq < a.nq ? __ldcg(a.thr + qq) : __builtin_huge_valf(); };
+        auto load_hb = [&](int qq) { return (qq < a.nq && a.hist) ? __ldcg(a.hbase + qq) : 0u; };
+        float thr_next = 0.f;
+        uint32_t hb_next = 0u;
+        if (t_begin < t_end) { thr_next = load_thr(query_of(t_begin)); hb_next = load_hb(query_of(t_begin)); }
         int it = 0;
         for (int t = t_begin; t < t_end; ++t, ++it) {
             const int ct = t / n_qgroups, qg = t - ct * n_qgroups;
@@ -292,13 +317,15 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             const uint32_t aph = (uint32_t)(it >> 1) & 1u;
             const int q = qt * BM + w * 32 + lane;
             const bool active = q < a.nq;
-            const float thr = active ? a.thr[q] : __builtin_huge_valf();
+            const float thr = thr_next;
+            const uint32_t hb = hb_next;
+            if (t + 1 < t_end) { thr_next = load_thr(query_of(t + 1)); hb_next = load_hb(query_of(t + 1)); }
             const uint32_t tile_row0 = a.row_begin + (uint32_t)ct * BN;
             mbar_wait(tfull_bar(buf), aph);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
             if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0, c0, c0 + EPI_CHUNKS);
-            else epilogue_filter(a, taddr, q, thr, tile_row0, c0);
+            else epilogue_filter(a, taddr, q, thr, hb, tile_row0, c0);
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) {

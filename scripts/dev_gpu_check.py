@@ -62,6 +62,8 @@ def timeit(variant, dtype, n, dim, nq, k, iters=5):
     idx.set_variant(variant)
     if os.environ.get("FIP_CTA_PAIR"):
         idx.set_option("cta_pair", int(os.environ["FIP_CTA_PAIR"]))
+    if os.environ.get("FIP_LIVE"):
+        idx.set_option("live_thresholds", int(os.environ["FIP_LIVE"]))
     if os.environ.get("FIP_SPLIT"):
         idx.set_option("query_split", int(os.environ["FIP_SPLIT"]))
     idx.set_option("profile_events", 1)

@@ -461,6 +461,31 @@ def test_concurrent_callers_are_coalesced_into_one_batch():
     idx.close()
 
 
+@pytest.mark.parametrize("variant,dtype,nq,k", [("tensor", "f16", 70, 100), ("tensor", "bf16", 33, 10), ("tensor", "f16", 200, 1024),
+                                                ("tensor", "f32", 16, 300), ("stream", "f16", 2, 100),
+                                                ("stream", "f32", 5, 1)])
+def test_live_thresholds_one_filter_launch_same_answer(variant, dtype, nq, k):
+    """Live thresholds (a filter launch raises its own thresholds from the score histogram) must
+    give bit-identical results to the fixed-threshold geometric phases, in fewer phases."""
+    dim, n = 128, 1_500_000
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    idx.set_variant(variant)
+    q = synthetic.synthetic_queries(nq, dim)
+    idx.set_option("live_thresholds", 0)
+    D0, I0 = idx.search(q, k)
+    phases0 = idx.stat("phases")
+    idx.set_option("live_thresholds", 1)
+    D1, I1 = idx.search(q, k)
+    assert idx.stat("overflow_queries") == 0
+    assert idx.stat("phases") == 2 and phases0 >= 2, (idx.stat("phases"), phases0)
+    assert np.array_equal(I0, I1) and np.array_equal(D0, D1)
+    corpus = synthetic.synthetic_corpus(0, n, dim, dtype)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
+    _check(D1, I1, Dr, Ir, dtype)
+    idx.close()
+
+
 def test_packed_exchange_buffer_merge():
     """The packed [distances | pad | ids] per-rank buffer of sharded.py, gathered as [g, total]
     bytes, merged by the strided K3 entry point == the oracle merge."""
