@@ -39,6 +39,13 @@ WORKLOADS = {
     "cfg5": (10_000_000, 384, "f16", 256, 1024),
 }
 METRIC = "QPS (100M x 768 fp16 flat-IP, k=100, batch 1024)"
+
+
+def metric_name(args, total_rows, dim, dtype, batch, k):
+    """BASELINE.json's metric for the default workload; the other workloads name their own shape."""
+    if args.workload == "cfg3" and not (args.rows or args.batch or args.k):
+        return METRIC
+    return f"QPS ({total_rows} x {dim} {dtype} flat-IP, k={k}, batch {batch})"
 UNIT = "queries/s"
 
 
@@ -162,7 +169,7 @@ def run_reference(args, rank, world):
     r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, target_s=12.0, steps=args.steps,
                        warmup=min(args.warmup, 1))
     line = {
-        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
+        "impl": "reference", "metric": metric_name(args, total_rows, dim, dtype, batch, k), "value": r["value"], "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": r["ms_per_step_scaled"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -354,7 +361,7 @@ def run_b200(args, rank, local_rank, world):
             with open(traffic_path) as f:
                 roof["traffic"] = json.load(f).get(f"{args.workload}_gpus{world}")
         line = {
-            "metric": METRIC, "value": batch / (ms_per_step * 1e-3), "unit": UNIT,
+            "metric": metric_name(args, total_rows, dim, dtype, batch, k), "value": batch / (ms_per_step * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": {"f16": "f16", "bf16": "bf16", "f32": "f32"}[dtype],
