@@ -39,6 +39,13 @@ EXPORTED_SYMBOLS = (
     "fip_exchange_create", "fip_exchange_ipc_handle", "fip_exchange_connect_ipc",
     "fip_exchange_connect_local", "fip_exchange_merge", "fip_exchange_destroy",
 )
+# include/ivfflat_b200.h (IVF-Flat L2 operator, same shared library)
+IVF_EXPORTED_SYMBOLS = (
+    "fivf_create", "fivf_destroy", "fivf_ntotal", "fivf_nlist", "fivf_dim", "fivf_is_trained",
+    "fivf_train", "fivf_set_centroids", "fivf_get_centroids", "fivf_add", "fivf_add_preassigned",
+    "fivf_assign", "fivf_list_sizes", "fivf_export_lists", "fivf_search", "fivf_search_device",
+    "fivf_set_option", "fivf_get_stat",
+)
 IPC_HANDLE_BYTES = 64
 
 
@@ -129,6 +136,40 @@ def load_library():
         lib.fip_last_error.argtypes = []
         lib.fip_last_error.restype = c.c_char_p
         lib.fip_abi_version.restype = c.c_int32
+        # IVF-Flat operator
+        lib.fivf_create.argtypes = [c.c_int32, c.c_int32, c.c_int32, c.POINTER(P)]
+        lib.fivf_create.restype = c.c_int
+        lib.fivf_destroy.argtypes = [P]
+        lib.fivf_destroy.restype = None
+        lib.fivf_ntotal.argtypes = [P]
+        lib.fivf_ntotal.restype = c.c_int64
+        for name in ("fivf_nlist", "fivf_dim", "fivf_is_trained"):
+            getattr(lib, name).argtypes = [P]
+            getattr(lib, name).restype = c.c_int32
+        lib.fivf_train.argtypes = [P, P, c.c_int64, c.c_int32, c.c_uint64]
+        lib.fivf_train.restype = c.c_int
+        lib.fivf_set_centroids.argtypes = [P, P]
+        lib.fivf_set_centroids.restype = c.c_int
+        lib.fivf_get_centroids.argtypes = [P, P]
+        lib.fivf_get_centroids.restype = c.c_int
+        lib.fivf_add.argtypes = [P, P, c.c_int64, P]
+        lib.fivf_add.restype = c.c_int
+        lib.fivf_add_preassigned.argtypes = [P, P, c.c_int64, P, P]
+        lib.fivf_add_preassigned.restype = c.c_int
+        lib.fivf_assign.argtypes = [P, P, c.c_int64, P]
+        lib.fivf_assign.restype = c.c_int
+        lib.fivf_list_sizes.argtypes = [P, P]
+        lib.fivf_list_sizes.restype = c.c_int
+        lib.fivf_export_lists.argtypes = [P, P, P]
+        lib.fivf_export_lists.restype = c.c_int
+        lib.fivf_search.argtypes = [P, P, c.c_int64, c.c_int32, c.c_int32, P, P]
+        lib.fivf_search.restype = c.c_int
+        lib.fivf_search_device.argtypes = [P, P, c.c_int64, c.c_int32, c.c_int32, P, P]
+        lib.fivf_search_device.restype = c.c_int
+        lib.fivf_set_option.argtypes = [P, c.c_char_p, c.c_int64]
+        lib.fivf_set_option.restype = c.c_int
+        lib.fivf_get_stat.argtypes = [P, c.c_char_p]
+        lib.fivf_get_stat.restype = c.c_int64
         lib.fip_compiled_sm.restype = c.c_int32
         _lib = lib
         return lib

@@ -1292,3 +1292,6 @@ int32_t fip_abi_version(void) { return 1; }
 int32_t fip_compiled_sm(void) { return 100; }
 
 }  // extern "C"
+
+// IVF-Flat (L2) operator: include/ivfflat_b200.h
+#include "ivf_api.cuh"

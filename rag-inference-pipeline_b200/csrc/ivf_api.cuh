@@ -1,0 +1,807 @@
+// C ABI of the IVF-Flat (L2) operator (include/ivfflat_b200.h) and its host-side orchestration.
+// Included at the end of flatip_api.cu (one translation unit: it reuses the select kernel, the
+// candidate-list workspace conventions, make_tmap, DevBuf and the error plumbing).
+//
+// Reference anchors: the index the reference builds and loads is an IndexIVFFlat / METRIC_L2 with
+// nlist = 4096 and nprobe = 64 (/root/reference/scripts/create_test_docs.py:83-104,
+// /root/reference/src/pipeline/components/faiss_store.py:66-93); it is searched through the same
+// `index.search(x, k)` call as the flat index (faiss_store.py:152).
+//
+// A search is: query norms -> coarse scores (all centroids) -> select nprobe -> [host: invert the
+// (query, list) pairs into list-major tiles] -> dense scan of each query's first list(s) -> select
+// (threshold + histogram) -> ONE filter scan of everything else with live thresholds -> select ->
+// finalize (distances, ids).  Overflowing candidate lists (adversarial data) redo the batch in
+// "safe mode" (phases too short to overflow), exactly like the flat path.
+#pragma once
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "../../include/ivfflat_b200.h"
+#include "ivf.cuh"
+
+struct fivf_index {
+    int dim = 0, nlist = 0, device = 0, num_sms = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    bool trained = false;
+    DevBuf<float> cent, cnorm;              // [nlist, dim], [nlist]
+    // sorted-by-list storage (valid when !dirty)
+    float* x = nullptr;                      // [n_sorted, dim]
+    int64_t* ids = nullptr;                  // [n_sorted]
+    float* xnorm = nullptr;                  // [n_sorted]
+    int64_t n_sorted = 0;
+    std::vector<int64_t> off;                // [nlist + 1] (host copy; lists are planned on the host)
+    // rows added since the last rebuild, in add order
+    float* pend_x = nullptr;
+    int64_t pend_n = 0, pend_cap = 0;
+    std::vector<int64_t> pend_ids;
+    std::vector<int32_t> pend_assign;
+    int64_t next_id = 0;
+    CUtensorMap tmap_x{};
+    bool tmap_valid = false;
+    // options
+    int force_safe = 0, live_thr = 1, qb_max = 16;
+    // workspace
+    DevBuf<uint64_t> ckeys, cand;
+    DevBuf<float> qnorm, probe_d, thr, sc, q32, out_d, stage, x2max, eps, ones;
+    DevBuf<int64_t> probe_i, pos, out_i, perm, doff;
+    DevBuf<int32_t> assign;
+    DevBuf<ivf::TileQuery> tile_q;
+    DevBuf<uint32_t> cnt, flags, hist, hbase;
+    DevBuf<ivf::Tile> tiles;
+    PinnedBuf<int64_t> h_probe, h_i;
+    PinnedBuf<uint8_t> h_plan;
+    PinnedBuf<uint32_t> h_flags;
+    PinnedBuf<float> h_q, h_d;
+    // stats of the last search
+    int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0;
+    int64_t ntotal() const { return n_sorted + pend_n; }
+};
+
+namespace {
+
+int fivf_use(const fivf_index* h) {
+    FIP_CUDA(cudaSetDevice(h->device));
+    return FIP_OK;
+}
+
+constexpr int kAssignChunk = 16384;   // rows per coarse-assignment chunk (keys: chunk * nlist * 8 B)
+
+// Nearest centroid of n device rows -> host `out` (chunked: coarse scores + row argmax).
+int fivf_assign_device(fivf_index* h, const float* x_dev, int64_t n, int32_t* out_host) {
+    const int nlist = h->nlist, dim = h->dim;
+    FIP_CUDA(h->ckeys.ensure((size_t)std::min<int64_t>(n, kAssignChunk) * nlist));
+    FIP_CUDA(h->assign.ensure((size_t)std::min<int64_t>(n, kAssignChunk)));
+    for (int64_t r0 = 0; r0 < n; r0 += kAssignChunk) {
+        const int m = (int)std::min<int64_t>(kAssignChunk, n - r0);
+        dim3 grid((nlist + ivf::CO_T - 1) / ivf::CO_T, (m + ivf::CO_T - 1) / ivf::CO_T);
+        ivf::coarse_scores_kernel<<<grid, 256, 0, h->stream>>>(x_dev + (size_t)r0 * dim, m, h->cent.p, nlist,
+                                                              h->cnorm.p, dim, h->ckeys.p, (uint32_t)nlist);
+        FIP_CUDA(cudaGetLastError());
+        ivf::row_argmax_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->ckeys.p, m, nlist, (uint32_t)nlist, h->assign.p);
+        FIP_CUDA(cudaGetLastError());
+        FIP_CUDA(cudaMemcpyAsync(out_host + r0, h->assign.p, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, h->stream));
+        FIP_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    return FIP_OK;
+}
+
+int fivf_update_cnorm(fivf_index* h) {
+    FIP_CUDA(h->cnorm.ensure(h->nlist));
+    ivf::row_norm2_kernel<<<(h->nlist + 7) / 8, 256, 0, h->stream>>>(h->cent.p, h->nlist, h->dim, h->cnorm.p);
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+
+// Stable counting sort of rows by list: off[nlist + 1], perm[pos] = source row.
+void counting_sort(const int32_t* assign, int64_t n, int nlist, std::vector<int64_t>* off,
+                   std::vector<int64_t>* perm) {
+    off->assign((size_t)nlist + 1, 0);
+    for (int64_t i = 0; i < n; ++i) (*off)[(size_t)assign[i] + 1]++;
+    for (int l = 0; l < nlist; ++l) (*off)[(size_t)l + 1] += (*off)[l];
+    perm->resize((size_t)n);
+    std::vector<int64_t> cur(off->begin(), off->end() - 1);
+    for (int64_t i = 0; i < n; ++i) (*perm)[(size_t)cur[assign[i]]++] = i;
+}
+
+// Merge the pending rows into the sorted-by-list storage (old rows of a list first, then the new
+// ones in add order, so positions inside a list follow add order = id order for sequential ids).
+int fivf_rebuild(fivf_index* h) {
+    if (h->pend_n == 0) return FIP_OK;
+    const int nlist = h->nlist, dim = h->dim;
+    const int64_t n_old = h->n_sorted, n_new = n_old + h->pend_n;
+    if (n_new >= (int64_t)0xFFFFFFFFll) return fail(FIP_ERR_INVALID, "an IVF index holds at most 2^32 - 2 rows per GPU");
+    std::vector<int64_t> cnt_new((size_t)nlist, 0);
+    for (int64_t i = 0; i < h->pend_n; ++i) cnt_new[h->pend_assign[(size_t)i]]++;
+    std::vector<int64_t> off_new((size_t)nlist + 1, 0), perm((size_t)n_new);
+    if (h->off.empty()) h->off.assign((size_t)nlist + 1, 0);
+    for (int l = 0; l < nlist; ++l)
+        off_new[(size_t)l + 1] = off_new[l] + (h->off[(size_t)l + 1] - h->off[l]) + cnt_new[l];
+    std::vector<int64_t> cur((size_t)nlist);
+    for (int l = 0; l < nlist; ++l) {   // virtual source = [old sorted rows ; pending rows]
+        int64_t p = off_new[l];
+        for (int64_t s = h->off[l]; s < h->off[(size_t)l + 1]; ++s) perm[(size_t)p++] = s;
+        cur[l] = p;
+    }
+    for (int64_t i = 0; i < h->pend_n; ++i) perm[(size_t)cur[h->pend_assign[(size_t)i]]++] = n_old + i;
+    // virtual source ids
+    DevBuf<int64_t> src_ids;
+    FIP_CUDA(src_ids.ensure((size_t)n_new));
+    if (n_old) FIP_CUDA(cudaMemcpyAsync(src_ids.p, h->ids, sizeof(int64_t) * n_old, cudaMemcpyDeviceToDevice, h->stream));
+    FIP_CUDA(cudaMemcpyAsync(src_ids.p + n_old, h->pend_ids.data(), sizeof(int64_t) * h->pend_n, cudaMemcpyHostToDevice, h->stream));
+    FIP_CUDA(h->perm.ensure((size_t)n_new));
+    FIP_CUDA(cudaMemcpyAsync(h->perm.p, perm.data(), sizeof(int64_t) * n_new, cudaMemcpyHostToDevice, h->stream));
+    float *nx = nullptr, *nn = nullptr;
+    int64_t* ni = nullptr;
+    FIP_CUDA(cudaMalloc((void**)&nx, (size_t)n_new * dim * sizeof(float)));
+    cudaError_t e = cudaMalloc((void**)&ni, (size_t)n_new * sizeof(int64_t));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&nn, (size_t)n_new * sizeof(float));
+    if (e != cudaSuccess) { cudaFree(nx); cudaFree(ni); src_ids.release(); FIP_CUDA(e); }
+    // gather in two launches (rows whose source is old storage / pending storage share one perm;
+    // the kernel takes one source, so the pending rows are addressed through an offset pointer)
+    ivf::gather_sorted2_kernel<<<(unsigned)((n_new + 7) / 8), 256, 0, h->stream>>>(
+        h->x, h->pend_x, n_old, src_ids.p, h->perm.p, n_new, dim, nx, ni, nn);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    src_ids.release();
+    if (e != cudaSuccess) { cudaFree(nx); cudaFree(ni); cudaFree(nn); FIP_CUDA(e); }
+    cudaFree(h->x); cudaFree(h->ids); cudaFree(h->xnorm); cudaFree(h->pend_x);
+    h->x = nx; h->ids = ni; h->xnorm = nn; h->n_sorted = n_new;
+    h->pend_x = nullptr; h->pend_n = 0; h->pend_cap = 0;
+    h->pend_ids.clear(); h->pend_ids.shrink_to_fit();
+    h->pend_assign.clear(); h->pend_assign.shrink_to_fit();
+    h->off.swap(off_new);
+    h->tmap_valid = false;
+    FIP_CUDA(h->x2max.ensure(1));
+    FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
+    ivf::max_norm_kernel<<<h->num_sms * 4, 256, 0, h->stream>>>(h->xnorm, n_new, h->x2max.p);
+    FIP_CUDA(cudaGetLastError());
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    return FIP_OK;
+}
+
+}  // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// Host plan: invert the probe table into list-major tiles, phase by phase.
+struct IvfPlan {
+    struct Phase { size_t t16_begin = 0, t16_n = 0, t4_begin = 0, t4_n = 0; };
+    std::vector<Phase> phases;
+    std::vector<ivf::Tile> tiles;
+    std::vector<ivf::TileQuery> tile_q;
+    int64_t rows = 0, pairs = 0;
+};
+
+struct Seg { int32_t list; uint32_t r0, r1; int32_t q; uint32_t skip; };
+
+// probes: [nq, nprobe] list numbers (-1 = none).
+//   normal mode: phase 0 (dense) scans only the first `target0` rows of each query's probe
+//     sequence -- enough to seed its threshold and score histogram; phase 1 scans EVERY probed list
+//     as a whole, grouped across the queries that probe it, with live thresholds; a query skips the
+//     rows of a list it already saw in phase 0 (TileQuery::skip), so nothing is scored twice and a
+//     list is still read once per query group;
+//   safe mode: the probe sequence is cut into phases of `cap` (dense) / `cap - k` rows so that no
+//     candidate list can overflow; partial lists become single-query tiles.
+void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, int k, int cap,
+                bool safe, int qb_big, IvfPlan* plan) {
+    const int nlist = h->nlist;
+    const std::vector<int64_t>& off = h->off;
+    std::vector<std::vector<Seg>> whole, part;   // per phase
+    auto phase_vecs = [&](size_t p) {
+        if (whole.size() <= p) { whole.resize(p + 1); part.resize(p + 1); }
+    };
+    const int64_t target0 = std::min<int64_t>(cap, std::max<int64_t>(4 * (int64_t)k, 256));
+    for (int q = 0; q < nq; ++q) {
+        if (!safe) {
+            int64_t cum = 0;
+            for (int j = 0; j < nprobe; ++j) {
+                const int64_t l = probes[(size_t)q * nprobe + j];
+                if (l < 0 || l >= nlist) continue;
+                const int64_t len = off[(size_t)l + 1] - off[l];
+                if (len == 0) continue;
+                int64_t take = 0;
+                if (cum < target0) {
+                    take = std::min(len, target0 - cum);
+                    phase_vecs(0);
+                    part[0].push_back(Seg{(int32_t)l, 0u, (uint32_t)take, q, 0u});
+                    cum += take;
+                }
+                if (take < len) {
+                    phase_vecs(1);
+                    whole[1].push_back(Seg{(int32_t)l, 0u, (uint32_t)len, q, (uint32_t)take});
+                }
+            }
+            continue;
+        }
+        size_t phase = 0;
+        int64_t used = 0, budget = cap;
+        for (int j = 0; j < nprobe; ++j) {
+            const int64_t l = probes[(size_t)q * nprobe + j];
+            if (l < 0 || l >= nlist) continue;
+            const int64_t len = off[(size_t)l + 1] - off[l];
+            int64_t r = 0;
+            while (r < len) {
+                const int64_t room = budget - used;
+                if (room <= 0) { phase++; used = 0; budget = std::max<int64_t>(256, cap - k); continue; }
+                const int64_t take = std::min(len - r, room);
+                phase_vecs(phase);
+                Seg s{(int32_t)l, (uint32_t)r, (uint32_t)(r + take), q, 0u};
+                (r == 0 && take == len ? whole : part)[phase].push_back(s);
+                r += take; used += take;
+                if (phase == 0 && used >= target0) { phase++; used = 0; budget = std::max<int64_t>(256, cap - k); }
+            }
+        }
+    }
+    plan->phases.assign(whole.size(), IvfPlan::Phase{});
+    std::vector<int32_t> lcount((size_t)nlist + 1);
+    std::vector<ivf::TileQuery> lq;
+    std::vector<ivf::Tile> t16, t4;
+    auto emit = [&](std::vector<ivf::Tile>& dst, int64_t list0, int64_t r0, int64_t r1, uint32_t qoff, uint32_t gq) {
+        for (int64_t r = r0; r < r1; r += ivf::SC_ROWS) {
+            const uint32_t nr = (uint32_t)std::min<int64_t>(ivf::SC_ROWS, r1 - r);
+            dst.push_back(ivf::Tile{(uint32_t)(list0 + r), nr, qoff, gq, (uint32_t)r});
+            plan->rows += nr;
+            plan->pairs += (int64_t)nr * gq;
+        }
+    };
+    for (size_t p = 0; p < whole.size(); ++p) {
+        t16.clear(); t4.clear();
+        // whole-list segments: bucket the queries by list (counting sort, O(pairs + nlist))
+        std::fill(lcount.begin(), lcount.end(), 0);
+        for (const Seg& s : whole[p]) lcount[(size_t)s.list + 1]++;
+        for (int l = 0; l < nlist; ++l) lcount[(size_t)l + 1] += lcount[l];
+        lq.resize(whole[p].size());
+        {
+            std::vector<int32_t> cur(lcount.begin(), lcount.end() - 1);
+            for (const Seg& s : whole[p]) lq[(size_t)cur[s.list]++] = ivf::TileQuery{s.q, s.skip};
+        }
+        for (int l = 0; l < nlist; ++l) {
+            const int m = lcount[(size_t)l + 1] - lcount[l];
+            if (m == 0) continue;
+            const int64_t len = off[(size_t)l + 1] - off[l];
+            for (int g0 = 0; g0 < m;) {
+                int gq = std::min(qb_big, m - g0);
+                const bool big = gq > 4;
+                if (!big) gq = std::min(4, m - g0);
+                const uint32_t qoff = (uint32_t)plan->tile_q.size();
+                for (int i = 0; i < gq; ++i) plan->tile_q.push_back(lq[(size_t)lcount[l] + g0 + i]);
+                emit(big ? t16 : t4, off[l], 0, len, qoff, (uint32_t)gq);
+                g0 += gq;
+            }
+        }
+        for (const Seg& s : part[p]) {
+            const uint32_t qoff = (uint32_t)plan->tile_q.size();
+            plan->tile_q.push_back(ivf::TileQuery{s.q, 0u});
+            emit(t4, off[s.list], s.r0, s.r1, qoff, 1u);
+        }
+        IvfPlan::Phase& ph = plan->phases[p];
+        ph.t16_begin = plan->tiles.size(); ph.t16_n = t16.size();
+        plan->tiles.insert(plan->tiles.end(), t16.begin(), t16.end());
+        ph.t4_begin = plan->tiles.size(); ph.t4_n = t4.size();
+        plan->tiles.insert(plan->tiles.end(), t4.begin(), t4.end());
+    }
+}
+
+template <int QB>
+int launch_ivf_scan(fivf_index* h, const ivf::ScanIvfArgs& a, int* launches) {
+    if (a.n_tiles == 0) return FIP_OK;
+    auto kern = ivf::ivf_scan_kernel<QB>;
+    const size_t smem = ivf::scan_smem_bytes(QB, h->dim);
+    FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = std::min(a.n_tiles, h->num_sms);
+    kern<<<grid, ivf::SC_THREADS, smem, h->stream>>>(h->tmap_x, a);
+    FIP_CUDA(cudaGetLastError());
+    (*launches)++;
+    return FIP_OK;
+}
+
+int ivf_select(fivf_index* h, int nq, int k, int cap, bool final_pass, bool live, int keep_max, int* launches) {
+    SelectArgs s{};
+    if (!final_pass) {   // exactness window (see ivf_eps_kernel)
+        s.win_eps = h->eps.p; s.win_scale = h->ones.p; s.keep_max = keep_max; s.uncert = h->flags.p + (nq + 1);
+    }
+    s.cand = h->cand.p; s.cnt = h->cnt.p; s.thr = h->thr.p; s.cap = (uint32_t)cap; s.k = k;
+    s.final_pass = final_pass ? 1 : 0; s.out_d = h->sc.p; s.out_i = h->pos.p; s.id_base = 0;
+    s.overflow = h->flags.p; s.dense_count = -1;
+    if (live && !final_pass) { s.hist = h->hist.p; s.hbase = h->hbase.p; }
+    const size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
+    FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    select_topk_kernel<<<nq, kSelectThreads, smem, h->stream>>>(s);
+    FIP_CUDA(cudaGetLastError());
+    (*launches)++;
+    return FIP_OK;
+}
+
+// One search of device-resident queries; results to device out_d / out_i.  Synchronises (the probe
+// table is planned on the host).  *overflowed = some candidate list overflowed (redo in safe mode).
+int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float* out_d, int64_t* out_i,
+             bool safe, bool* overflowed) {
+    const int dim = h->dim, nlist = h->nlist;
+    int launches = 0;
+    nprobe = std::max(1, std::min(nprobe, nlist));
+    FIP_CUDA(h->qnorm.ensure(nq));
+    FIP_CUDA(h->ckeys.ensure((size_t)nq * nlist));
+    FIP_CUDA(h->probe_d.ensure((size_t)nq * nprobe));
+    FIP_CUDA(h->probe_i.ensure((size_t)nq * nprobe));
+    FIP_CUDA(h->flags.ensure(2 * ((size_t)nq + 1)));
+    FIP_CUDA(h->thr.ensure(nq));
+    FIP_CUDA(h->cnt.ensure(nq));
+    FIP_CUDA(h->sc.ensure((size_t)nq * k));
+    FIP_CUDA(h->pos.ensure((size_t)nq * k));
+    FIP_CUDA(h->h_probe.ensure((size_t)nq * nprobe));
+    FIP_CUDA(h->eps.ensure(nq));
+    FIP_CUDA(h->ones.ensure(nq));
+    FIP_CUDA(h->x2max.ensure(1));
+    if (h->n_sorted == 0) FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
+    ivf::row_norm2_kernel<<<(nq + 7) / 8, 256, 0, h->stream>>>(q_dev, nq, dim, h->qnorm.p);
+    FIP_CUDA(cudaGetLastError());
+    ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim, h->eps.p, h->ones.p);
+    FIP_CUDA(cudaGetLastError());
+    init_lists_kernel<<<(nq + 256) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nq);
+    FIP_CUDA(cudaGetLastError());
+    // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
+    {
+        dim3 grid((nlist + ivf::CO_T - 1) / ivf::CO_T, (nq + ivf::CO_T - 1) / ivf::CO_T);
+        ivf::coarse_scores_kernel<<<grid, 256, 0, h->stream>>>(q_dev, nq, h->cent.p, nlist, h->cnorm.p, dim,
+                                                              h->ckeys.p, (uint32_t)nlist);
+        FIP_CUDA(cudaGetLastError());
+        SelectArgs s{};
+        s.cand = h->ckeys.p; s.cnt = h->cnt.p; s.thr = h->thr.p; s.cap = (uint32_t)nlist; s.k = nprobe;
+        s.final_pass = 1; s.out_d = h->probe_d.p; s.out_i = h->probe_i.p; s.id_base = 0;
+        s.overflow = h->flags.p; s.dense_count = nlist;
+        const size_t smem = ((size_t)nlist + (size_t)next_pow2(nprobe)) * sizeof(uint64_t);
+        FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        select_topk_kernel<<<nq, kSelectThreads, smem, h->stream>>>(s);
+        FIP_CUDA(cudaGetLastError());
+        launches += 4;
+    }
+    FIP_CUDA(cudaMemcpyAsync(h->h_probe.p, h->probe_i.p, sizeof(int64_t) * (size_t)nq * nprobe,
+                             cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+
+    const int cap = safe ? kMaxCap : std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
+    const bool live = h->live_thr && !safe;
+    const int keep_max = std::min(cap / 2, 2 * k + 64);   // truncation limit of the exactness window
+    const bool big_ok = h->qb_max >= 16 && ivf::scan_smem_bytes(16, dim) <= 227 * 1024;
+    IvfPlan plan;
+    const auto t0 = std::chrono::steady_clock::now();
+    build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, &plan);
+    h->st_plan_us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
+    const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
+    FIP_CUDA(h->h_plan.ensure(tile_bytes + tq_bytes + 16));
+    FIP_CUDA(h->tiles.ensure(plan.tiles.size() + 1));
+    FIP_CUDA(h->tile_q.ensure(plan.tile_q.size() + 1));
+    if (tile_bytes) {
+        memcpy(h->h_plan.p, plan.tiles.data(), tile_bytes);
+        FIP_CUDA(cudaMemcpyAsync(h->tiles.p, h->h_plan.p, tile_bytes, cudaMemcpyHostToDevice, h->stream));
+    }
+    if (tq_bytes) {
+        memcpy(h->h_plan.p + tile_bytes, plan.tile_q.data(), tq_bytes);
+        FIP_CUDA(cudaMemcpyAsync(h->tile_q.p, h->h_plan.p + tile_bytes, tq_bytes, cudaMemcpyHostToDevice, h->stream));
+    }
+    FIP_CUDA(h->cand.ensure((size_t)nq * cap));
+    if (live) {
+        FIP_CUDA(h->hist.ensure((size_t)nq * kHistBins));
+        FIP_CUDA(h->hbase.ensure(nq));
+    }
+    if (!h->tmap_valid && h->n_sorted > 0) {
+        int rc = make_tmap(&h->tmap_x, h->x, kF32, dim, (uint64_t)h->n_sorted);
+        if (rc) return rc;
+        h->tmap_valid = true;
+    }
+    // the coarse select used cnt / thr: reset the lists
+    init_lists_kernel<<<(nq + 256) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nq);
+    FIP_CUDA(cudaGetLastError());
+    launches++;
+
+    ivf::ScanIvfArgs a{};
+    a.tile_q = h->tile_q.p; a.q32 = q_dev; a.xnorm = h->xnorm; a.dim = dim;
+    a.lists.nq = nq; a.lists.thr = h->thr.p; a.lists.cnt = h->cnt.p; a.lists.cand = h->cand.p;
+    a.lists.cap = (uint32_t)cap; a.lists.k_thr = k;
+    if (live) { a.lists.hist = h->hist.p; a.lists.hbase = h->hbase.p; a.lists.win_eps = h->eps.p; a.lists.win_scale = h->ones.p; }
+    const size_t n_phases = plan.phases.size();
+    for (size_t p = 0; p < n_phases; ++p) {
+        const IvfPlan::Phase& ph = plan.phases[p];
+        a.dense = p == 0 ? 1 : 0;
+        a.tiles = h->tiles.p + ph.t16_begin; a.n_tiles = (int)ph.t16_n;
+        int rc = launch_ivf_scan<16>(h, a, &launches);
+        if (rc) return rc;
+        a.tiles = h->tiles.p + ph.t4_begin; a.n_tiles = (int)ph.t4_n;
+        rc = launch_ivf_scan<4>(h, a, &launches);
+        if (rc) return rc;
+        rc = ivf_select(h, nq, k, cap, false, live, keep_max, &launches);
+        if (rc) return rc;
+    }
+    if (n_phases > 0) {   // exact distances for the survivors, then the final ranking
+        const int64_t warps = (int64_t)nq * keep_max;
+        const unsigned grid = (unsigned)std::min<int64_t>((warps + 7) / 8, (int64_t)h->num_sms * 8);
+        ivf::ivf_rescore_kernel<<<grid, 256, 0, h->stream>>>(h->cand.p, h->cnt.p, (uint32_t)cap, nq, keep_max, h->x, q_dev, dim);
+        FIP_CUDA(cudaGetLastError());
+        launches++;
+    }
+    {   // (nothing scanned -- empty index or empty probed lists -- gives all padding)
+        int rc = ivf_select(h, nq, k, cap, true, false, 0, &launches);
+        if (rc) return rc;
+    }
+    const int64_t tot = (int64_t)nq * k;
+    ivf::ivf_finalize_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(
+        h->sc.p, h->pos.p, h->ids, nq, k, out_d, out_i);
+    FIP_CUDA(cudaGetLastError());
+    launches++;
+    FIP_CUDA(h->h_flags.ensure(4));
+    FIP_CUDA(cudaMemcpyAsync(h->h_flags.p, h->flags.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    *overflowed = h->h_flags.p[0] != 0;
+    h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)plan.tiles.size();
+    h->st_rows = plan.rows; h->st_pairs = plan.pairs; h->st_cap = cap;
+    h->st_tiles16 = 0;
+    for (const auto& ph : plan.phases) h->st_tiles16 += (int64_t)ph.t16_n;
+    return FIP_OK;
+}
+
+int fivf_search_checked(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float* out_d,
+                        int64_t* out_i) {
+    int rc = fivf_rebuild(h);
+    if (rc) return rc;
+    bool over = false;
+    rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, h->force_safe != 0, &over);
+    if (rc) return rc;
+    h->st_overflow = over ? 1 : 0;
+    if (over) {
+        rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, true, &over);
+        if (rc) return rc;
+        if (over) return fail(FIP_ERR_STATE, "internal error: IVF safe mode overflowed a candidate list");
+    }
+    return FIP_OK;
+}
+
+int fivf_check_search(const fivf_index* h, const void* q, int64_t nq, int32_t k, const void* d, const void* i) {
+    if (!h) return fail(FIP_ERR_INVALID, "null index");
+    if (nq < 0 || (nq > 0 && !q)) return fail(FIP_ERR_INVALID, "bad query buffer");
+    if (k < 1 || k > kMaxK) return fail(FIP_ERR_INVALID, "k must be in [1, 2048]");
+    if (nq > 0 && (!d || !i)) return fail(FIP_ERR_INVALID, "null output buffer");
+    if (nq > (int64_t)1 << 20) return fail(FIP_ERR_INVALID, "at most 2^20 queries per call");
+    if (!h->trained) return fail(FIP_ERR_STATE, "IVF index is not trained (no centroids)");
+    return FIP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fivf_create(int32_t dim, int32_t nlist, int32_t device, fivf_index** out) {
+    if (!out) return fail(FIP_ERR_INVALID, "null output handle");
+    *out = nullptr;
+    if (dim < 32 || dim % 32 != 0 || dim > 4096)
+        return fail(FIP_ERR_INVALID, "IVF-Flat needs 32 <= dim <= 4096 and dim % 32 == 0 (128-byte TMA chunks)");
+    if (nlist < 1 || nlist > kMaxCap) return fail(FIP_ERR_INVALID, "nlist must be in [1, 16384]");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        return fail(FIP_ERR_NODEVICE, "no CUDA device visible (this library has no CPU fallback)");
+    }
+    if (device < 0 || device >= count) return fail(FIP_ERR_INVALID, "device index out of range");
+    cudaDeviceProp prop{};
+    FIP_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(FIP_ERR_NODEVICE, std::string("device is ") + prop.name + ", this library is built for sm_100a only");
+    fivf_index* h = new fivf_index();
+    h->dim = dim; h->nlist = nlist; h->device = device; h->num_sms = prop.multiProcessorCount;
+    h->off.assign((size_t)nlist + 1, 0);
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = h->cent.ensure((size_t)nlist * dim);
+    if (e == cudaSuccess) e = h->cnorm.ensure(nlist);
+    if (e != cudaSuccess) { delete h; FIP_CUDA(e); }
+    *out = h;
+    return FIP_OK;
+}
+
+void fivf_destroy(fivf_index* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->x); cudaFree(h->ids); cudaFree(h->xnorm); cudaFree(h->pend_x);
+    h->cent.release(); h->cnorm.release(); h->ckeys.release(); h->cand.release(); h->qnorm.release();
+    h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
+    h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
+    h->doff.release(); h->assign.release(); h->tile_q.release(); h->cnt.release(); h->flags.release();
+    h->hist.release(); h->hbase.release(); h->tiles.release(); h->h_probe.release(); h->h_i.release();
+    h->h_plan.release(); h->h_flags.release(); h->h_q.release(); h->h_d.release();
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int64_t fivf_ntotal(const fivf_index* h) { return h ? h->ntotal() : -1; }
+int32_t fivf_nlist(const fivf_index* h) { return h ? h->nlist : -1; }
+int32_t fivf_dim(const fivf_index* h) { return h ? h->dim : -1; }
+int32_t fivf_is_trained(const fivf_index* h) { return h && h->trained ? 1 : 0; }
+
+int fivf_set_centroids(fivf_index* h, const float* centroids) {
+    if (!h || !centroids) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (h->ntotal() > 0) return fail(FIP_ERR_STATE, "centroids cannot change once vectors were added");
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    FIP_CUDA(cudaMemcpyAsync(h->cent.p, centroids, sizeof(float) * (size_t)h->nlist * h->dim, cudaMemcpyHostToDevice, h->stream));
+    rc = fivf_update_cnorm(h);
+    if (rc) return rc;
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    h->trained = true;
+    return FIP_OK;
+}
+
+int fivf_get_centroids(fivf_index* h, float* out) {
+    if (!h || !out) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->trained) return fail(FIP_ERR_STATE, "IVF index is not trained (no centroids)");
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    FIP_CUDA(cudaMemcpyAsync(out, h->cent.p, sizeof(float) * (size_t)h->nlist * h->dim, cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    return FIP_OK;
+}
+
+// k-means for the coarse quantizer (faiss Clustering::train as IndexIVF::train drives it: at most
+// 256 training points per centroid, random distinct rows as initial centroids, `niter` Lloyd
+// iterations, empty clusters re-seeded by splitting a large one with a +-1/1024 perturbation).
+// The random choices differ from faiss's (its RNG stream is not reproduced): trained centroids are
+// a property of this library; an index trained by faiss is imported with fivf_set_centroids /
+// fivf_load_lists instead.
+int fivf_train(fivf_index* h, const float* x, int64_t n, int32_t niter, uint64_t seed) {
+    if (!h || !x) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const int nlist = h->nlist, dim = h->dim;
+    if (h->ntotal() > 0) return fail(FIP_ERR_STATE, "train() must precede add()");
+    if (n < nlist) return fail(FIP_ERR_INVALID, "Number of training points (" + std::to_string(n) +
+                                                ") should be at least as large as number of clusters (" + std::to_string(nlist) + ")");
+    if (niter < 0) niter = 10;
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    // deterministic shuffle (splitmix64-driven Fisher-Yates) for the subsample and the seeds
+    std::vector<int64_t> order((size_t)n);
+    std::iota(order.begin(), order.end(), 0);
+    uint64_t st = seed;
+    auto next = [&]() { uint64_t z = (st += 0x9E3779B97F4A7C15ull); z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+                        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31); };
+    for (int64_t i = n - 1; i > 0; --i) std::swap(order[(size_t)i], order[(size_t)(next() % (uint64_t)(i + 1))]);
+    const int64_t nt = std::min<int64_t>(n, (int64_t)256 * nlist);
+    DevBuf<float> tx;
+    FIP_CUDA(tx.ensure((size_t)nt * dim));
+    {
+        std::vector<float> stage((size_t)std::min<int64_t>(nt, 65536) * dim);
+        for (int64_t r0 = 0; r0 < nt; r0 += 65536) {
+            const int64_t m = std::min<int64_t>(65536, nt - r0);
+            for (int64_t i = 0; i < m; ++i)
+                memcpy(stage.data() + (size_t)i * dim, x + (size_t)order[(size_t)(r0 + i)] * dim, sizeof(float) * dim);
+            cudaError_t e = cudaMemcpy(tx.p + (size_t)r0 * dim, stage.data(), sizeof(float) * (size_t)m * dim, cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+        }
+    }
+    // initial centroids: the first nlist rows of the shuffled training set
+    cudaError_t e = cudaMemcpyAsync(h->cent.p, tx.p, sizeof(float) * (size_t)nlist * dim, cudaMemcpyDeviceToDevice, h->stream);
+    if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+    std::vector<int32_t> assign((size_t)nt);
+    std::vector<int64_t> off, perm;
+    std::vector<float> hc;
+    auto cleanup = [&](int code) { tx.release(); return code; };
+    for (int it = 0; it < niter; ++it) {
+        rc = fivf_update_cnorm(h);
+        if (rc) return cleanup(rc);
+        rc = fivf_assign_device(h, tx.p, nt, assign.data());
+        if (rc) return cleanup(rc);
+        counting_sort(assign.data(), nt, nlist, &off, &perm);
+        e = h->perm.ensure((size_t)nt);
+        if (e == cudaSuccess) e = h->doff.ensure((size_t)nlist + 1);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h->perm.p, perm.data(), sizeof(int64_t) * nt, cudaMemcpyHostToDevice, h->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h->doff.p, off.data(), sizeof(int64_t) * ((size_t)nlist + 1), cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+        ivf::centroid_mean_kernel<<<dim3(nlist, (dim + 255) / 256), 256, 0, h->stream>>>(tx.p, h->perm.p, h->doff.p, dim, h->cent.p);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+        // empty clusters: split the (currently) largest cluster, symmetric perturbation
+        std::vector<int64_t> size((size_t)nlist);
+        int n_empty = 0;
+        for (int l = 0; l < nlist; ++l) { size[l] = off[(size_t)l + 1] - off[l]; n_empty += size[l] == 0; }
+        if (n_empty) {
+            hc.resize((size_t)nlist * dim);
+            e = cudaMemcpy(hc.data(), h->cent.p, sizeof(float) * hc.size(), cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+            for (int l = 0; l < nlist; ++l) {
+                if (size[l] != 0) continue;
+                const int big = (int)(std::max_element(size.begin(), size.end()) - size.begin());
+                const float eps = 1.0f / 1024.0f;
+                for (int c = 0; c < dim; ++c) {
+                    const float v = hc[(size_t)big * dim + c];
+                    const float s = (c & 1) ? eps : -eps;
+                    hc[(size_t)l * dim + c] = v * (1.0f + s);
+                    hc[(size_t)big * dim + c] = v * (1.0f - s);
+                }
+                size[l] = size[big] / 2;
+                size[big] -= size[l];
+            }
+            e = cudaMemcpy(h->cent.p, hc.data(), sizeof(float) * hc.size(), cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) { tx.release(); FIP_CUDA(e); }
+        }
+    }
+    tx.release();
+    rc = fivf_update_cnorm(h);
+    if (rc) return rc;
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    h->trained = true;
+    return FIP_OK;
+}
+
+// Nearest centroid (list number) of n host rows.
+int fivf_assign(fivf_index* h, const float* x, int64_t n, int32_t* out) {
+    if (!h || (n > 0 && (!x || !out))) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->trained) return fail(FIP_ERR_STATE, "IVF index is not trained (no centroids)");
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    for (int64_t r0 = 0; r0 < n; r0 += kAssignChunk) {
+        const int64_t m = std::min<int64_t>(kAssignChunk, n - r0);
+        FIP_CUDA(h->stage.ensure((size_t)m * h->dim));
+        FIP_CUDA(cudaMemcpyAsync(h->stage.p, x + (size_t)r0 * h->dim, sizeof(float) * (size_t)m * h->dim, cudaMemcpyHostToDevice, h->stream));
+        rc = fivf_assign_device(h, h->stage.p, m, out + r0);
+        if (rc) return rc;
+    }
+    return FIP_OK;
+}
+
+static int fivf_reserve_pending(fivf_index* h, int64_t want) {
+    if (want <= h->pend_cap) return FIP_OK;
+    const int64_t new_cap = std::max<int64_t>(want, h->pend_cap + h->pend_cap / 2);
+    float* p = nullptr;
+    FIP_CUDA(cudaMalloc((void**)&p, (size_t)new_cap * h->dim * sizeof(float)));
+    if (h->pend_x && h->pend_n) {
+        cudaError_t e = cudaMemcpyAsync(p, h->pend_x, (size_t)h->pend_n * h->dim * sizeof(float), cudaMemcpyDeviceToDevice, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { cudaFree(p); FIP_CUDA(e); }
+    }
+    cudaFree(h->pend_x);
+    h->pend_x = p;
+    h->pend_cap = new_cap;
+    return FIP_OK;
+}
+
+// IndexIVF::add / add_with_ids: assign each row to its nearest centroid and append it to that list.
+// ids == null: sequential ids starting at ntotal (faiss add()).  `assign` (optional, [n]) overrides
+// the coarse assignment (an imported index keeps the lists it was built with).
+static int fivf_add_impl(fivf_index* h, const float* x, int64_t n, const int64_t* ids, const int32_t* assign) {
+    if (!h || (n > 0 && !x)) return fail(FIP_ERR_INVALID, "null argument");
+    if (n < 0) return fail(FIP_ERR_INVALID, "negative row count");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->trained) return fail(FIP_ERR_STATE, "IVF index is not trained (no centroids)");
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    rc = fivf_reserve_pending(h, h->pend_n + n);
+    if (rc) return rc;
+    const size_t a0 = h->pend_assign.size();
+    h->pend_assign.resize(a0 + (size_t)n);
+    for (int64_t r0 = 0; r0 < n; r0 += 65536) {
+        const int64_t m = std::min<int64_t>(65536, n - r0);
+        float* dst = h->pend_x + (size_t)(h->pend_n + r0) * h->dim;
+        cudaError_t e = cudaMemcpyAsync(dst, x + (size_t)r0 * h->dim, sizeof(float) * (size_t)m * h->dim, cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) { h->pend_assign.resize(a0); FIP_CUDA(e); }
+        if (assign) {
+            for (int64_t i = 0; i < m; ++i) {
+                const int32_t l = assign[r0 + i];
+                if (l < 0 || l >= h->nlist) { h->pend_assign.resize(a0); cudaStreamSynchronize(h->stream); return fail(FIP_ERR_INVALID, "list number out of range"); }
+                h->pend_assign[a0 + (size_t)(r0 + i)] = l;
+            }
+        } else {
+            rc = fivf_assign_device(h, dst, m, h->pend_assign.data() + a0 + r0);
+            if (rc) { h->pend_assign.resize(a0); return rc; }
+        }
+    }
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    for (int64_t i = 0; i < n; ++i) h->pend_ids.push_back(ids ? ids[i] : h->next_id + i);
+    h->next_id += n;
+    h->pend_n += n;
+    return FIP_OK;
+}
+int fivf_add(fivf_index* h, const float* x, int64_t n, const int64_t* ids) { return fivf_add_impl(h, x, n, ids, nullptr); }
+int fivf_add_preassigned(fivf_index* h, const float* x, int64_t n, const int64_t* ids, const int32_t* assign) {
+    if (n > 0 && !assign) return fail(FIP_ERR_INVALID, "null assignment");
+    return fivf_add_impl(h, x, n, ids, assign);
+}
+
+int fivf_list_sizes(fivf_index* h, int64_t* out) {
+    if (!h || !out) return fail(FIP_ERR_INVALID, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    rc = fivf_rebuild(h);
+    if (rc) return rc;
+    for (int l = 0; l < h->nlist; ++l) out[l] = h->off[(size_t)l + 1] - h->off[l];
+    return FIP_OK;
+}
+
+// The inverted lists, concatenated in list order: codes [ntotal, dim] fp32, ids [ntotal].
+int fivf_export_lists(fivf_index* h, float* codes, int64_t* ids) {
+    if (!h) return fail(FIP_ERR_INVALID, "null index");
+    std::lock_guard<std::mutex> lk(h->mu);
+    int rc = fivf_use(h);
+    if (rc) return rc;
+    rc = fivf_rebuild(h);
+    if (rc) return rc;
+    if (h->n_sorted == 0) return FIP_OK;
+    if (codes) FIP_CUDA(cudaMemcpyAsync(codes, h->x, sizeof(float) * (size_t)h->n_sorted * h->dim, cudaMemcpyDeviceToHost, h->stream));
+    if (ids) FIP_CUDA(cudaMemcpyAsync(ids, h->ids, sizeof(int64_t) * (size_t)h->n_sorted, cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    return FIP_OK;
+}
+
+int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int32_t k, int32_t nprobe,
+                       float* distances_dev, int64_t* ids_dev) {
+    int rc = fivf_check_search(h, queries_dev, nq, k, distances_dev, ids_dev);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    rc = fivf_use(h);
+    if (rc) return rc;
+    return fivf_search_checked(h, queries_dev, (int)nq, k, nprobe, distances_dev, ids_dev);
+}
+
+int fivf_search(fivf_index* h, const float* queries, int64_t nq, int32_t k, int32_t nprobe,
+                float* distances, int64_t* ids) {
+    int rc = fivf_check_search(h, queries, nq, k, distances, ids);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    rc = fivf_use(h);
+    if (rc) return rc;
+    const size_t nqd = (size_t)nq * h->dim, nqk = (size_t)nq * k;
+    FIP_CUDA(h->h_q.ensure(nqd));
+    FIP_CUDA(h->h_d.ensure(nqk));
+    FIP_CUDA(h->h_i.ensure(nqk));
+    FIP_CUDA(h->q32.ensure(nqd));
+    FIP_CUDA(h->out_d.ensure(nqk));
+    FIP_CUDA(h->out_i.ensure(nqk));
+    memcpy(h->h_q.p, queries, sizeof(float) * nqd);
+    FIP_CUDA(cudaMemcpyAsync(h->q32.p, h->h_q.p, sizeof(float) * nqd, cudaMemcpyHostToDevice, h->stream));
+    rc = fivf_search_checked(h, h->q32.p, (int)nq, k, nprobe, h->out_d.p, h->out_i.p);
+    if (rc) return rc;
+    FIP_CUDA(cudaMemcpyAsync(h->h_d.p, h->out_d.p, sizeof(float) * nqk, cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaMemcpyAsync(h->h_i.p, h->out_i.p, sizeof(int64_t) * nqk, cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaStreamSynchronize(h->stream));
+    memcpy(distances, h->h_d.p, sizeof(float) * nqk);
+    memcpy(ids, h->h_i.p, sizeof(int64_t) * nqk);
+    return FIP_OK;
+}
+
+int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
+    if (!h || !key) return fail(FIP_ERR_INVALID, "null argument");
+    const std::string k(key);
+    if (k == "force_safe") h->force_safe = (int)value;
+    else if (k == "live_thresholds") h->live_thr = (int)value;
+    else if (k == "max_queries_per_tile") h->qb_max = (int)value;
+    else return fail(FIP_ERR_INVALID, "unknown option " + k);
+    return FIP_OK;
+}
+
+int64_t fivf_get_stat(const fivf_index* h, const char* key) {
+    if (!h || !key) return -1;
+    const std::string k(key);
+    if (k == "launches") return h->st_launches;
+    if (k == "phases") return h->st_phases;
+    if (k == "tiles") return h->st_tiles;
+    if (k == "tiles16") return h->st_tiles16;
+    if (k == "rows_scanned") return h->st_rows;
+    if (k == "pairs_scored") return h->st_pairs;
+    if (k == "overflow") return h->st_overflow;
+    if (k == "candidate_capacity") return h->st_cap;
+    if (k == "plan_us") return h->st_plan_us;
+    return -1;
+}
+
+}  // extern "C"

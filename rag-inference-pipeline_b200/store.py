@@ -12,6 +12,8 @@ It is looked up by the retrieval service under the registry name ``faiss_store``
 
 ``settings.faiss_index_path`` may name
   * a faiss flat index file (``IxFI``) -- what the reference's ``faiss.read_index`` consumes,
+  * a faiss IVF-Flat index file (``IwFl``, METRIC_L2) -- what the reference's own builder writes;
+    it is served by the IVF-Flat operator (``ivf.py``) with ``nprobe = settings.faiss_nprobe``,
   * a FIPB corpus file written by ``index_io.write_fipb`` (fp32 / fp16 / bf16 rows), or
   * ``synthetic:<rows>[?dim=..&dtype=..&seed=..]`` -- a Philox corpus generated on the device.
 """
@@ -67,7 +69,30 @@ class B200FlatIPStore:
         index.add_synthetic(nrows, seed, row0)
         return index
 
-    def _load_file(self) -> FlatIPIndex:
+    def _load_ivf(self):
+        """A faiss IndexIVFFlat file -- the index type the reference's own builder writes
+        (``/root/reference/scripts/create_test_docs.py:83-104``).  Centroids and inverted lists are
+        imported unchanged; ``nprobe`` follows ``settings.faiss_nprobe`` like the reference
+        (``faiss_store.py:84-93``), falling back to the value stored in the file."""
+        from .ivf import IVFFlatL2Index
+
+        f = index_io.read_faiss_ivfflat(str(self.index_path))
+        if f.metric != "l2":
+            raise ValueError("only METRIC_L2 IVF-Flat indexes are supported")
+        nprobe = int(getattr(self.settings, "faiss_nprobe", 0) or f.nprobe or 1)
+        index = IVFFlatL2Index(f.dim, f.nlist, self.device, nprobe=nprobe)
+        index.set_centroids(f.centroids)
+        list_numbers = np.repeat(np.arange(f.nlist, dtype=np.int32), f.sizes)
+        step = max(1, _UPLOAD_CHUNK_BYTES // (f.dim * 4))
+        for r0 in range(0, f.ntotal, step):
+            index.add_preassigned(f.codes[r0:r0 + step], f.ids[r0:r0 + step], list_numbers[r0:r0 + step])
+        logger.info("Set FAISS nprobe to %d for IVF index (searching %.2f%% of clusters)", nprobe,
+                    nprobe / f.nlist * 100)
+        return index
+
+    def _load_file(self):
+        if index_io.is_faiss_ivfflat(str(self.index_path)):
+            return self._load_ivf()
         info = index_io.read_header(str(self.index_path))
         if info.metric != "ip":
             raise ValueError("only inner-product flat indexes are supported (file holds an "
@@ -100,7 +125,7 @@ class B200FlatIPStore:
         logger.info("Loading FAISS index from %s", self._raw_path)
         try:
             index = self._load_synthetic() if synthetic else self._load_file()
-            if self.variant != "auto":
+            if self.variant != "auto" and hasattr(index, "set_variant"):
                 index.set_variant(self.variant)
             self._index = index
             self._is_loaded = True
@@ -175,6 +200,8 @@ class B200FlatIPStore:
         batch = q.shape[0]
         distances = torch.empty((batch, int(k)), dtype=torch.float32, device=q.device)
         indices = torch.empty((batch, int(k)), dtype=torch.int64, device=q.device)
+        if not hasattr(self._index, "set_variant"):   # IVF runs on its own stream
+            torch.cuda.current_stream(q.device).synchronize()
         try:
             self._index.search_device(q.data_ptr(), batch, int(k), distances.data_ptr(),
                                       indices.data_ptr(),

@@ -1,0 +1,184 @@
+"""GPU parity tests of the IVF-Flat (L2) operator (include/ivfflat_b200.h) against the
+numpy restatement of faiss IndexIVFFlat search (oracle/ivf_oracle.py), through the C ABI.
+
+The oracle searches the SAME index (centroids and inverted lists exported from the GPU index, or
+lists it built itself and imported with add_preassigned), so the comparison pins the search path:
+coarse probe selection, list scan, top-k, distance / id / padding contract.
+Acceptance: squared L2 distances within 1e-5 relative (+1e-4 absolute: the operator evaluates
+||q||^2 - (2<q,x> - ||x||^2) in fp32) of the fp64 oracle; ids bit-exact outside near-tie windows.
+"""
+import types
+
+import numpy as np
+import pytest
+
+import ivf_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(n, d, nq, seed=0, clustered=False):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    if clustered:
+        x += 4.0 * rng.standard_normal((16, d)).astype(np.float32)[rng.integers(0, 16, n)]
+    q = x[rng.integers(0, n, nq)] + 0.5 * rng.standard_normal((nq, d)).astype(np.float32)
+    return x, q.astype(np.float32)
+
+
+def _stable_probe_rows(q, centroids, nprobe):
+    """Queries whose nprobe-th / (nprobe+1)-th centroid distances are not a near tie."""
+    d = np.sort(ivf_oracle.sq_l2(q, centroids), axis=1)
+    if nprobe >= centroids.shape[0]:
+        return np.ones(len(q), dtype=bool)
+    return (d[:, nprobe] - d[:, nprobe - 1]) > 1e-3 + 2e-5 * d[:, nprobe]
+
+
+def _check(index, q, k, nprobe):
+    sizes, codes, ids = index.export_lists()
+    cent = index.centroids()
+    D, I = index.search(q, k, nprobe=nprobe)
+    Dr, Ir, _, D64 = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, k + 1, nprobe)
+    ok = _stable_probe_rows(q, cent, nprobe)
+    assert ok.mean() > 0.9
+    res = ivf_oracle.compare_ivf(D[ok], I[ok], Dr[ok, :k], Ir[ok, :k], D64[ok])
+    assert res["dist_bad"] == 0 and res["pad_bad"] == 0 and res["id_mismatch_outside_ties"] == 0, res
+    assert res["id_mismatch_total"] <= max(2, D.size // 200), res
+    # rows are ascending and padding sits at the end
+    valid = I >= 0
+    assert np.all(valid[:, :-1] >= valid[:, 1:])
+    assert np.all((np.diff(D, axis=1) >= 0) | ~valid[:, 1:])
+    return D, I
+
+
+@pytest.mark.parametrize("n,d,nlist,nq,k,nprobe", [
+    (20000, 64, 32, 37, 10, 4),
+    (50000, 768, 64, 64, 100, 8),
+    (30000, 128, 256, 200, 10, 64),     # many queries per list: 16-query tiles
+    (6000, 96, 64, 5, 50, 1),           # k > rows of the probed list: padding
+    (20000, 64, 2, 9, 10, 1),           # lists longer than the candidate capacity: split segments
+    (5000, 32, 16, 1, 1, 16),           # nprobe == nlist: exhaustive
+])
+def test_ivf_search_matches_oracle(n, d, nlist, nq, k, nprobe):
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(n, d, nq, seed=n + d)
+    index = IVFFlatL2Index(d, nlist)
+    index.train(x[: min(n, 40 * nlist)])
+    assert index.is_trained
+    index.add(x)
+    assert index.ntotal == n
+    D, I = _check(index, q, k, nprobe)
+    if nprobe == nlist:   # exhaustive probing == exact flat L2 search
+        d64 = ivf_oracle.sq_l2(q, x)
+        assert np.array_equal(I[:, 0], np.argmin(d64, axis=1))
+    assert index.stat("overflow") == 0
+    index.close()
+
+
+def test_ivf_safe_mode_and_fixed_thresholds_agree():
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(40000, 64, 50, seed=5, clustered=True)
+    index = IVFFlatL2Index(64, 8)
+    index.train(x[:2000])
+    index.add(x)
+    D0, I0 = _check(index, q, 100, 4)
+    index.set_option("force_safe", 1)
+    D1, I1 = index.search(q, 100, nprobe=4)
+    assert index.stat("phases") >= 2 and index.stat("candidate_capacity") == 16384
+    index.set_option("force_safe", 0)
+    index.set_option("live_thresholds", 0)
+    D2, I2 = index.search(q, 100, nprobe=4)
+    index.set_option("live_thresholds", 1)
+    index.set_option("max_queries_per_tile", 4)
+    D3, I3 = index.search(q, 100, nprobe=4)
+    for D, I in ((D1, I1), (D2, I2), (D3, I3)):
+        assert np.array_equal(I, I0) and np.array_equal(D, D0)
+    index.close()
+
+
+def test_ivf_incremental_add_ids_and_duplicates():
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(9000, 64, 20, seed=9)
+    x[100] = x[7000]            # duplicate rows land in the same list: lower id first
+    q[0] = x[100]
+    index = IVFFlatL2Index(64, 16)
+    index.train(x[:1000])
+    index.add(x[:3000])
+    _check(index, q, 5, 4)      # forces a rebuild; the next adds are merged into sorted storage
+    index.add(x[3000:6000])
+    index.add_with_ids(x[6000:], np.arange(6000, 9000, dtype=np.int64) + 1_000_000_000_000)
+    assert index.ntotal == 9000
+    D, I = _check(index, q, 5, 4)
+    assert list(I[0, :2]) == [100, 7000 + 1_000_000_000_000] and D[0, 0] <= 1e-3 and D[0, 1] <= 1e-3
+    sizes, codes, ids = index.export_lists()
+    assert sizes.sum() == 9000 and len(np.unique(ids)) == 9000
+    # every list keeps add order
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    for l in range(16):
+        assert np.all(np.diff(ids[off[l]:off[l + 1]]) > 0)
+    index.close()
+
+
+def test_ivf_assignment_is_nearest_centroid():
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, _ = _data(20000, 128, 1, seed=3)
+    index = IVFFlatL2Index(128, 100)
+    index.train(x[:5000], niter=5)
+    cent = index.centroids()
+    assert np.isfinite(cent).all()
+    a = index.assign(x)
+    d = ivf_oracle.sq_l2(x, cent)
+    best = d.min(axis=1)
+    got = d[np.arange(len(x)), a]
+    assert np.all(got <= best + 1e-3 * np.maximum(1.0, best))
+    assert (a == np.argmin(d, axis=1)).mean() > 0.999
+    # k-means did its job: lower quantisation error than the initial (random-row) centroids
+    index2 = IVFFlatL2Index(128, 100)
+    index2.train(x[:5000], niter=0)
+    d0 = ivf_oracle.sq_l2(x, index2.centroids()).min(axis=1)
+    assert best.mean() < d0.mean()
+    index.add(x)
+    assert (index.list_sizes() > 0).all()
+    with pytest.raises(Exception, match="at least as large as number of clusters"):
+        IVFFlatL2Index(128, 100).train(x[:50])
+    with pytest.raises(Exception, match="not trained"):
+        IVFFlatL2Index(128, 100).add(x[:5])
+    index.close()
+    index2.close()
+
+
+def test_store_loads_faiss_ivfflat_file(tmp_path):
+    """The reference's default index type (scripts/create_test_docs.py:83-104) loads through the
+    store and is searched with settings.faiss_nprobe (faiss_store.py:84-93)."""
+    from rag_inference_pipeline_b200 import B200FlatIPStore, index_io
+
+    d, nlist, n = 768, 32, 12000
+    x, q = _data(n, d, 32, seed=11)
+    rng = np.random.default_rng(1)
+    cent = x[rng.choice(n, nlist, replace=False)].copy()
+    assign = ivf_oracle.assign_nearest(x, cent)
+    sizes, codes, ids = ivf_oracle.build_lists(x, np.arange(n, dtype=np.int64), assign, nlist)
+    path = tmp_path / "faiss_index.bin"
+    index_io.write_faiss_ivfflat(str(path), cent, sizes, codes, ids, nprobe=64)
+    settings = types.SimpleNamespace(faiss_index_path=str(path), faiss_dim=d, faiss_use_mmap=False,
+                                     faiss_nprobe=8)
+    store = B200FlatIPStore(settings)
+    store.load()
+    assert store.is_loaded and store.index_size == n
+    D, I = store.search(q, 10)
+    assert D.dtype == np.float32 and I.dtype == np.int64 and D.shape == (32, 10)
+    Dr, Ir, _, D64 = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, 11, 8)
+    ok = _stable_probe_rows(q, cent, 8)
+    res = ivf_oracle.compare_ivf(D[ok], I[ok], Dr[ok, :10], Ir[ok, :10], D64[ok])
+    assert res["dist_bad"] == 0 and res["id_mismatch_outside_ties"] == 0, res
+    with pytest.raises(ValueError, match="Embedding dimension mismatch"):
+        store.search(q[:, :64], 10)
+    import torch
+    Dt, It = store.search_device(torch.from_numpy(q).cuda(), 10)
+    assert np.array_equal(It.cpu().numpy(), I) and np.array_equal(Dt.cpu().numpy(), D)
+    store.unload()
+    assert not store.is_loaded

@@ -1,0 +1,88 @@
+"""CPU tests of the IVF-Flat operator's host side: the oracle against brute force, the faiss
+IndexIVFFlat file layout round trip, and the C-ABI symbols declared in include/ivfflat_b200.h."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import ivf_oracle
+from conftest import ROOT, gpu_available
+
+
+def _index(n=3000, d=32, nlist=12, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    cent = x[rng.choice(n, nlist, replace=False)].copy()
+    assign = ivf_oracle.assign_nearest(x, cent)
+    sizes, codes, ids = ivf_oracle.build_lists(x, np.arange(n, dtype=np.int64), assign, nlist)
+    q = rng.standard_normal((7, d)).astype(np.float32)
+    return x, cent, sizes, codes, ids, q
+
+
+def test_oracle_exhaustive_probing_is_brute_force_l2():
+    x, cent, sizes, codes, ids, q = _index()
+    D, I, P, D64 = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, 10, nprobe=len(cent))
+    d = ((q[:, None, :].astype(np.float64) - x[None].astype(np.float64)) ** 2).sum(-1)
+    ref = np.argsort(d, axis=1, kind="stable")[:, :10]
+    assert np.array_equal(I, ref)
+    assert np.allclose(D, np.take_along_axis(d, ref, 1), rtol=1e-6)
+    assert np.array_equal(ids[P], I)
+
+
+def test_oracle_probes_restrict_the_scan_and_pad():
+    x, cent, sizes, codes, ids, q = _index(n=200, nlist=40)
+    D, I, _, _ = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, 50, nprobe=2)
+    probes = ivf_oracle.coarse_probes(q, cent, 2)
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    for qi in range(len(q)):
+        allowed = set()
+        for l in probes[qi]:
+            allowed.update(ids[off[l]:off[l + 1]].tolist())
+        got = I[qi][I[qi] >= 0]
+        assert set(got.tolist()) == allowed or len(got) == 50
+        assert np.all(D[qi][I[qi] < 0] == ivf_oracle.FLT_MAX)
+        assert np.all(np.diff(D[qi][I[qi] >= 0]) >= 0)
+    # the nearest centroid of a centroid is itself
+    assert np.array_equal(ivf_oracle.coarse_probes(cent, cent, 1)[:, 0], np.arange(len(cent)))
+
+
+def test_faiss_ivfflat_file_round_trip(tmp_path):
+    from rag_inference_pipeline_b200 import index_io
+
+    _, cent, sizes, codes, ids, _ = _index()
+    for s in (sizes, np.concatenate([[int(sizes.sum())], np.zeros(len(sizes) - 1, np.int64)])):
+        path = str(tmp_path / "ivf.bin")
+        index_io.write_faiss_ivfflat(path, cent, s, codes, ids, nprobe=64)
+        assert index_io.is_faiss_ivfflat(path)
+        f = index_io.read_faiss_ivfflat(path)
+        assert (f.dim, f.ntotal, f.nlist, f.nprobe, f.metric) == (32, 3000, 12, 64, "l2")
+        assert np.array_equal(f.centroids, cent) and np.array_equal(f.sizes, s)
+        assert np.array_equal(f.codes, codes) and np.array_equal(f.ids, ids)
+    with open(path, "r+b") as fh:   # truncated file fails loudly
+        fh.truncate(os.path.getsize(path) - 100)
+    with pytest.raises(ValueError, match="shorter"):
+        index_io.read_faiss_ivfflat(path)
+    flat = str(tmp_path / "flat.bin")
+    index_io.write_faiss_flat(flat, codes)
+    assert not index_io.is_faiss_ivfflat(flat)
+
+
+def test_library_exports_every_declared_ivf_symbol(native_lib):
+    from rag_inference_pipeline_b200 import _native
+
+    text = open(os.path.join(ROOT, "include", "ivfflat_b200.h")).read()
+    declared = set(re.findall(r"\b(fivf_[a-z0-9_]+)\s*\(", text))
+    assert declared == set(_native.IVF_EXPORTED_SYMBOLS), declared ^ set(_native.IVF_EXPORTED_SYMBOLS)
+    for name in declared:
+        assert hasattr(native_lib, name), name
+
+
+@pytest.mark.skipif(gpu_available(), reason="checks the no-GPU failure mode")
+def test_ivf_has_no_cpu_fallback(native_lib):
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+    from rag_inference_pipeline_b200._native import FIP_ERR_NODEVICE, FlatIPError
+
+    with pytest.raises(FlatIPError) as ei:
+        IVFFlatL2Index(64, 8)
+    assert ei.value.code == FIP_ERR_NODEVICE
