@@ -71,7 +71,7 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
 
 /* options: "force_safe", "live_thresholds", "max_queries_per_tile" (4 or 16).
  * stats of the last search: "launches", "phases", "tiles", "tiles16", "rows_scanned",
- * "pairs_scored", "overflow", "candidate_capacity", "plan_us". */
+ * "pairs_scored", "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm". */
 int fivf_set_option(fivf_index* h, const char* key, int64_t value);
 int64_t fivf_get_stat(const fivf_index* h, const char* key);
 

@@ -176,14 +176,25 @@ struct ScanIvfArgs {
     ScanArgs lists;            // thr / cnt / cand / cap / hist / hbase / k_thr (common.cuh)
 };
 
-constexpr int SC_ROWS = 512;                 // rows per tile: 2 per thread
-constexpr int SC_THREADS = 256;
-constexpr int SC_BOX_ROWS = 128;             // make_tmap's box: 128 bytes x 128 rows, SWIZZLE_128B
-constexpr int SC_BOXES = SC_ROWS / SC_BOX_ROWS;
-constexpr int SC_STAGE_BYTES = SC_ROWS * 128;   // 64 KB: one 32-float K chunk of every row
-constexpr int SC_STAGES = 2;
+constexpr int SC_ROWS = 512;                 // rows per tile: up to 4 per consumer thread
+constexpr int SC_CONSUMERS = 128;            // warps 0..3 compute, warp 4 is the TMA producer; 2 CTAs per SM
+constexpr int SC_THREADS = SC_CONSUMERS + 32;
+constexpr int SC_BOX_ROWS = 128;             // TMA box: 64 bytes x 128 rows, SWIZZLE_64B (= one row slot per thread)
+constexpr int SC_SLOTS = SC_ROWS / SC_BOX_ROWS;
+constexpr int SC_CHUNK = 16;                 // floats of K per pipeline stage (64 bytes of every row)
+constexpr int SC_BOX_BYTES = SC_BOX_ROWS * SC_CHUNK * 4;   // 8 KB
+constexpr int SC_STAGE_BYTES = SC_SLOTS * SC_BOX_BYTES;    // 32 KB
+constexpr int SC_MAX_STAGES = 8;
+// Two CTAs per SM: (228 KB - 2 x 1 KB system reserve) / 2 per CTA, everything in dynamic shared
+// memory (no static arrays): [512-byte alignment slack | ring | queries | tile state + barriers].
+constexpr size_t SC_SMEM_LIMIT = (228 * 1024 - 2 * 1024) / 2;
+constexpr size_t SC_AUX_BYTES = 384;   // s_qid[16], s_skip[16], s_thr[16], full[8], empty[8]
+inline int scan_stages(int qb, int dim) {
+    const long long room = (long long)SC_SMEM_LIMIT - 512 - (long long)SC_AUX_BYTES - (long long)qb * dim * 4;
+    return (int)std::max<long long>(0, std::min<long long>(SC_MAX_STAGES, room / SC_STAGE_BYTES));
+}
 inline size_t scan_smem_bytes(int qb, int dim) {
-    return (size_t)SC_STAGES * SC_STAGE_BYTES + (size_t)qb * dim * 4 + 1024 /*align*/ + 256;
+    return (size_t)scan_stages(qb, dim) * SC_STAGE_BYTES + (size_t)qb * dim * 4 + 512 + SC_AUX_BYTES;
 }
 
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -207,59 +218,155 @@ __device__ __forceinline__ void fma2(uint64_t& d, uint64_t a, uint64_t b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
-// Persistent CTAs, static round-robin tile schedule.  The K chunks of all of a CTA's tiles form ONE
-// stream through a 2-stage TMA ring (thread 0 refills a stage as soon as the CTA has consumed it),
-// so the first chunks of the next tile are already in flight while the current tile's epilogue and
-// the next tile's query staging run.  x rows come in through the SWIZZLE_128B tensor map (lane i
-// reads row i: the swizzle spreads the 8 granules of 8 consecutive rows over all banks, so the
-// 128-bit loads are conflict-free without padding).  The tile's queries sit TRANSPOSED in shared
-// memory (s_q[k][j]), so one warp-wide broadcast load yields the k-th component of four queries as
-// two packed pairs and the inner product runs on FFMA2: per 16-byte step of its two rows a thread
-// issues 2 + QB shared loads, 8 pack moves and 4 QB packed FMAs (= 8 QB fp32 FMAs).
-// Every (row, query) score is one fp32 FMA chain in k order: bit-identical for any tiling.
+// One tile for one consumer thread: R row slots (rows tid + 128 h) x QB queries.  The tile's
+// queries sit TRANSPOSED in shared memory (s_q[k][j]), so one warp-wide broadcast load yields the
+// k-th component of four queries as two packed pairs and the products run on FFMA2 (the scalar x
+// operand is broadcast by the instruction: `FFMA2 R, Rx.F32, Rq.F32x2, R`).  Shared-memory
+// wavefronts per FFMA2 = 2 / QB + 1 / R (a 128-bit broadcast load costs 2 wavefronts, a per-lane
+// one 4): 0.375 at QB = 16, R = 4, below the 0.5 at which the LSU instead of the FMA pipe would
+// bind (ncu: R = 2 ran at 67 % LSU / 57 % FMA).  Every (row, query) score is one fp32 FMA chain in
+// k order: bit-identical for any tiling or grouping.
+template <int QB, int R>
+__device__ __forceinline__ void consume_tile(const ScanIvfArgs& a, const Tile& t, uint32_t base, uint32_t sq_addr,
+                                             uint64_t* s_full, uint64_t* s_empty, const int* s_qid,
+                                             const uint32_t* s_skip, const float* s_thr, int stages, int nkc,
+                                             int tid, int lane, int& s, uint32_t& ph) {
+    const uint32_t r_off = (uint32_t)tid * 64u;          // 64-byte row slots, 8 KB per box
+    const uint32_t sw = (uint32_t)((tid >> 1) & 3);      // SWIZZLE_64B: granule ^= (row / 2) % 4
+    uint64_t acc[R][QB / 2];   // [row slot][query pair]
+#pragma unroll
+    for (int h = 0; h < R; ++h)
+#pragma unroll
+        for (int p = 0; p < QB / 2; ++p) acc[h][p] = 0ull;
+    for (int kc = 0; kc < nkc; ++kc) {
+        mbar_wait(smem_u32(&s_full[s]), ph);
+        const uint32_t st = base + s * SC_STAGE_BYTES + r_off;
+#pragma unroll 2
+        for (int g = 0; g < SC_CHUNK / 4; ++g) {   // unrolled by two only: four row-slot variants share the i-cache
+            const uint32_t go = ((uint32_t)g ^ sw) * 16u;
+            float xv[R][4];
+#pragma unroll
+            for (int h = 0; h < R; ++h) {
+                const float4 x = lds_f4(st + h * SC_BOX_BYTES + go);
+                xv[h][0] = x.x; xv[h][1] = x.y; xv[h][2] = x.z; xv[h][3] = x.w;
+            }
+            const uint32_t qa = sq_addr + (uint32_t)((kc * SC_CHUNK + g * 4) * QB) * 4u;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+                for (int jj = 0; jj < QB / 4; ++jj) {
+                    uint64_t q01, q23;
+                    lds_2x64(qa + (uint32_t)((kk * QB + 4 * jj) * 4), q01, q23);
+#pragma unroll
+                    for (int h = 0; h < R; ++h) {
+                        const uint64_t px = pack2(xv[h][kk], xv[h][kk]);
+                        fma2(acc[h][2 * jj], px, q01);
+                        fma2(acc[h][2 * jj + 1], px, q23);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(smem_u32(&s_empty[s]));   // this warp is done with stage s
+        if (++s == stages) { s = 0; ph ^= 1u; }
+    }
+    // epilogue: score = 2 <q, x> - ||x||^2, filter, append
+    bool need = false;
+    int need_q = 0;
+#pragma unroll
+    for (int h = 0; h < R; ++h) {
+        const uint32_t r = (uint32_t)tid + (uint32_t)(SC_BOX_ROWS * h);
+        if (r < t.nrows) {
+            const uint32_t pos = t.row0 + r;
+            const uint32_t rel = t.rel0 + r;
+            const float xn = __ldg(a.xnorm + pos);
+#pragma unroll
+            for (int p = 0; p < QB / 2; ++p) {
+                float d2[2];
+                unpack2(acc[h][p], d2[0], d2[1]);
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int j = 2 * p + e;
+                    const float sc = fmaf(2.0f, d2[e], -xn);
+                    if (sc > s_thr[j] && rel >= s_skip[j]) {   // unused slots carry +inf, dense phases -inf
+                        const int q = s_qid[j];
+                        if (a.dense) {
+                            const uint32_t slot = atomicAdd(a.lists.cnt + q, 1u);
+                            if (slot < a.lists.cap) a.lists.cand[(size_t)q * a.lists.cap + slot] = make_raw_key(sc, pos);
+                        } else if (append_candidate(a.lists, q, sc, pos)) {
+                            need = true; need_q = q;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    __syncwarp();
+    if (a.lists.hist && !a.dense) refresh_thresholds_warp(a.lists, need, need_q, lane);
+}
+
+// Persistent CTAs (two per SM), static round-robin tile schedule, warp-specialised: warp 4 streams
+// the 16-float K chunks of ALL of the CTA's tiles through a ring of `stages` stages (TMA, full /
+// empty mbarriers), running ahead across tile boundaries, so HBM stays busy during epilogues and
+// query staging; warps 0..3 consume (no CTA-wide barrier in the K loop: a warp releases a stage
+// with one mbarrier arrival).  x rows come in through a SWIZZLE_64B tensor map, one 128-row box
+// per row slot (lane i reads row i: the swizzle spreads the granules of 8 consecutive rows over all
+// banks, so the 128-bit loads are conflict-free without padding); only the boxes that hold rows of
+// the tile are loaded, and the inner loop is instantiated per number of live row slots, so a short
+// tile costs neither bandwidth nor FMAs for its missing rows.
 template <int QB>
-__global__ void __launch_bounds__(SC_THREADS, 1)
-ivf_scan_kernel(const __grid_constant__ CUtensorMap tmap_x, ScanIvfArgs a) {
+__global__ void __launch_bounds__(SC_THREADS, 2)
+ivf_scan_kernel(const __grid_constant__ CUtensorMap tmap_x, ScanIvfArgs a, int stages) {
     static_assert(QB % 4 == 0, "queries are loaded four at a time");
+    static_assert(QB <= 16, "tile state is sized for 16 queries");
     extern __shared__ uint8_t smem_raw[];
-    __shared__ int s_qid[QB];
-    __shared__ uint32_t s_skip[QB];
-    __shared__ float s_thr[QB];
-    __shared__ __align__(8) uint64_t s_bar[SC_STAGES];
-    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t sq_addr = base + SC_STAGES * SC_STAGE_BYTES;
-    float* s_q = reinterpret_cast<float*>(smem_raw + (sq_addr - smem_u32(smem_raw)));   // [dim][QB]
+    const uint32_t base = (smem_u32(smem_raw) + 511u) & ~511u;   // SWIZZLE_64B pattern repeats every 512 bytes
+    const uint32_t sq_addr = base + (uint32_t)stages * SC_STAGE_BYTES;
+    uint8_t* gen = smem_raw + (sq_addr - smem_u32(smem_raw));
+    float* s_q = reinterpret_cast<float*>(gen);                  // [dim][QB]
+    uint8_t* aux = gen + (size_t)QB * a.dim * 4;
+    uint64_t* s_full = reinterpret_cast<uint64_t*>(aux);         // [8]
+    uint64_t* s_empty = s_full + SC_MAX_STAGES;                  // [8]
+    int* s_qid = reinterpret_cast<int*>(aux + 128);              // [16]
+    uint32_t* s_skip = reinterpret_cast<uint32_t*>(aux + 192);   // [16]
+    float* s_thr = reinterpret_cast<float*>(aux + 256);          // [16]
     const int tid = threadIdx.x, lane = tid & 31;
-    const int nkc = a.dim / 32;
+    const int nkc = a.dim / SC_CHUNK;
     const int my_tiles = a.n_tiles > (int)blockIdx.x ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-    const long long total_chunks = (long long)my_tiles * nkc;
     if (tid == 0) {
         tma_prefetch_desc(&tmap_x);
-        for (int s = 0; s < SC_STAGES; ++s) mbar_init(smem_u32(&s_bar[s]), 1);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(smem_u32(&s_full[s]), 1);
+            mbar_init(smem_u32(&s_empty[s]), SC_CONSUMERS / 32);
+        }
         fence_barrier_init();
     }
     __syncthreads();
-    auto issue = [&](long long c) {   // thread 0: load chunk c of this CTA's chunk stream
-        const int ti = (int)(c / nkc), kc = (int)(c - (long long)ti * nkc);
-        const uint32_t row0 = a.tiles[(size_t)blockIdx.x + (size_t)ti * gridDim.x].row0;
-        const int s = (int)(c % SC_STAGES);
-        const uint32_t bar = smem_u32(&s_bar[s]);
-        mbar_arrive_expect_tx(bar, SC_STAGE_BYTES);
-#pragma unroll
-        for (int b = 0; b < SC_BOXES; ++b)   // rows past the list's end are loaded and ignored
-            tma_load_2d(base + s * SC_STAGE_BYTES + b * SC_BOX_ROWS * 128, &tmap_x, bar, kc * 32,
-                        (int)row0 + b * SC_BOX_ROWS);
-    };
-    if (tid == 0)
-        for (long long c = 0; c < SC_STAGES && c < total_chunks; ++c) issue(c);
-
-    // this thread's two rows inside a stage: r and r + 256  (box = r / 128, 128-byte row slots)
-    const uint32_t ra_off = (uint32_t)tid * 128u, rb_off = (uint32_t)(tid + 256) * 128u;
-    const uint32_t sw = (uint32_t)(tid & 7);   // (tid + 256) & 7 == tid & 7
-    long long c = 0;
+    if (tid >= SC_CONSUMERS) {   // ===================== TMA producer (one lane)
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int ti = 0; ti < my_tiles; ++ti) {
+                const Tile t = a.tiles[(size_t)blockIdx.x + (size_t)ti * gridDim.x];
+                const int slots = (int)(t.nrows + SC_BOX_ROWS - 1) / SC_BOX_ROWS;
+                for (int kc = 0; kc < nkc; ++kc) {
+                    mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
+                    const uint32_t bar = smem_u32(&s_full[s]);
+                    mbar_arrive_expect_tx(bar, (uint32_t)slots * SC_BOX_BYTES);
+                    for (int b = 0; b < slots; ++b)   // rows past the list's end are loaded and ignored
+                        tma_load_2d(base + s * SC_STAGE_BYTES + b * SC_BOX_BYTES, &tmap_x, bar,
+                                    kc * SC_CHUNK, (int)t.row0 + b * SC_BOX_ROWS);
+                    if (++s == stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+        return;
+    }
+    int s = 0;
+    uint32_t ph = 0;
     for (int ti = 0; ti < my_tiles; ++ti) {
         const Tile t = a.tiles[(size_t)blockIdx.x + (size_t)ti * gridDim.x];
-        __syncthreads();   // previous tile's epilogue is done with s_qid / s_thr / s_skip
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // previous tile's epilogue and K loop are done
         if (tid < QB) {
             TileQuery tq{-1, 0u};
             if (tid < (int)t.nq) tq = a.tile_q[t.qoff + tid];
@@ -267,83 +374,41 @@ ivf_scan_kernel(const __grid_constant__ CUtensorMap tmap_x, ScanIvfArgs a) {
             s_skip[tid] = tq.skip;
             s_thr[tid] = tq.q < 0 ? __builtin_huge_valf() : (a.dense ? kNegInf : __ldcg(a.lists.thr + tq.q));
         }
-        // stage the tile's queries transposed: s_q[k][j] (zeros for unused slots)
-        for (int i = tid; i < QB * (a.dim / 4); i += SC_THREADS) {
-            const int j = i % QB, v = i / QB;   // lanes walk the queries: <= 4-way store conflicts
-            float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (j < (int)t.nq) {
-                const int q = a.tile_q[t.qoff + j].q;
-                val = __ldg(reinterpret_cast<const float4*>(a.q32 + (size_t)q * a.dim) + v);
-            }
-            float* dst = s_q + (size_t)(4 * v) * QB + j;
-            dst[0] = val.x; dst[QB] = val.y; dst[2 * QB] = val.z; dst[3 * QB] = val.w;
-        }
-        __syncthreads();
-        uint64_t acc[2][QB / 2];   // [row][query pair]
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // stage the tile's queries transposed: s_q[k][j]; loads are issued eight at a time so the
+        // L2 round trips overlap (lanes walk the queries: <= 4-way store conflicts; slots of unused
+        // queries keep stale values: their scores meet a +inf threshold)
+        {
+            const int vec = a.dim / 4, total = QB * vec;
+            constexpr int BATCH = 8;
+            for (int i0 = tid; i0 < total; i0 += SC_CONSUMERS * BATCH) {
+                float4 val[BATCH];
 #pragma unroll
-        for (int p = 0; p < QB / 2; ++p) { acc[0][p] = 0ull; acc[1][p] = 0ull; }
-        for (int kc = 0; kc < nkc; ++kc, ++c) {
-            const int s = (int)(c % SC_STAGES);
-            mbar_wait(smem_u32(&s_bar[s]), (uint32_t)((c / SC_STAGES) & 1));
-            const uint32_t st = base + s * SC_STAGE_BYTES;
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-                const uint32_t go = ((uint32_t)g ^ sw) * 16u;
-                const float4 xa = lds_f4(st + ra_off + go);
-                const float4 xb = lds_f4(st + rb_off + go);
-                const float xav[4] = {xa.x, xa.y, xa.z, xa.w}, xbv[4] = {xb.x, xb.y, xb.z, xb.w};
-                const uint32_t qa = sq_addr + (uint32_t)((kc * 32 + g * 4) * QB) * 4u;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {
-                    const uint64_t pa = pack2(xav[kk], xav[kk]), pb = pack2(xbv[kk], xbv[kk]);
-#pragma unroll
-                    for (int jj = 0; jj < QB / 4; ++jj) {
-                        uint64_t q01, q23;
-                        lds_2x64(qa + (uint32_t)((kk * QB + 4 * jj) * 4), q01, q23);
-                        fma2(acc[0][2 * jj], pa, q01); fma2(acc[0][2 * jj + 1], pa, q23);
-                        fma2(acc[1][2 * jj], pb, q01); fma2(acc[1][2 * jj + 1], pb, q23);
-                    }
+                for (int u = 0; u < BATCH; ++u) {
+                    const int i = i0 + u * SC_CONSUMERS;
+                    const int j = i % QB, v = i / QB;
+                    val[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (i < total && j < (int)t.nq)
+                        val[u] = __ldg(reinterpret_cast<const float4*>(a.q32 + (size_t)s_qid[j] * a.dim) + v);
                 }
-            }
-            __syncthreads();   // the CTA has consumed stage s
-            if (tid == 0 && c + SC_STAGES < total_chunks) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                issue(c + SC_STAGES);
-            }
-        }
-        // epilogue: score = 2 <q, x> - ||x||^2, filter, append
-        bool need = false;
-        int need_q = 0;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const uint32_t r = (uint32_t)tid + 256u * h;
-            if (r < t.nrows) {
-                const uint32_t pos = t.row0 + r;
-                const uint32_t rel = t.rel0 + r;
-                const float xn = __ldg(a.xnorm + pos);
-#pragma unroll
-                for (int p = 0; p < QB / 2; ++p) {
-                    float d2[2];
-                    unpack2(acc[h][p], d2[0], d2[1]);
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int j = 2 * p + e;
-                        const float sc = fmaf(2.0f, d2[e], -xn);
-                        if (sc > s_thr[j] && rel >= s_skip[j]) {   // unused slots carry +inf, dense phases -inf
-                            const int q = s_qid[j];
-                            if (a.dense) {
-                                const uint32_t slot = atomicAdd(a.lists.cnt + q, 1u);
-                                if (slot < a.lists.cap) a.lists.cand[(size_t)q * a.lists.cap + slot] = make_raw_key(sc, pos);
-                            } else if (append_candidate(a.lists, q, sc, pos)) {
-                                need = true; need_q = q;
-                            }
-                        }
+                for (int u = 0; u < BATCH; ++u) {
+                    const int i = i0 + u * SC_CONSUMERS;
+                    if (i < total) {
+                        const int j = i % QB, v = i / QB;
+                        float* dst = s_q + (size_t)(4 * v) * QB + j;
+                        dst[0] = val[u].x; dst[QB] = val[u].y; dst[2 * QB] = val[u].z; dst[3 * QB] = val[u].w;
                     }
                 }
             }
         }
-        __syncwarp();
-        if (a.lists.hist && !a.dense) refresh_thresholds_warp(a.lists, need, need_q, lane);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        switch ((t.nrows + SC_BOX_ROWS - 1) / SC_BOX_ROWS) {
+            case 1: consume_tile<QB, 1>(a, t, base, sq_addr, s_full, s_empty, s_qid, s_skip, s_thr, stages, nkc, tid, lane, s, ph); break;
+            case 2: consume_tile<QB, 2>(a, t, base, sq_addr, s_full, s_empty, s_qid, s_skip, s_thr, stages, nkc, tid, lane, s, ph); break;
+            case 3: consume_tile<QB, 3>(a, t, base, sq_addr, s_full, s_empty, s_qid, s_skip, s_thr, stages, nkc, tid, lane, s, ph); break;
+            default: consume_tile<QB, 4>(a, t, base, sq_addr, s_full, s_empty, s_qid, s_skip, s_thr, stages, nkc, tid, lane, s, ph); break;
+        }
     }
 }
 

@@ -58,7 +58,7 @@ struct fivf_index {
     PinnedBuf<float> h_q, h_d;
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -293,9 +293,16 @@ int launch_ivf_scan(fivf_index* h, const ivf::ScanIvfArgs& a, int* launches) {
     if (a.n_tiles == 0) return FIP_OK;
     auto kern = ivf::ivf_scan_kernel<QB>;
     const size_t smem = ivf::scan_smem_bytes(QB, h->dim);
+    const int stages = ivf::scan_stages(QB, h->dim);
+    if (stages < 2) return fail(FIP_ERR_INVALID, "dim too large for the IVF scan kernel's shared-memory ring");
     FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int grid = std::min(a.n_tiles, h->num_sms);
-    kern<<<grid, ivf::SC_THREADS, smem, h->stream>>>(h->tmap_x, a);
+    if (QB == 16 && h->st_occ16 < 0) {
+        int occ = 0;
+        FIP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, ivf::SC_THREADS, smem));
+        h->st_occ16 = occ;
+    }
+    const int grid = std::min(a.n_tiles, 2 * h->num_sms);   // two CTAs per SM
+    kern<<<grid, ivf::SC_THREADS, smem, h->stream>>>(h->tmap_x, a, stages);
     FIP_CUDA(cudaGetLastError());
     (*launches)++;
     return FIP_OK;
@@ -368,7 +375,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     const int cap = safe ? kMaxCap : std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
     const bool live = h->live_thr && !safe;
     const int keep_max = std::min(cap / 2, 2 * k + 64);   // truncation limit of the exactness window
-    const bool big_ok = h->qb_max >= 16 && ivf::scan_smem_bytes(16, dim) <= 227 * 1024;
+    const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
     IvfPlan plan;
     const auto t0 = std::chrono::steady_clock::now();
     build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, &plan);
@@ -391,8 +398,18 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         FIP_CUDA(h->hbase.ensure(nq));
     }
     if (!h->tmap_valid && h->n_sorted > 0) {
-        int rc = make_tmap(&h->tmap_x, h->x, kF32, dim, (uint64_t)h->n_sorted);
-        if (rc) return rc;
+        // [n_sorted, dim] fp32, box = 16 floats (64 bytes) x 128 rows, SWIZZLE_64B
+        EncodeTiledFn enc = get_encode_fn();
+        if (!enc) return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+        cuuint64_t dims[2] = {(cuuint64_t)dim, (cuuint64_t)h->n_sorted};
+        cuuint64_t strides[1] = {(cuuint64_t)dim * 4};
+        cuuint32_t box[2] = {(cuuint32_t)ivf::SC_CHUNK, (cuuint32_t)ivf::SC_BOX_ROWS};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = enc(&h->tmap_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, h->x, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+            return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
         h->tmap_valid = true;
     }
     // the coarse select used cnt / thr: reset the lists
@@ -801,6 +818,7 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "overflow") return h->st_overflow;
     if (k == "candidate_capacity") return h->st_cap;
     if (k == "plan_us") return h->st_plan_us;
+    if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
 }
 

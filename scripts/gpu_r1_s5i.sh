@@ -1,0 +1,8 @@
+#!/bin/bash
+# Session-5 call I: IVF scan v4b (batched query staging, granule loop not unrolled): parity, timing, ncu full.
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_ivf.py -q > gpurun_out/s5i_pytest_ivf.log 2>&1; echo "pytest ivf rc=$?"; tail -5 gpurun_out/s5i_pytest_ivf.log
+export IVF_TRAIN=100000
+timeout 600 python scripts/dev_ivf_check.py 1000000 768 1024 16 1,32,256,1024 10 > gpurun_out/s5i_time_1M.log 2>&1; echo "time rc=$?"; tail -6 gpurun_out/s5i_time_1M.log
+CMD="python scripts/dev_ivf_check.py 1000000 768 1024 16 1024 10 2"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:ivf_scan_kernel -s 12 -c 4 -o gpurun_out/s5i_prof_ivf $CMD > gpurun_out/s5i_ncu.log 2>&1; echo "ncu rc=$?"
