@@ -26,8 +26,8 @@ _blas_handle = None
 
 
 def build(force: bool = False) -> str:
-    src = os.path.join(_HERE, "faiss_flat_restatement.c")
-    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("faiss_flat_restatement.c", "faiss_ivf_restatement.c")]
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < max(map(os.path.getmtime, srcs)):
         subprocess.run(["make", "-C", _HERE, "-B" if force else "-s"], check=True)
     return _LIB_PATH
 
@@ -62,6 +62,11 @@ def load():
             ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
             ctypes.c_int]
         _lib.oracle_max_threads.restype = ctypes.c_int
+        _lib.oracle_ivf_search_l2.restype = ctypes.c_int
+        _lib.oracle_ivf_search_l2.argtypes = [
+            ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64,
+            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
         _lib.oracle_synthetic_rows.restype = ctypes.c_int
         _lib.oracle_synthetic_rows.argtypes = [
             ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_uint64,
@@ -108,3 +113,26 @@ def synthetic_corpus(row0: int, nrows: int, dim: int, dtype: str = "f32", seed: 
     if rc != 0:
         raise RuntimeError("oracle_synthetic_rows failed")
     return out
+
+
+def ivf_search_l2(queries: np.ndarray, centroids: np.ndarray, sizes: np.ndarray, codes: np.ndarray,
+                  ids: np.ndarray, k: int, nprobe: int, *, nthreads: int = 0):
+    """faiss-style CPU IVF-Flat (L2) search (oracle/faiss_ivf_restatement.c): OpenMP over queries,
+    per-query coarse probe + list scan + k-max-heap.  Returns (D float32 [B,k], I int64 [B,k])."""
+    lib = load()
+    q = np.ascontiguousarray(queries, dtype=np.float32)
+    c = np.ascontiguousarray(centroids, dtype=np.float32)
+    x = np.ascontiguousarray(codes, dtype=np.float32)
+    i = np.ascontiguousarray(ids, dtype=np.int64)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    B, d = q.shape
+    if c.shape[1] != d or x.shape != (int(off[-1]), d) or i.shape != (int(off[-1]),):
+        raise ValueError("shape mismatch")
+    D = np.empty((B, k), dtype=np.float32)
+    I = np.empty((B, k), dtype=np.int64)
+    rc = lib.oracle_ivf_search_l2(q.ctypes.data, B, d, c.ctypes.data, c.shape[0], off.ctypes.data,
+                                  x.ctypes.data, i.ctypes.data, k, nprobe, D.ctypes.data,
+                                  I.ctypes.data, int(nthreads))
+    if rc != 0:
+        raise RuntimeError(f"oracle_ivf_search_l2 failed: {rc}")
+    return D, I

@@ -86,3 +86,19 @@ def test_ivf_has_no_cpu_fallback(native_lib):
     with pytest.raises(FlatIPError) as ei:
         IVFFlatL2Index(64, 8)
     assert ei.value.code == FIP_ERR_NODEVICE
+
+
+def test_c_restatement_of_faiss_ivf_matches_numpy_oracle():
+    """oracle/faiss_ivf_restatement.c (the timed CPU baseline: OpenMP over queries, per-query
+    coarse probe + list scan + k-max-heap) against the fp64 numpy restatement."""
+    import c_oracle
+
+    _, cent, sizes, codes, ids, q = _index(n=20000, d=64, nlist=50, seed=3)
+    for k, nprobe in ((10, 5), (300, 2), (5, 50), (1, 1)):
+        D, I, _, D64 = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, k + 1, nprobe)
+        Dc, Ic = c_oracle.ivf_search_l2(q, cent, sizes, codes, ids, k, nprobe)
+        res = ivf_oracle.compare_ivf(Dc, Ic, D[:, :k], I[:, :k], D64)
+        assert res["dist_bad"] == 0 and res["pad_bad"] == 0 and res["id_mismatch_outside_ties"] == 0, res
+    D1, I1 = c_oracle.ivf_search_l2(q, cent, sizes, codes, ids, 10, 5, nthreads=1)
+    D2, I2 = c_oracle.ivf_search_l2(q, cent, sizes, codes, ids, 10, 5, nthreads=4)
+    assert np.array_equal(I1, I2) and np.array_equal(D1, D2)
