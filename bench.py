@@ -390,13 +390,159 @@ def run_b200(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------
+# Second operator: IVF-Flat (L2) at the reference's own index shape.  Not the
+# driver's default line; same JSON contract, run with `--workload ivf`.
+# ------------------------------------------------------------------------------------------
+IVF_SHAPE = dict(rows=4_500_000, dim=768, nlist=4096, nprobe=64, batch=32, k=10, train=100_000)
+
+
+def run_ivf(args):
+    """`--workload ivf`: IndexIVFFlat(IndexFlatL2(768), 768, 4096, METRIC_L2), nprobe 64, over 4.5 M
+    standard-normal rows (/root/reference/scripts/create_test_docs.py:12,83-104), batch 32, k 10
+    (configs/retrieval_faiss_only.yaml: retrieval_batch_size / retrieval_k).  The quantizer is trained
+    on 100 000 rows (the reference trains on 10 000, which on structure-free Gaussian data yields one
+    545 k-row list that every query probes; `--ivf-train 10000` reproduces that).  value = QPS with
+    device-resident queries (wall clock: the call plans on the host and blocks), e2e = the host API.
+    roofline: HBM -- algorithmic bytes = the rows of every list probed by at least one query, read
+    once (fp32), over the device time of the scan launches.  cpu_baseline / --impl reference: the C
+    restatement of faiss's IVF search (oracle/faiss_ivf_restatement.c) on the same index and queries."""
+    import numpy as np
+    import torch
+
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    sh = dict(IVF_SHAPE)
+    if args.rows:
+        sh["rows"] = args.rows
+    if args.batch:
+        sh["batch"] = args.batch
+    if args.k:
+        sh["k"] = args.k
+    if args.ivf_train:
+        sh["train"] = args.ivf_train
+    n, dim, nlist, nprobe, B, k = sh["rows"], sh["dim"], sh["nlist"], sh["nprobe"], sh["batch"], sh["k"]
+    metric = f"QPS ({n} x {dim} fp32 IVF-Flat L2, nlist {nlist}, nprobe {nprobe}, k={k}, batch {B})"
+    config = {"workload": f"IVF-Flat (L2) search, standard-normal {n} x {dim} fp32 corpus, nlist {nlist} "
+                          f"(trained on {sh['train']} rows), nprobe {nprobe}, batch {B}, k {k}, 1 GPU",
+              "l2": "probed lists >> L2 (126 MB), no flush"}
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    rng = np.random.default_rng(0)
+    reference = args.impl == "reference"
+    keep_host = reference or not args.no_cpu_baseline
+    t0 = time.time()
+    first = rng.standard_normal((min(n, 100_000), dim), dtype=np.float32)
+    # (the reference arm too builds the index with the GPU library, then times the CPU port on it)
+    index = IVFFlatL2Index(dim, nlist, nprobe=nprobe)
+    index.train(first[:sh["train"]] if sh["train"] <= len(first) else
+                np.concatenate([first, rng.standard_normal((sh["train"] - len(first), dim), dtype=np.float32)]))
+    index.add(first)
+    done = len(first)
+    while done < n:
+        m = min(100_000, n - done)
+        index.add(rng.standard_normal((m, dim), dtype=np.float32))
+        done += m
+    sizes = index.list_sizes()
+    build_s = time.time() - t0
+    q = (first[rng.integers(0, min(len(first), 4096), B)] + 0.3 * rng.standard_normal((B, dim), dtype=np.float32)).astype(np.float32)
+
+    def cpu_leg(steps, warmup):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import c_oracle
+        szs, codes, ids = index.export_lists()
+        cent = index.centroids()
+        for _ in range(max(1, warmup)):
+            c_oracle.ivf_search_l2(q, cent, szs, codes, ids, k, nprobe)
+        ts = []
+        for _ in range(max(1, steps)):
+            t = time.perf_counter()
+            Dc, Ic = c_oracle.ivf_search_l2(q, cent, szs, codes, ids, k, nprobe)
+            ts.append(time.perf_counter() - t)
+        t = sum(ts) / len(ts)
+        return {"value": B / t, "unit": UNIT, "cores": c_oracle.max_threads(), "kind": "port",
+                "sample": (f"oracle/faiss_ivf_restatement.c (faiss-cpu IVF algorithm: OpenMP over queries, "
+                           f"coarse probe + list scan + k-heap) on the full index and the same {B} queries; "
+                           f"{t * 1e3:.1f} ms per search; host cpu_count={os.cpu_count()}"),
+                "ms": t * 1e3}, (Dc, Ic)
+
+    if reference:
+        cb, _ = cpu_leg(args.steps, min(args.warmup, 1))
+        line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": UNIT, "n_gpus": 1,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {k_: cb[k_] for k_ in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        os.dup2(saved_stdout, 1)
+        print(json.dumps(line), flush=True)
+        return
+
+    index.set_option("profile_events", 1)
+    qd = torch.from_numpy(q).cuda()
+    D = torch.empty((B, k), dtype=torch.float32, device="cuda")
+    I = torch.empty((B, k), dtype=torch.int64, device="cuda")
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        index.search_device(qd.data_ptr(), B, k, D.data_ptr(), I.data_ptr())
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches = scan_ns = 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        index.search_device(qd.data_ptr(), B, k, D.data_ptr(), I.data_ptr())
+        launches += index.stat("launches")
+        scan_ns += index.stat("scan_ns")
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / args.steps
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        Dh, Ih = index.search(q, k)
+    dt_e2e = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop()
+    peaks = load_peaks()
+    distinct = index.stat("distinct_rows")
+    alg_bytes = distinct * dim * 4 + nlist * dim * 4 + B * dim * 4 + B * k * 12
+    scan_s = scan_ns / args.steps * 1e-9
+    roof = {"bound": "hbm", "achieved": alg_bytes / scan_s / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "peak_source": f"{peaks['source']} (copy bandwidth)", "kernel": "ivf_scan_kernel",
+            "launch": {"scan_ms_per_search": scan_s * 1e3, "distinct_probed_rows": distinct,
+                       "rows_scanned": index.stat("rows_scanned"), "pairs_scored": index.stat("pairs_scored"),
+                       "tiles": index.stat("tiles"), "tiles16": index.stat("tiles16")},
+            "kernel_share_of_step": scan_s / dt, "whole_search_frac": alg_bytes / dt / 1e9 / peaks["hbm_gbs"],
+            "traffic": None}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    cb = None
+    verify = None
+    if keep_host:
+        cb, (Dc, Ic) = cpu_leg(1, 1)
+        verify = {"ids_equal_cpu_port": float((Ih == Ic).mean()),
+                  "max_rel_dist_err_vs_cpu_port": float(np.max(np.abs(Dh - Dc) / np.maximum(Dc, 1e-6)))}
+        cb = {k_: cb[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+    line = {"metric": metric, "value": B / dt, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": warm,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config, "clocks": clocks,
+            "e2e": {"value": B / dt_e2e, "unit": UNIT, "h2d_bytes_per_step": B * dim * 4,
+                    "d2h_bytes_per_step": B * k * 12, "api": "IVFFlatL2Index.search (fivf_search, host buffers)"},
+            "gpu_launches": launches, "roofline": roof, "cpu_baseline": cb,
+            "timing": "wall clock around the blocking search call (host plan and both synchronisations included)",
+            "list_sizes": {"min": int(sizes.min()), "mean": float(sizes.mean()), "max": int(sizes.max())},
+            "index_build_s": build_s, "verify": verify}
+    index.close()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
-    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="cfg3")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["ivf"], default="cfg3")
+    ap.add_argument("--ivf-train", type=int, default=0, help="--workload ivf: rows the quantizer is trained on")
     ap.add_argument("--rows", type=int, default=0, help="override total corpus rows")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--k", type=int, default=0)
@@ -411,6 +557,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     if world != args.gpus and world > 1:
         args.gpus = world
+    if args.workload == "ivf":
+        if rank == 0:
+            run_ivf(args)
+        return
     if args.impl == "reference":
         run_reference(args, rank, world)
         return

@@ -431,12 +431,20 @@ __global__ void max_norm_kernel(const float* __restrict__ xnorm, int64_t n, floa
 // The selects keep every candidate within 2 eps of the k-th best (select.cuh, "exactness window"),
 // ivf_rescore_kernel then evaluates sum (q - x)^2 directly (what faiss's IVFFlatScannerL2 computes,
 // no cancellation) and the final select ranks by that.
+// With `tf32` set (some lists go through the tensor-core kernel, tc_ivf.cuh) the bound also covers
+// the truncation of both operands to tf32 (2^-9 + 2^-20 relative to ||q|| ||x||) and the tensor
+// core's fp32 accumulation, on the doubled inner product.
 __global__ void ivf_eps_kernel(const float* __restrict__ qnorm, const float* __restrict__ x2max, int nq,
-                               int dim, float* __restrict__ eps, float* __restrict__ ones) {
+                               int dim, int tf32, float* __restrict__ eps, float* __restrict__ ones) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const float X2 = *x2max;
-    eps[q] = 1.01f * 5.9604645e-8f * (float)(dim + 1) * (2.0f * sqrtf(qnorm[q] * X2) + X2);
+    float e = 1.01f * 5.9604645e-8f * (float)(dim + 1) * (2.0f * sqrtf(qnorm[q] * X2) + X2);
+    if (tf32) {
+        const float rel = (float)dim * 1.1920929e-7f + 1.0f / 512 + 1.0f / 1048576;
+        e = fmaxf(e, 1.01f * (2.0f * rel * sqrtf(qnorm[q] * X2) + 5.9604645e-8f * (float)(dim + 1) * X2));
+    }
+    eps[q] = e;
     ones[q] = 1.0f;
 }
 

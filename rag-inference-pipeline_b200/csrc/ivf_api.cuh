@@ -21,6 +21,7 @@
 
 #include "../../include/ivfflat_b200.h"
 #include "ivf.cuh"
+#include "tc_ivf.cuh"
 
 struct fivf_index {
     int dim = 0, nlist = 0, device = 0, num_sms = 0;
@@ -43,7 +44,10 @@ struct fivf_index {
     CUtensorMap tmap_x{};
     bool tmap_valid = false;
     // options
-    int force_safe = 0, live_thr = 1, qb_max = 16;
+    int force_safe = 0, live_thr = 1, qb_max = 16, profile = 0;
+    int tc_min = 16;   // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
+    CUtensorMap tmap_x128{};   // SWIZZLE_128B map of the sorted storage (tensor-core kernel)
+    cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
     // workspace
     DevBuf<uint64_t> ckeys, cand;
     DevBuf<float> qnorm, probe_d, thr, sc, q32, out_d, stage, x2max, eps, ones;
@@ -52,13 +56,16 @@ struct fivf_index {
     DevBuf<ivf::TileQuery> tile_q;
     DevBuf<uint32_t> cnt, flags, hist, hbase;
     DevBuf<ivf::Tile> tiles;
+    DevBuf<ivf::TcItem> tc_items;
+    DevBuf<int32_t> qmap;
+    DevBuf<float> qprep;
     PinnedBuf<int64_t> h_probe, h_i;
     PinnedBuf<uint8_t> h_plan;
     PinnedBuf<uint32_t> h_flags;
     PinnedBuf<float> h_q, h_d;
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -175,7 +182,11 @@ struct IvfPlan {
     std::vector<Phase> phases;
     std::vector<ivf::Tile> tiles;
     std::vector<ivf::TileQuery> tile_q;
-    int64_t rows = 0, pairs = 0;
+    int64_t rows = 0, pairs = 0, distinct_rows = 0;   // distinct_rows: rows of the lists probed by >= 1 query
+    // tensor-core path (phase 1 of the normal mode only): 128-query groups of heavily probed lists
+    std::vector<ivf::TcItem> tc_items;
+    std::vector<int32_t> qmap;     // prepared-query row -> query number (-1 = padding)
+    int64_t tc_pairs = 0;
 };
 
 struct Seg { int32_t list; uint32_t r0, r1; int32_t q; uint32_t skip; };
@@ -189,7 +200,7 @@ struct Seg { int32_t list; uint32_t r0, r1; int32_t q; uint32_t skip; };
 //   safe mode: the probe sequence is cut into phases of `cap` (dense) / `cap - k` rows so that no
 //     candidate list can overflow; partial lists become single-query tiles.
 void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, int k, int cap,
-                bool safe, int qb_big, IvfPlan* plan) {
+                bool safe, int qb_big, int tc_min, IvfPlan* plan) {
     const int nlist = h->nlist;
     const std::vector<int64_t>& off = h->off;
     std::vector<std::vector<Seg>> whole, part;   // per phase
@@ -197,6 +208,13 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
         if (whole.size() <= p) { whole.resize(p + 1); part.resize(p + 1); }
     };
     const int64_t target0 = std::min<int64_t>(cap, std::max<int64_t>(4 * (int64_t)k, 256));
+    {
+        std::vector<uint8_t> seen((size_t)nlist, 0);
+        for (size_t i = 0; i < (size_t)nq * nprobe; ++i) {
+            const int64_t l = probes[i];
+            if (l >= 0 && l < nlist && !seen[(size_t)l]) { seen[(size_t)l] = 1; plan->distinct_rows += off[(size_t)l + 1] - off[l]; }
+        }
+    }
     for (int q = 0; q < nq; ++q) {
         if (!safe) {
             int64_t cum = 0;
@@ -265,6 +283,38 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
             const int m = lcount[(size_t)l + 1] - lcount[l];
             if (m == 0) continue;
             const int64_t len = off[(size_t)l + 1] - off[l];
+            if (p == 1 && !safe && tc_min > 0 && m >= tc_min) {
+                // heavily probed list: its queries that did not pre-scan part of it in phase 0 go to
+                // the tensor-core kernel in groups of up to 128 (moved to the front of the bucket)
+                ivf::TileQuery* b = lq.data() + lcount[l];
+                int nfree = (int)(std::stable_partition(b, b + m, [](const ivf::TileQuery& t) { return t.skip == 0; }) - b);
+                int taken = 0;
+                while (nfree - taken >= tc_min) {
+                    const int gq = std::min(128, nfree - taken);
+                    const uint32_t qrow0 = (uint32_t)plan->qmap.size();
+                    for (int i = 0; i < 128; ++i) plan->qmap.push_back(i < gq ? b[taken + i].q : -1);
+                    for (int64_t r = 0; r < len; r += tc::BN)
+                        plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len), qrow0, 0u});
+                    plan->rows += len;
+                    plan->pairs += len * gq;
+                    plan->tc_pairs += len * gq;
+                    taken += gq;
+                }
+                if (taken) {   // the rest of the bucket stays on the FFMA2 path
+                    for (int i = taken; i < m; ++i) b[i - taken] = b[i];
+                }
+                const int rest = m - taken;
+                for (int g0 = 0; g0 < rest;) {
+                    int gq = std::min(qb_big, rest - g0);
+                    const bool big = gq > 4;
+                    if (!big) gq = std::min(4, rest - g0);
+                    const uint32_t qoff = (uint32_t)plan->tile_q.size();
+                    for (int i = 0; i < gq; ++i) plan->tile_q.push_back(b[g0 + i]);
+                    emit(big ? t16 : t4, off[l], 0, len, qoff, (uint32_t)gq);
+                    g0 += gq;
+                }
+                continue;
+            }
             for (int g0 = 0; g0 < m;) {
                 int gq = std::min(qb_big, m - g0);
                 const bool big = gq > 4;
@@ -348,8 +398,6 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     if (h->n_sorted == 0) FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
     ivf::row_norm2_kernel<<<(nq + 7) / 8, 256, 0, h->stream>>>(q_dev, nq, dim, h->qnorm.p);
     FIP_CUDA(cudaGetLastError());
-    ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim, h->eps.p, h->ones.p);
-    FIP_CUDA(cudaGetLastError());
     init_lists_kernel<<<(nq + 256) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nq);
     FIP_CUDA(cudaGetLastError());
     // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
@@ -378,7 +426,8 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
     IvfPlan plan;
     const auto t0 = std::chrono::steady_clock::now();
-    build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, &plan);
+    const bool tc_ok = h->tc_min > 0 && dim % 32 == 0;
+    build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
     h->st_plan_us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
     const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
     FIP_CUDA(h->h_plan.ensure(tile_bytes + tq_bytes + 16));
@@ -391,6 +440,26 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     if (tq_bytes) {
         memcpy(h->h_plan.p + tile_bytes, plan.tile_q.data(), tq_bytes);
         FIP_CUDA(cudaMemcpyAsync(h->tile_q.p, h->h_plan.p + tile_bytes, tq_bytes, cudaMemcpyHostToDevice, h->stream));
+    }
+    const bool use_tc = !plan.tc_items.empty();
+    ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim, use_tc ? 1 : 0,
+                                                               h->eps.p, h->ones.p);
+    FIP_CUDA(cudaGetLastError());
+    CUtensorMap tmap_qg{};
+    if (use_tc) {   // prepared queries of the tensor-core groups + the item list
+        const size_t rows = plan.qmap.size();
+        FIP_CUDA(h->qmap.ensure(rows));
+        FIP_CUDA(h->qprep.ensure(rows * (size_t)dim));
+        FIP_CUDA(h->tc_items.ensure(plan.tc_items.size()));
+        FIP_CUDA(cudaMemcpyAsync(h->qmap.p, plan.qmap.data(), rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+        FIP_CUDA(cudaMemcpyAsync(h->tc_items.p, plan.tc_items.data(), plan.tc_items.size() * sizeof(ivf::TcItem),
+                                 cudaMemcpyHostToDevice, h->stream));
+        const int64_t vecs = (int64_t)rows * (dim / 4);
+        ivf::gather_queries_kernel<<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(q_dev, h->qmap.p, (int64_t)rows, dim, h->qprep.p);
+        FIP_CUDA(cudaGetLastError());
+        launches++;
+        int rc = make_tmap(&tmap_qg, h->qprep.p, kF32, dim, (uint64_t)rows);
+        if (rc) return rc;
     }
     FIP_CUDA(h->cand.ensure((size_t)nq * cap));
     if (live) {
@@ -410,6 +479,8 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS)
             return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+        int rc128 = make_tmap(&h->tmap_x128, h->x, kF32, dim, (uint64_t)h->n_sorted);
+        if (rc128) return rc128;
         h->tmap_valid = true;
     }
     // the coarse select used cnt / thr: reset the lists
@@ -426,12 +497,29 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     for (size_t p = 0; p < n_phases; ++p) {
         const IvfPlan::Phase& ph = plan.phases[p];
         a.dense = p == 0 ? 1 : 0;
+        const bool timed = h->profile && p < 4;
+        if (timed) {
+            if (!h->ev[0]) for (auto& e : h->ev) FIP_CUDA(cudaEventCreate(&e));
+            FIP_CUDA(cudaEventRecord(h->ev[2 * p], h->stream));
+        }
+        if (p == 1 && use_tc) {   // heavily probed lists: tcgen05 tiles
+            ivf::TcIvfArgs ta{};
+            ta.items = h->tc_items.p; ta.n_items = (int)plan.tc_items.size(); ta.qmap = h->qmap.p;
+            ta.xnorm = h->xnorm; ta.dim = dim; ta.lists = a.lists;
+            constexpr int smem = tc::Cfg<2, 1, 1>::SMEM_BYTES;
+            FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            const int grid = std::min(ta.n_items, h->num_sms);
+            ivf::tc_ivf_kernel<<<grid, ivf::TCI_THREADS, smem, h->stream>>>(tmap_qg, h->tmap_x128, ta);
+            FIP_CUDA(cudaGetLastError());
+            launches++;
+        }
         a.tiles = h->tiles.p + ph.t16_begin; a.n_tiles = (int)ph.t16_n;
         int rc = launch_ivf_scan<16>(h, a, &launches);
         if (rc) return rc;
         a.tiles = h->tiles.p + ph.t4_begin; a.n_tiles = (int)ph.t4_n;
         rc = launch_ivf_scan<4>(h, a, &launches);
         if (rc) return rc;
+        if (timed) FIP_CUDA(cudaEventRecord(h->ev[2 * p + 1], h->stream));
         rc = ivf_select(h, nq, k, cap, false, live, keep_max, &launches);
         if (rc) return rc;
     }
@@ -457,6 +545,15 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     *overflowed = h->h_flags.p[0] != 0;
     h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)plan.tiles.size();
     h->st_rows = plan.rows; h->st_pairs = plan.pairs; h->st_cap = cap;
+    h->st_distinct_rows = plan.distinct_rows;
+    h->st_tc_items = (int64_t)plan.tc_items.size(); h->st_tc_pairs = plan.tc_pairs;
+    h->st_scan_ns = 0;
+    if (h->profile)
+        for (size_t p = 0; p < n_phases && p < 4; ++p) {
+            float ms = 0.f;
+            FIP_CUDA(cudaEventElapsedTime(&ms, h->ev[2 * p], h->ev[2 * p + 1]));
+            h->st_scan_ns += (int64_t)(ms * 1e6);
+        }
     h->st_tiles16 = 0;
     for (const auto& ph : plan.phases) h->st_tiles16 += (int64_t)ph.t16_n;
     return FIP_OK;
@@ -529,8 +626,9 @@ void fivf_destroy(fivf_index* h) {
     h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
     h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
     h->doff.release(); h->assign.release(); h->tile_q.release(); h->cnt.release(); h->flags.release();
-    h->hist.release(); h->hbase.release(); h->tiles.release(); h->h_probe.release(); h->h_i.release();
+    h->hist.release(); h->hbase.release(); h->tiles.release(); h->tc_items.release(); h->qmap.release(); h->qprep.release(); h->h_probe.release(); h->h_i.release();
     h->h_plan.release(); h->h_flags.release(); h->h_q.release(); h->h_d.release();
+    for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -802,6 +900,8 @@ int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
     if (k == "force_safe") h->force_safe = (int)value;
     else if (k == "live_thresholds") h->live_thr = (int)value;
     else if (k == "max_queries_per_tile") h->qb_max = (int)value;
+    else if (k == "profile_events") h->profile = (int)value;
+    else if (k == "tensor_min_queries") h->tc_min = (int)value;
     else return fail(FIP_ERR_INVALID, "unknown option " + k);
     return FIP_OK;
 }
@@ -818,6 +918,10 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "overflow") return h->st_overflow;
     if (k == "candidate_capacity") return h->st_cap;
     if (k == "plan_us") return h->st_plan_us;
+    if (k == "distinct_rows") return h->st_distinct_rows;
+    if (k == "scan_ns") return h->st_scan_ns;
+    if (k == "tensor_items") return h->st_tc_items;
+    if (k == "tensor_pairs") return h->st_tc_pairs;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
 }

@@ -59,7 +59,7 @@ def main():
               f"tiles={index.stat('tiles')} (16-query: {index.stat('tiles16')}) rows_scanned={rows} "
               f"({rows * dim * 4 / dt / 1e9:.0f} GB/s of list bytes) pairs={pairs} ({pairs * dim / dt / 1e12:.2f} TFMA/s) "
               f"plan={index.stat('plan_us')} us launches={index.stat('launches')} phases={index.stat('phases')} "
-              f"overflow={index.stat('overflow')} occ16={index.stat('scan16_ctas_per_sm')}", flush=True)
+              f"overflow={index.stat('overflow')} tensor_items={index.stat('tensor_items')} tensor_pairs={index.stat('tensor_pairs')}", flush=True)
     index.close()
 
 

@@ -98,6 +98,32 @@ def test_ivf_safe_mode_and_fixed_thresholds_agree():
     index.close()
 
 
+def test_ivf_tensor_core_path_for_heavily_probed_lists():
+    """Lists probed by >= 16 queries of the batch go through the tcgen05 tile kernel (tf32 filter +
+    exactness window + exact rescoring): same results as the FFMA2-only path, bit for bit."""
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(60000, 256, 300, seed=21)
+    index = IVFFlatL2Index(256, 64)
+    index.train(x[:4000])
+    index.add(x)
+    D0, I0 = _check(index, q, 20, 16)
+    assert index.stat("tensor_items") > 0 and index.stat("tensor_pairs") > 0
+    index.set_option("tensor_min_queries", 0)
+    D1, I1 = index.search(q, 20, nprobe=16)
+    assert index.stat("tensor_items") == 0
+    assert np.array_equal(I0, I1) and np.array_equal(D0, D1)
+    index.set_option("tensor_min_queries", 16)
+    xc, qc = _data(30000, 64, 200, seed=22, clustered=True)   # large norms, small distances
+    index2 = IVFFlatL2Index(64, 16)
+    index2.train(xc[:2000])
+    index2.add(xc)
+    _check(index2, qc, 50, 8)
+    assert index2.stat("tensor_items") > 0
+    index.close()
+    index2.close()
+
+
 def test_ivf_incremental_add_ids_and_duplicates():
     from rag_inference_pipeline_b200 import IVFFlatL2Index
 
