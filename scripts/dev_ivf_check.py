@@ -23,6 +23,8 @@ def main():
     iters = int(sys.argv[7]) if len(sys.argv) > 7 else 10
     rng = np.random.default_rng(0)
     index = IVFFlatL2Index(dim, nlist, nprobe=nprobe)
+    if "IVF_TC_MIN" in os.environ:
+        index.set_option("tensor_min_queries", int(os.environ["IVF_TC_MIN"]))
     t = time.time()
     first = rng.standard_normal((min(n, 100000), dim), dtype=np.float32)
     ntrain = int(os.environ.get("IVF_TRAIN", 10000))
