@@ -71,7 +71,7 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
 
 /* options: "force_safe", "live_thresholds", "max_queries_per_tile" (4 or 16), "profile_events"
  * (1: CUDA events around the scan launches, read back as "scan_ns"), "tensor_min_queries" (a list
- * probed by at least this many queries of a batch is scored on the tensor cores; default 16, 0 = never).
+ * probed by at least this many queries of a batch is scored on the tensor cores; default 8, 0 = never).
  * stats of the last search: "launches", "phases", "tiles", "tiles16", "rows_scanned",
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
  * "tensor_items", "tensor_pairs", "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm". */

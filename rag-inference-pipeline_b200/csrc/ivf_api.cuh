@@ -45,7 +45,7 @@ struct fivf_index {
     bool tmap_valid = false;
     // options
     int force_safe = 0, live_thr = 1, qb_max = 16, profile = 0;
-    int tc_min = 16;   // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
+    int tc_min = 8;    // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
     CUtensorMap tmap_x128{};   // SWIZZLE_128B map of the sorted storage (tensor-core kernel)
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
     // workspace
@@ -208,6 +208,13 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
         if (whole.size() <= p) { whole.resize(p + 1); part.resize(p + 1); }
     };
     const int64_t target0 = std::min<int64_t>(cap, std::max<int64_t>(4 * (int64_t)k, 256));
+    if (!safe) {
+        phase_vecs(1);
+        whole[1].reserve((size_t)nq * nprobe);
+        part[0].reserve((size_t)nq * 2);
+        plan->tile_q.reserve((size_t)nq * nprobe / 2 + 64);
+        plan->qmap.reserve((size_t)nq * nprobe + 128);
+    }
     {
         std::vector<uint8_t> seen((size_t)nlist, 0);
         for (size_t i = 0; i < (size_t)nq * nprobe; ++i) {
@@ -288,18 +295,23 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
                 // the tensor-core kernel in groups of up to 128 (moved to the front of the bucket)
                 ivf::TileQuery* b = lq.data() + lcount[l];
                 int nfree = (int)(std::stable_partition(b, b + m, [](const ivf::TileQuery& t) { return t.skip == 0; }) - b);
-                int taken = 0;
+                int taken = 0, ngroups = 0;
+                const uint32_t qrow_first = (uint32_t)plan->qmap.size();
                 while (nfree - taken >= tc_min) {
                     const int gq = std::min(128, nfree - taken);
-                    const uint32_t qrow0 = (uint32_t)plan->qmap.size();
                     for (int i = 0; i < 128; ++i) plan->qmap.push_back(i < gq ? b[taken + i].q : -1);
-                    for (int64_t r = 0; r < len; r += tc::BN)
-                        plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len), qrow0, 0u});
                     plan->rows += len;
                     plan->pairs += len * gq;
                     plan->tc_pairs += len * gq;
                     taken += gq;
+                    ngroups++;
                 }
+                // row-tile major: the groups of one 256-row tile are adjacent items, i.e. run on
+                // different SMs at the same time, so the tile comes from HBM once and from L2 after
+                for (int64_t r = 0; r < len; r += tc::BN)
+                    for (int g = 0; g < ngroups; ++g)
+                        plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len),
+                                                             qrow_first + 128u * (uint32_t)g, 0u});
                 if (taken) {   // the rest of the bucket stays on the FFMA2 path
                     for (int i = taken; i < m; ++i) b[i - taken] = b[i];
                 }

@@ -113,7 +113,7 @@ def test_ivf_tensor_core_path_for_heavily_probed_lists():
     D1, I1 = index.search(q, 20, nprobe=16)
     assert index.stat("tensor_items") == 0
     assert np.array_equal(I0, I1) and np.array_equal(D0, D1)
-    index.set_option("tensor_min_queries", 16)
+    index.set_option("tensor_min_queries", 8)
     xc, qc = _data(30000, 64, 200, seed=22, clustered=True)   # large norms, small distances
     index2 = IVFFlatL2Index(64, 16)
     index2.train(xc[:2000])
@@ -122,6 +122,21 @@ def test_ivf_tensor_core_path_for_heavily_probed_lists():
     assert index2.stat("tensor_items") > 0
     index.close()
     index2.close()
+
+
+def test_ivf_empty_index_and_zero_query_warmup():
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(3000, 64, 4, seed=2)
+    index = IVFFlatL2Index(64, 8)
+    index.train(x[:500])
+    D, I = index.search(q, 5, nprobe=3)          # trained, nothing added yet: all padding
+    assert np.all(I == -1) and np.all(D == ivf_oracle.FLT_MAX)
+    index.add(x)
+    D, I = index.search(np.zeros((1, 64), np.float32), 1, nprobe=8)   # FAISSStore.load's warm-up call
+    assert I.shape == (1, 1) and 0 <= I[0, 0] < 3000
+    assert I[0, 0] == np.argmin((x.astype(np.float64) ** 2).sum(1))
+    index.close()
 
 
 def test_ivf_incremental_add_ids_and_duplicates():
