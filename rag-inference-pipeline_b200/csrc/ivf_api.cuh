@@ -58,6 +58,7 @@ struct fivf_index {
     DevBuf<ivf::Tile> tiles;
     DevBuf<ivf::TcItem> tc_items;
     DevBuf<int32_t> qmap;
+    DevBuf<uint32_t> qskip;
     DevBuf<float> qprep;
     PinnedBuf<int64_t> h_probe, h_i;
     PinnedBuf<uint8_t> h_plan;
@@ -186,6 +187,7 @@ struct IvfPlan {
     // tensor-core path (phase 1 of the normal mode only): 128-query groups of heavily probed lists
     std::vector<ivf::TcItem> tc_items;
     std::vector<int32_t> qmap;     // prepared-query row -> query number (-1 = padding)
+    std::vector<uint32_t> qskip;   // prepared-query row -> TileQuery::skip
     int64_t tc_pairs = 0;
 };
 
@@ -291,15 +293,18 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
             if (m == 0) continue;
             const int64_t len = off[(size_t)l + 1] - off[l];
             if (p == 1 && !safe && tc_min > 0 && m >= tc_min) {
-                // heavily probed list: its queries that did not pre-scan part of it in phase 0 go to
-                // the tensor-core kernel in groups of up to 128 (moved to the front of the bucket)
+                // heavily probed list: its queries go to the tensor-core kernel in groups of up to 128
+                // (a query that pre-scanned the head of the list in phase 0 carries its skip count)
                 ivf::TileQuery* b = lq.data() + lcount[l];
-                int nfree = (int)(std::stable_partition(b, b + m, [](const ivf::TileQuery& t) { return t.skip == 0; }) - b);
+                const int nfree = m;
                 int taken = 0, ngroups = 0;
                 const uint32_t qrow_first = (uint32_t)plan->qmap.size();
-                while (nfree - taken >= tc_min) {
+                while (taken < nfree) {   // the last group may be small: its tile comes from L2 anyway
                     const int gq = std::min(128, nfree - taken);
-                    for (int i = 0; i < 128; ++i) plan->qmap.push_back(i < gq ? b[taken + i].q : -1);
+                    for (int i = 0; i < 128; ++i) {
+                        plan->qmap.push_back(i < gq ? b[taken + i].q : -1);
+                        plan->qskip.push_back(i < gq ? b[taken + i].skip : 0u);
+                    }
                     plan->rows += len;
                     plan->pairs += len * gq;
                     plan->tc_pairs += len * gq;
@@ -311,7 +316,7 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
                 for (int64_t r = 0; r < len; r += tc::BN)
                     for (int g = 0; g < ngroups; ++g)
                         plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len),
-                                                             qrow_first + 128u * (uint32_t)g, 0u});
+                                                             qrow_first + 128u * (uint32_t)g, (uint32_t)off[l]});
                 if (taken) {   // the rest of the bucket stays on the FFMA2 path
                     for (int i = taken; i < m; ++i) b[i - taken] = b[i];
                 }
@@ -463,7 +468,9 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         FIP_CUDA(h->qmap.ensure(rows));
         FIP_CUDA(h->qprep.ensure(rows * (size_t)dim));
         FIP_CUDA(h->tc_items.ensure(plan.tc_items.size()));
+        FIP_CUDA(h->qskip.ensure(rows));
         FIP_CUDA(cudaMemcpyAsync(h->qmap.p, plan.qmap.data(), rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+        FIP_CUDA(cudaMemcpyAsync(h->qskip.p, plan.qskip.data(), rows * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
         FIP_CUDA(cudaMemcpyAsync(h->tc_items.p, plan.tc_items.data(), plan.tc_items.size() * sizeof(ivf::TcItem),
                                  cudaMemcpyHostToDevice, h->stream));
         const int64_t vecs = (int64_t)rows * (dim / 4);
@@ -516,7 +523,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         }
         if (p == 1 && use_tc) {   // heavily probed lists: tcgen05 tiles
             ivf::TcIvfArgs ta{};
-            ta.items = h->tc_items.p; ta.n_items = (int)plan.tc_items.size(); ta.qmap = h->qmap.p;
+            ta.items = h->tc_items.p; ta.n_items = (int)plan.tc_items.size(); ta.qmap = h->qmap.p; ta.qskip = h->qskip.p;
             ta.xnorm = h->xnorm; ta.dim = dim; ta.lists = a.lists;
             constexpr int smem = tc::Cfg<2, 1, 1>::SMEM_BYTES;
             FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -638,7 +645,7 @@ void fivf_destroy(fivf_index* h) {
     h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
     h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
     h->doff.release(); h->assign.release(); h->tile_q.release(); h->cnt.release(); h->flags.release();
-    h->hist.release(); h->hbase.release(); h->tiles.release(); h->tc_items.release(); h->qmap.release(); h->qprep.release(); h->h_probe.release(); h->h_i.release();
+    h->hist.release(); h->hbase.release(); h->tiles.release(); h->tc_items.release(); h->qmap.release(); h->qskip.release(); h->qprep.release(); h->h_probe.release(); h->h_i.release();
     h->h_plan.release(); h->h_flags.release(); h->h_q.release(); h->h_d.release();
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);

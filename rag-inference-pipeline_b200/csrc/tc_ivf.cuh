@@ -24,12 +24,13 @@ struct TcItem {
     uint32_t row0;      // first list position of the tile (sorted storage)
     uint32_t row_end;   // end of the list segment (tile covers [row0, min(row0 + 256, row_end)))
     uint32_t qrow0;     // first row of the 128-query group in the prepared-query matrix
-    uint32_t pad;
+    uint32_t list0;     // first position of the list (TileQuery::skip counts rows from here)
 };
 struct TcIvfArgs {
     const TcItem* items;
     int n_items;
     const int32_t* qmap;     // [prepared rows] query number, -1 = padding
+    const uint32_t* qskip;   // [prepared rows] rows of the list this query already scored in phase 0
     const float* xnorm;      // [N]
     int dim;
     ScanArgs lists;          // thr / cnt / cand / cap / hist / hbase / k_thr / win_* (common.cuh)
@@ -43,8 +44,13 @@ constexpr int TCI_CHUNKS = tc::BN / 32 / (TCI_EPI_WARPS / 4);
 // Same two-pass scheme as tc::epilogue_filter (pass 1 builds per-chunk masks, ONE atomicAdd
 // reserves the slots, pass 2 re-reads the chunks that had survivors), with the norm bias applied.
 __device__ __forceinline__ void tci_load_chunk(const TcIvfArgs& a, uint32_t taddr, int c, uint32_t row_base,
-                                               uint32_t row_end, float (&v)[32]) {
+                                               uint32_t row_end, uint32_t row_min, float (&v)[32]) {
     tc::tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+    if (row_base < row_min) {   // this query pre-scanned the head of the list in phase 0 (rare)
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (row_base + j < row_min) v[j] = kNegInf;
+    }
     // every lane reads the same norm: one broadcast transaction per load (lists start at arbitrary
     // positions, so the norms cannot be fetched as aligned vectors); rows past the list are dropped
 #pragma unroll
@@ -53,7 +59,7 @@ __device__ __forceinline__ void tci_load_chunk(const TcIvfArgs& a, uint32_t tadd
 }
 
 __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr, int q, float thr, uint32_t hb,
-                                             uint32_t tile_row0, uint32_t row_end, int c0) {
+                                             uint32_t tile_row0, uint32_t row_end, uint32_t row_min, int c0) {
     static_assert(TCI_CHUNKS <= 4, "masks are packed into two 64-bit registers");
     uint64_t m01 = 0ull, m23 = 0ull;
     uint32_t n = 0;
@@ -63,7 +69,7 @@ __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr,
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
         if (row_base >= row_end) break;  // warp-uniform
         float v[32];
-        tci_load_chunk(a, taddr, c, row_base, row_end, v);
+        tci_load_chunk(a, taddr, c, row_base, row_end, row_min, v);
         uint32_t mask = 0u;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -95,7 +101,7 @@ __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr,
         const int c = c0 + ci;
         const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
         float v[32];
-        tci_load_chunk(a, taddr, c, row_base, row_end, v);
+        tci_load_chunk(a, taddr, c, row_base, row_end, row_min, v);
         const uint32_t inv_row0 = 0xFFFFFFFFu - row_base;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -201,12 +207,13 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const int buf = n & 1;
             const uint32_t aph = (uint32_t)(n >> 1) & 1u;
             const int q = a.qmap[it.qrow0 + w * 32 + lane];
+            const uint32_t row_min = it.list0 + a.qskip[it.qrow0 + w * 32 + lane];
             const float thr = q >= 0 ? __ldcg(a.lists.thr + q) : __builtin_huge_valf();
             const uint32_t hb = (q >= 0 && a.lists.hist) ? __ldcg(a.lists.hbase + q) : 0u;
             tc::mbar_wait(tfull_bar(buf), aph);
             tc::tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * tc::BN;
-            tci_epilogue(a, taddr, q, thr, hb, it.row0, it.row_end, c0);
+            tci_epilogue(a, taddr, q, thr, hb, it.row0, it.row_end, row_min, c0);
             tc::tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(tempty_bar(buf));
