@@ -298,25 +298,33 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
                 ivf::TileQuery* b = lq.data() + lcount[l];
                 const int nfree = m;
                 int taken = 0, ngroups = 0;
-                const uint32_t qrow_first = (uint32_t)plan->qmap.size();
+                uint32_t g_qrow0[64], g_qrows[64];   // a list has at most nq / 128 + 1 groups per round
                 while (taken < nfree) {   // the last group may be small: its tile comes from L2 anyway
                     const int gq = std::min(128, nfree - taken);
-                    for (int i = 0; i < 128; ++i) {
-                        plan->qmap.push_back(i < gq ? b[taken + i].q : -1);
-                        plan->qskip.push_back(i < gq ? b[taken + i].skip : 0u);
+                    const int padded = (gq + 31) / 32 * 32;
+                    const size_t base = plan->qmap.size();
+                    plan->qmap.resize(base + (size_t)padded, -1);
+                    plan->qskip.resize(base + (size_t)padded, 0u);
+                    for (int i = 0; i < gq; ++i) {
+                        plan->qmap[base + (size_t)i] = b[taken + i].q;
+                        plan->qskip[base + (size_t)i] = b[taken + i].skip;
                     }
                     plan->rows += len;
                     plan->pairs += len * gq;
                     plan->tc_pairs += len * gq;
                     taken += gq;
-                    ngroups++;
+                    g_qrow0[ngroups] = (uint32_t)base;
+                    g_qrows[ngroups] = (uint32_t)padded;
+                    if (++ngroups == 64 || taken == nfree) {
+                        // row-tile major: the groups of one 256-row tile are adjacent items, i.e. run
+                        // on different SMs at the same time: the tile comes from HBM once, then from L2
+                        for (int64_t r = 0; r < len; r += tc::BN)
+                            for (int g = 0; g < ngroups; ++g)
+                                plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len),
+                                                                     g_qrow0[g], (uint32_t)off[l], g_qrows[g]});
+                        ngroups = 0;
+                    }
                 }
-                // row-tile major: the groups of one 256-row tile are adjacent items, i.e. run on
-                // different SMs at the same time, so the tile comes from HBM once and from L2 after
-                for (int64_t r = 0; r < len; r += tc::BN)
-                    for (int g = 0; g < ngroups; ++g)
-                        plan->tc_items.push_back(ivf::TcItem{(uint32_t)(off[l] + r), (uint32_t)(off[l] + len),
-                                                             qrow_first + 128u * (uint32_t)g, (uint32_t)off[l]});
                 if (taken) {   // the rest of the bucket stays on the FFMA2 path
                     for (int i = taken; i < m; ++i) b[i - taken] = b[i];
                 }
@@ -477,8 +485,19 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         ivf::gather_queries_kernel<<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(q_dev, h->qmap.p, (int64_t)rows, dim, h->qprep.p);
         FIP_CUDA(cudaGetLastError());
         launches++;
-        int rc = make_tmap(&tmap_qg, h->qprep.p, kF32, dim, (uint64_t)rows);
-        if (rc) return rc;
+        {   // [rows, dim] fp32, box = 32 floats x 32 rows, SWIZZLE_128B
+            EncodeTiledFn enc = get_encode_fn();
+            if (!enc) return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+            cuuint64_t dims[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+            cuuint64_t strides[1] = {(cuuint64_t)dim * 4};
+            cuuint32_t box[2] = {32u, 32u};
+            cuuint32_t estr[2] = {1, 1};
+            CUresult r = enc(&tmap_qg, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, h->qprep.p, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS)
+                return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+        }
     }
     FIP_CUDA(h->cand.ensure((size_t)nq * cap));
     if (live) {

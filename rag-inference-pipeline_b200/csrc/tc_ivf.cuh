@@ -25,6 +25,7 @@ struct TcItem {
     uint32_t row_end;   // end of the list segment (tile covers [row0, min(row0 + 256, row_end)))
     uint32_t qrow0;     // first row of the 128-query group in the prepared-query matrix
     uint32_t list0;     // first position of the list (TileQuery::skip counts rows from here)
+    uint32_t qrows;     // prepared rows of the group: its query count rounded up to 32 (<= 128)
 };
 struct TcIvfArgs {
     const TcItem* items;
@@ -121,8 +122,11 @@ __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr,
                                 (int)(threadIdx.x & 31));
 }
 
-// tmap_q: prepared queries [groups * 128, dim] fp32 (read as tf32); tmap_x: sorted list storage
-// [N, dim] fp32.  Both use make_tmap's [32 floats x 128 rows] SWIZZLE_128B boxes.
+// tmap_q: prepared queries [sum of qrows, dim] fp32 (read as tf32), [32 floats x 32 rows]
+// SWIZZLE_128B boxes: a group occupies qrows (a multiple of 32, <= 128) rows and only those are
+// loaded; the rest of the 128-row A tile keeps stale shared memory, whose (garbage) accumulator
+// lanes belong to no query.  tmap_x: sorted list storage [N, dim] fp32, make_tmap's
+// [32 floats x 128 rows] boxes.
 __global__ void __launch_bounds__(TCI_THREADS, 1)
 tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, TcIvfArgs a) {
     using C = tc::Cfg<2, 1, 1>;
@@ -164,8 +168,9 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                 for (int kb = 0; kb < nkb; ++kb) {
                     tc::mbar_wait(empty_bar(s), ph ^ 1u);
                     const uint32_t sa = base + s * STAGE_BYTES;
-                    tc::mbar_arrive_expect_tx(full_bar(s), STAGE_BYTES);
-                    tc::tma_load_2d(sa, &tmap_q, full_bar(s), kb * C::BK, (int)it.qrow0);
+                    tc::mbar_arrive_expect_tx(full_bar(s), tc::B_BYTES + it.qrows * tc::BK_BYTES);
+                    for (uint32_t r = 0; r < it.qrows; r += 32)
+                        tc::tma_load_2d(sa + r * tc::BK_BYTES, &tmap_q, full_bar(s), kb * C::BK, (int)(it.qrow0 + r));
                     tc::tma_load_2d(sa + B_OFF, &tmap_x, full_bar(s), kb * C::BK, (int)it.row0);
                     tc::tma_load_2d(sa + B_OFF + tc::BOX_ROWS * tc::BK_BYTES, &tmap_x, full_bar(s), kb * C::BK,
                                     (int)it.row0 + tc::BOX_ROWS);
@@ -206,8 +211,9 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const TcItem it = a.items[t];
             const int buf = n & 1;
             const uint32_t aph = (uint32_t)(n >> 1) & 1u;
-            const int q = a.qmap[it.qrow0 + w * 32 + lane];
-            const uint32_t row_min = it.list0 + a.qskip[it.qrow0 + w * 32 + lane];
+            const uint32_t qr = (uint32_t)(w * 32 + lane);
+            const int q = qr < it.qrows ? a.qmap[it.qrow0 + qr] : -1;
+            const uint32_t row_min = it.list0 + (qr < it.qrows ? a.qskip[it.qrow0 + qr] : 0u);
             const float thr = q >= 0 ? __ldcg(a.lists.thr + q) : __builtin_huge_valf();
             const uint32_t hb = (q >= 0 && a.lists.hist) ? __ldcg(a.lists.hbase + q) : 0u;
             tc::mbar_wait(tfull_bar(buf), aph);
