@@ -58,6 +58,7 @@ def _check(index, q, k, nprobe):
     (6000, 96, 64, 5, 50, 1),           # k > rows of the probed list: padding
     (20000, 64, 2, 9, 10, 1),           # lists longer than the candidate capacity: split segments
     (5000, 32, 16, 1, 1, 16),           # nprobe == nlist: exhaustive
+    (50000, 64, 16, 20, 1024, 8),       # large k: 16 K-entry candidate lists, dense phase of 16 K rows
 ])
 def test_ivf_search_matches_oracle(n, d, nlist, nq, k, nprobe):
     from rag_inference_pipeline_b200 import IVFFlatL2Index
