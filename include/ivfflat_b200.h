@@ -74,7 +74,8 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
  * probed by at least this many queries of a batch is scored on the tensor cores; default 8, 0 = never).
  * stats of the last search: "launches", "phases", "tiles", "tiles16", "rows_scanned",
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
- * "tensor_items", "tensor_pairs", "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm". */
+ * "tensor_items", "tensor_pairs", "crowded_window" (1: the tf32 filter's exactness window overflowed
+ * for some query and the batch was redone with the fp32 filter), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm". */
 int fivf_set_option(fivf_index* h, const char* key, int64_t value);
 int64_t fivf_get_stat(const fivf_index* h, const char* key);
 

@@ -66,7 +66,7 @@ struct fivf_index {
     PinnedBuf<float> h_q, h_d;
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -403,7 +403,7 @@ int ivf_select(fivf_index* h, int nq, int k, int cap, bool final_pass, bool live
 // One search of device-resident queries; results to device out_d / out_i.  Synchronises (the probe
 // table is planned on the host).  *overflowed = some candidate list overflowed (redo in safe mode).
 int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float* out_d, int64_t* out_i,
-             bool safe, bool* overflowed) {
+             bool safe, bool allow_tc, bool* overflowed, bool* crowded) {
     const int dim = h->dim, nlist = h->nlist;
     int launches = 0;
     nprobe = std::max(1, std::min(nprobe, nlist));
@@ -451,7 +451,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
     IvfPlan plan;
     const auto t0 = std::chrono::steady_clock::now();
-    const bool tc_ok = h->tc_min > 0 && dim % 32 == 0;
+    const bool tc_ok = allow_tc && h->tc_min > 0 && dim % 32 == 0;
     build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
     h->st_plan_us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
     const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
@@ -579,8 +579,12 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     launches++;
     FIP_CUDA(h->h_flags.ensure(4));
     FIP_CUDA(cudaMemcpyAsync(h->h_flags.p, h->flags.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaMemcpyAsync(h->h_flags.p + 1, h->flags.p + (nq + 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
     FIP_CUDA(cudaStreamSynchronize(h->stream));
     *overflowed = h->h_flags.p[0] != 0;
+    // some query's exactness window held more than keep_max candidates and was truncated; with the
+    // tf32 filter in play the caller redoes the batch on the (much narrower) fp32 window
+    *crowded = h->h_flags.p[1] != 0 && use_tc;
     h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)plan.tiles.size();
     h->st_rows = plan.rows; h->st_pairs = plan.pairs; h->st_cap = cap;
     h->st_distinct_rows = plan.distinct_rows;
@@ -601,12 +605,17 @@ int fivf_search_checked(fivf_index* h, const float* q_dev, int nq, int k, int np
                         int64_t* out_i) {
     int rc = fivf_rebuild(h);
     if (rc) return rc;
-    bool over = false;
-    rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, h->force_safe != 0, &over);
+    bool over = false, crowded = false;
+    rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, h->force_safe != 0, true, &over, &crowded);
     if (rc) return rc;
     h->st_overflow = over ? 1 : 0;
+    h->st_crowded = crowded ? 1 : 0;
+    if (crowded && !over) {   // near-tie clusters tighter than tf32 resolves: FFMA2 (fp32) filter only
+        rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, h->force_safe != 0, false, &over, &crowded);
+        if (rc) return rc;
+    }
     if (over) {
-        rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, true, &over);
+        rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, true, false, &over, &crowded);
         if (rc) return rc;
         if (over) return fail(FIP_ERR_STATE, "internal error: IVF safe mode overflowed a candidate list");
     }
@@ -960,6 +969,7 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "scan_ns") return h->st_scan_ns;
     if (k == "tensor_items") return h->st_tc_items;
     if (k == "tensor_pairs") return h->st_tc_pairs;
+    if (k == "crowded_window") return h->st_crowded;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
 }
