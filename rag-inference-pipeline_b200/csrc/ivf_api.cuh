@@ -64,6 +64,7 @@ struct fivf_index {
     PinnedBuf<uint8_t> h_plan;
     PinnedBuf<uint32_t> h_flags;
     PinnedBuf<float> h_q, h_d;
+    void* plan_ws = nullptr;   // IvfPlan: host plan workspace, reused by every search (build_plan)
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
             st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0;
@@ -178,6 +179,12 @@ namespace {
 
 // ------------------------------------------------------------------------------------------
 // Host plan: invert the probe table into list-major tiles, phase by phase.
+struct Seg { int32_t list; uint32_t r0, r1; int32_t q; uint32_t skip; };
+struct IvfPlan;
+void fivf_free_plan(void* p);
+
+// Lives in the index and is reused by every search: the vectors keep their capacity, so planning
+// costs no allocations (fresh multi-megabyte vectors meant mmap + page faults on every call).
 struct IvfPlan {
     struct Phase { size_t t16_begin = 0, t16_n = 0, t4_begin = 0, t4_n = 0; };
     std::vector<Phase> phases;
@@ -189,9 +196,23 @@ struct IvfPlan {
     std::vector<int32_t> qmap;     // prepared-query row -> query number (-1 = padding)
     std::vector<uint32_t> qskip;   // prepared-query row -> TileQuery::skip
     int64_t tc_pairs = 0;
+    // scratch of build_plan
+    std::vector<std::vector<Seg>> whole, part;   // per phase
+    std::vector<int32_t> lcount, cur;
+    std::vector<ivf::TileQuery> lq;
+    std::vector<ivf::Tile> t16, t4;
+    std::vector<uint8_t> seen;
+    void reset() {
+        phases.clear(); tiles.clear(); tile_q.clear(); tc_items.clear(); qmap.clear(); qskip.clear();
+        rows = pairs = distinct_rows = tc_pairs = 0;
+        for (auto& v : whole) v.clear();
+        for (auto& v : part) v.clear();
+        lq.clear(); t16.clear(); t4.clear();
+    }
 };
 
-struct Seg { int32_t list; uint32_t r0, r1; int32_t q; uint32_t skip; };
+
+void fivf_free_plan(void* p) { delete static_cast<IvfPlan*>(p); }
 
 // probes: [nq, nprobe] list numbers (-1 = none).
 //   normal mode: phase 0 (dense) scans only the first `target0` rows of each query's probe
@@ -205,7 +226,9 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
                 bool safe, int qb_big, int tc_min, IvfPlan* plan) {
     const int nlist = h->nlist;
     const std::vector<int64_t>& off = h->off;
-    std::vector<std::vector<Seg>> whole, part;   // per phase
+    plan->reset();
+    std::vector<std::vector<Seg>>& whole = plan->whole;
+    std::vector<std::vector<Seg>>& part = plan->part;
     auto phase_vecs = [&](size_t p) {
         if (whole.size() <= p) { whole.resize(p + 1); part.resize(p + 1); }
     };
@@ -214,11 +237,19 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
         phase_vecs(1);
         whole[1].reserve((size_t)nq * nprobe);
         part[0].reserve((size_t)nq * 2);
-        plan->tile_q.reserve((size_t)nq * nprobe / 2 + 64);
-        plan->qmap.reserve((size_t)nq * nprobe + 128);
+        const size_t pairs_max = (size_t)nq * nprobe;
+        plan->tile_q.reserve(pairs_max + (size_t)nq * 2 + 64);
+        if (tc_min > 0) {
+            const size_t rows_max = pairs_max + 32 * std::min<size_t>((size_t)nlist, pairs_max);
+            plan->qmap.reserve(rows_max);
+            plan->qskip.reserve(rows_max);
+            plan->tc_items.reserve(pairs_max / 4 + 1024);
+        }
+        plan->tiles.reserve(pairs_max / 4 + (size_t)nq * 2 + 1024);
     }
     {
-        std::vector<uint8_t> seen((size_t)nlist, 0);
+        std::vector<uint8_t>& seen = plan->seen;
+        seen.assign((size_t)nlist, 0);
         for (size_t i = 0; i < (size_t)nq * nprobe; ++i) {
             const int64_t l = probes[i];
             if (l >= 0 && l < nlist && !seen[(size_t)l]) { seen[(size_t)l] = 1; plan->distinct_rows += off[(size_t)l + 1] - off[l]; }
@@ -265,10 +296,15 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
             }
         }
     }
-    plan->phases.assign(whole.size(), IvfPlan::Phase{});
-    std::vector<int32_t> lcount((size_t)nlist + 1);
-    std::vector<ivf::TileQuery> lq;
-    std::vector<ivf::Tile> t16, t4;
+    size_t n_phases = whole.size();
+    while (n_phases > 0 && whole[n_phases - 1].empty() && part[n_phases - 1].empty() && n_phases > 2) n_phases--;
+    plan->phases.assign(n_phases, IvfPlan::Phase{});
+    std::vector<int32_t>& lcount = plan->lcount;
+    lcount.assign((size_t)nlist + 1, 0);
+    std::vector<ivf::TileQuery>& lq = plan->lq;
+    std::vector<ivf::Tile>& t16 = plan->t16;
+    std::vector<ivf::Tile>& t4 = plan->t4;
+    t16.reserve(4096); t4.reserve(4096);
     auto emit = [&](std::vector<ivf::Tile>& dst, int64_t list0, int64_t r0, int64_t r1, uint32_t qoff, uint32_t gq) {
         for (int64_t r = r0; r < r1; r += ivf::SC_ROWS) {
             const uint32_t nr = (uint32_t)std::min<int64_t>(ivf::SC_ROWS, r1 - r);
@@ -277,7 +313,7 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
             plan->pairs += (int64_t)nr * gq;
         }
     };
-    for (size_t p = 0; p < whole.size(); ++p) {
+    for (size_t p = 0; p < n_phases; ++p) {
         t16.clear(); t4.clear();
         // whole-list segments: bucket the queries by list (counting sort, O(pairs + nlist))
         std::fill(lcount.begin(), lcount.end(), 0);
@@ -285,7 +321,8 @@ void build_plan(const fivf_index* h, const int64_t* probes, int nq, int nprobe, 
         for (int l = 0; l < nlist; ++l) lcount[(size_t)l + 1] += lcount[l];
         lq.resize(whole[p].size());
         {
-            std::vector<int32_t> cur(lcount.begin(), lcount.end() - 1);
+            std::vector<int32_t>& cur = plan->cur;
+            cur.assign(lcount.begin(), lcount.end() - 1);
             for (const Seg& s : whole[p]) lq[(size_t)cur[s.list]++] = ivf::TileQuery{s.q, s.skip};
         }
         for (int l = 0; l < nlist; ++l) {
@@ -449,7 +486,8 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     const bool live = h->live_thr && !safe;
     const int keep_max = std::min(cap / 2, 2 * k + 64);   // truncation limit of the exactness window
     const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
-    IvfPlan plan;
+    if (!h->plan_ws) h->plan_ws = new IvfPlan();
+    IvfPlan& plan = *static_cast<IvfPlan*>(h->plan_ws);
     const auto t0 = std::chrono::steady_clock::now();
     const bool tc_ok = allow_tc && h->tc_min > 0 && dim % 32 == 0;
     build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
@@ -675,6 +713,7 @@ void fivf_destroy(fivf_index* h) {
     h->doff.release(); h->assign.release(); h->tile_q.release(); h->cnt.release(); h->flags.release();
     h->hist.release(); h->hbase.release(); h->tiles.release(); h->tc_items.release(); h->qmap.release(); h->qskip.release(); h->qprep.release(); h->h_probe.release(); h->h_i.release();
     h->h_plan.release(); h->h_flags.release(); h->h_q.release(); h->h_d.release();
+    fivf_free_plan(h->plan_ws);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -975,3 +1014,70 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Test hook (no GPU needed): runs the host planner on a synthetic probe table and checks its
+// invariant -- every (query, probed list) pair is scored over exactly the rows of that list, once
+// (dense prefix + skip-aware main phase, FFMA2 tiles + tensor items) -- and times it.
+// sizes [nlist]; probes [nq, nprobe] (list numbers, -1 = none, no duplicates within a query).
+// out[0..7] = phases, tiles, tensor_items, rows, pairs, plan_us (best of iters), bad_pairs, qmap_rows.
+extern "C" int fivf_debug_plan(int32_t nlist, const int64_t* sizes, const int64_t* probes, int32_t nq,
+                               int32_t nprobe, int32_t k, int32_t cap, int32_t safe, int32_t tc_min,
+                               int32_t iters, int64_t* out) {
+    if (nlist < 1 || !sizes || !probes || !out || nq < 1 || nprobe < 1 || k < 1 || cap < k) return FIP_ERR_INVALID;
+    fivf_index h;
+    h.nlist = nlist;
+    h.off.assign((size_t)nlist + 1, 0);
+    for (int l = 0; l < nlist; ++l) h.off[(size_t)l + 1] = h.off[l] + sizes[l];
+    IvfPlan plan;
+    int64_t best = INT64_MAX;
+    for (int it = 0; it < std::max(1, iters); ++it) {
+        const auto t0 = std::chrono::steady_clock::now();
+        build_plan(&h, probes, nq, nprobe, k, cap, safe != 0, 16, tc_min, &plan);
+        best = std::min<int64_t>(best, std::chrono::duration_cast<std::chrono::microseconds>(
+                                           std::chrono::steady_clock::now() - t0).count());
+    }
+    // coverage[q][j] = rows of probes[q][j] scored for q
+    std::vector<int64_t> cov((size_t)nq * nprobe, 0);
+    auto list_of = [&](uint32_t pos) {
+        return (int)(std::upper_bound(h.off.begin(), h.off.end(), (int64_t)pos) - h.off.begin()) - 1;
+    };
+    auto credit = [&](int q, int l, int64_t rows) -> bool {
+        for (int j = 0; j < nprobe; ++j)
+            if (probes[(size_t)q * nprobe + j] == l) { cov[(size_t)q * nprobe + j] += rows; return true; }
+        return false;
+    };
+    int64_t bad = 0;
+    for (const ivf::Tile& t : plan.tiles) {
+        const int l = list_of(t.row0);
+        if (t.nrows == 0 || t.nrows > (uint32_t)ivf::SC_ROWS || t.nq == 0 || t.nq > 16 ||
+            (int64_t)t.row0 + t.nrows > h.off[(size_t)l + 1] || (int64_t)t.row0 - t.rel0 != h.off[l]) { bad++; continue; }
+        for (uint32_t i = 0; i < t.nq; ++i) {
+            const ivf::TileQuery tq = plan.tile_q[t.qoff + i];
+            const int64_t lo = std::max<int64_t>(t.rel0, tq.skip), hi = (int64_t)t.rel0 + t.nrows;
+            if (!credit(tq.q, l, std::max<int64_t>(0, hi - lo))) bad++;
+        }
+    }
+    for (const ivf::TcItem& t : plan.tc_items) {
+        const int l = list_of(t.row0);
+        if ((int64_t)t.list0 != h.off[l] || (int64_t)t.row_end != h.off[(size_t)l + 1] || t.qrows == 0 || t.qrows > 128 ||
+            t.qrows % 32 != 0 || t.qrow0 + t.qrows > plan.qmap.size()) { bad++; continue; }
+        const int64_t r0 = (int64_t)t.row0 - t.list0, r1 = std::min<int64_t>(r0 + tc::BN, (int64_t)t.row_end - t.list0);
+        for (uint32_t i = 0; i < t.qrows; ++i) {
+            const int q = plan.qmap[t.qrow0 + i];
+            if (q < 0) continue;
+            const int64_t lo = std::max<int64_t>(r0, plan.qskip[t.qrow0 + i]);
+            if (!credit(q, l, std::max<int64_t>(0, r1 - lo))) bad++;
+        }
+    }
+    // dense-phase prefixes were credited through their own tiles; every pair must now be complete
+    for (int q = 0; q < nq; ++q)
+        for (int j = 0; j < nprobe; ++j) {
+            const int64_t l = probes[(size_t)q * nprobe + j];
+            const int64_t want = (l >= 0 && l < nlist) ? sizes[l] : 0;
+            if (cov[(size_t)q * nprobe + j] != want) bad++;
+        }
+    out[0] = (int64_t)plan.phases.size(); out[1] = (int64_t)plan.tiles.size(); out[2] = (int64_t)plan.tc_items.size();
+    out[3] = plan.rows; out[4] = plan.pairs; out[5] = best; out[6] = bad; out[7] = (int64_t)plan.qmap.size();
+    return FIP_OK;
+}

@@ -102,3 +102,43 @@ def test_c_restatement_of_faiss_ivf_matches_numpy_oracle():
     D1, I1 = c_oracle.ivf_search_l2(q, cent, sizes, codes, ids, 10, 5, nthreads=1)
     D2, I2 = c_oracle.ivf_search_l2(q, cent, sizes, codes, ids, 10, 5, nthreads=4)
     assert np.array_equal(I1, I2) and np.array_equal(D1, D2)
+
+
+@pytest.mark.parametrize("nlist,nq,nprobe,k,cap,safe,tc_min", [
+    (4096, 256, 64, 84, 4096, 0, 8),     # reference shape: tensor items + FFMA2 tiles
+    (4096, 32, 64, 84, 4096, 0, 8),      # few queries per list: FFMA2 tiles only
+    (512, 300, 32, 84, 4096, 0, 0),      # tensor path off
+    (64, 200, 16, 84, 4096, 1, 8),       # safe mode: phases of cap - k rows, partial lists
+    (64, 100, 16, 300, 16384, 1, 0),
+    (16, 500, 16, 84, 4096, 0, 8),       # every list probed by every query: several 128-query groups
+])
+def test_host_plan_covers_every_probed_list_exactly_once(native_lib, nlist, nq, nprobe, k, cap, safe, tc_min):
+    """The IVF host planner (csrc/ivf_api.cuh build_plan) through its no-GPU test hook: every
+    (query, probed list) pair must be scored over exactly the rows of that list, once, whatever mix
+    of dense prefixes, skip-aware FFMA2 tiles, tensor-core items and safe-mode phases is planned."""
+    import ctypes
+
+    f = native_lib.fivf_debug_plan
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int32] * 7 + [ctypes.c_void_p]
+    rng = np.random.default_rng(nlist + nq)
+    sizes = rng.poisson(900, nlist).astype(np.int64)
+    sizes[0] = 0                      # an empty list
+    sizes[1] = 30000                  # a list longer than the candidate capacity
+    sizes[2] = 5
+    probes = np.stack([rng.choice(nlist, nprobe, replace=False) for _ in range(nq)]).astype(np.int64)
+    probes[0, -1] = -1                # fewer than nprobe lists for one query
+    others = np.setdiff1d(np.arange(nlist), [1])
+    probes[1] = np.concatenate([[1], rng.choice(others, nprobe - 1, replace=False)])   # starts in the long list
+    out = np.zeros(8, np.int64)
+    rc = f(nlist, sizes.ctypes.data, probes.ctypes.data, nq, nprobe, k, cap, safe, tc_min, 1, out.ctypes.data)
+    assert rc == 0
+    phases, tiles, items, rows, pairs, _, bad, qrows = out.tolist()
+    assert bad == 0
+    want_pairs = int(sum(sizes[l] for l in probes.ravel() if l >= 0))
+    assert pairs >= want_pairs          # (tensor items count the skipped head rows too)
+    assert phases >= 2 or rows == 0
+    if tc_min == 0 or safe:
+        assert items == 0 and qrows == 0
+    if (nlist, tc_min, safe) == (16, 8, 0):
+        assert items > 0 and qrows % 32 == 0
