@@ -26,9 +26,20 @@ def create_b200_flat_ip_store(settings, config: dict[str, Any] | None = None) ->
     return B200FlatIPStore(settings, config or {})
 
 
-def install(component_factories: dict, *, replace_faiss: bool = True) -> dict:
-    """Register the B200 store in a ``COMPONENT_FACTORIES``-style mapping (mutates and returns it)."""
+def install(component_factories: dict, *, replace_faiss: bool = True,
+            replace_document_store: bool = False) -> dict:
+    """Register the B200 store in a ``COMPONENT_FACTORIES``-style mapping (mutates and returns it).
+
+    ``replace_document_store``: also put the batched ``CandidateFeed`` (candidate_feed.py) behind
+    the reference's ``ComponentType.DOCUMENT_STORE`` / ``"document_store"`` key
+    (component_factory.py:30-31,68)."""
     component_factories[COMPONENT_TYPE] = create_b200_flat_ip_store
+    if replace_document_store:
+        from .candidate_feed import create_candidate_feed
+        for key in list(component_factories.keys()):
+            if key == "document_store" or getattr(key, "value", None) == "document_store":
+                component_factories[key] = create_candidate_feed
+        component_factories.setdefault("document_store", create_candidate_feed)
     if replace_faiss:
         for key in list(component_factories.keys()):
             if key == "faiss_store" or getattr(key, "value", None) == "faiss":
