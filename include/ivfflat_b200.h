@@ -65,17 +65,21 @@ int fivf_export_lists(fivf_index* h, float* codes, int64_t* ids);
 int fivf_search(fivf_index* h, const float* queries, int64_t nq, int32_t k, int32_t nprobe,
                 float* distances, int64_t* ids);
 /* Same with device buffers on the index's GPU (co-located embedder, benchmarks).  Blocking: the
- * probe table is inverted into list-major tiles on the host. */
+ * sizes of the list-major work lists are read back to size the scan launches. */
 int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int32_t k, int32_t nprobe,
                        float* distances_dev, int64_t* ids_dev);
 
 /* options: "force_safe", "live_thresholds", "max_queries_per_tile" (4 or 16), "profile_events"
  * (1: CUDA events around the scan launches, read back as "scan_ns"), "tensor_min_queries" (a list
- * probed by at least this many queries of a batch is scored on the tensor cores; default 8, 0 = never).
+ * probed by at least this many queries of a batch is scored on the tensor cores; default 8, 0 = never),
+ * "device_plan" (default 1: for batches of >= 1024 (query, probe) pairs the probe table is inverted into
+ * work lists by GPU kernels and only their sizes are read back; 2: for every batch; 0: always on the
+ * host, which safe mode does anyway).
  * stats of the last search: "launches", "phases", "tiles", "tiles16", "rows_scanned",
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
  * "tensor_items", "tensor_pairs", "crowded_window" (1: the tf32 filter's exactness window overflowed
- * for some query and the batch was redone with the fp32 filter), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm". */
+ * for some query and the batch was redone with the fp32 filter), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm",
+ * "device_plan" (1: the last search was planned on the device). */
 int fivf_set_option(fivf_index* h, const char* key, int64_t value);
 int64_t fivf_get_stat(const fivf_index* h, const char* key);
 

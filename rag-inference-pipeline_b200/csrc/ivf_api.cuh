@@ -22,6 +22,7 @@
 #include "../../include/ivfflat_b200.h"
 #include "ivf.cuh"
 #include "tc_ivf.cuh"
+#include "ivf_plan.cuh"
 
 struct fivf_index {
     int dim = 0, nlist = 0, device = 0, num_sms = 0;
@@ -45,6 +46,7 @@ struct fivf_index {
     bool tmap_valid = false;
     // options
     int force_safe = 0, live_thr = 1, qb_max = 16, profile = 0;
+    int device_plan = 1;   // normal-mode searches are planned by the ivf_plan.cuh kernels (0: host planner, 1: batches of >= 1024 (query, probe) pairs, 2: always)
     int tc_min = 8;    // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
     CUtensorMap tmap_x128{};   // SWIZZLE_128B map of the sorted storage (tensor-core kernel)
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
@@ -60,6 +62,10 @@ struct fivf_index {
     DevBuf<int32_t> qmap;
     DevBuf<uint32_t> qskip;
     DevBuf<float> qprep;
+    DevBuf<int64_t> loff;                    // [nlist + 1] list boundaries on the device (device planner)
+    bool loff_valid = false;
+    DevBuf<uint32_t> plan_z, plan_take, plan_bases, plan_tile0base;   // device planner workspace
+    PinnedBuf<ivf::PlanCounts> h_counts;
     PinnedBuf<int64_t> h_probe, h_i;
     PinnedBuf<uint8_t> h_plan;
     PinnedBuf<uint32_t> h_flags;
@@ -67,7 +73,7 @@ struct fivf_index {
     void* plan_ws = nullptr;   // IvfPlan: host plan workspace, reused by every search (build_plan)
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0, st_device_plan = 0;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -165,6 +171,7 @@ int fivf_rebuild(fivf_index* h) {
     h->pend_assign.clear(); h->pend_assign.shrink_to_fit();
     h->off.swap(off_new);
     h->tmap_valid = false;
+    h->loff_valid = false;
     FIP_CUDA(h->x2max.ensure(1));
     FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
     ivf::max_norm_kernel<<<h->num_sms * 4, 256, 0, h->stream>>>(h->xnorm, n_new, h->x2max.p);
@@ -478,47 +485,134 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         FIP_CUDA(cudaGetLastError());
         launches += 4;
     }
-    FIP_CUDA(cudaMemcpyAsync(h->h_probe.p, h->probe_i.p, sizeof(int64_t) * (size_t)nq * nprobe,
-                             cudaMemcpyDeviceToHost, h->stream));
-    FIP_CUDA(cudaStreamSynchronize(h->stream));
-
     const int cap = safe ? kMaxCap : std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
     const bool live = h->live_thr && !safe;
     const int keep_max = std::min(cap / 2, 2 * k + 64);   // truncation limit of the exactness window
     const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
+    const bool tc_ok = allow_tc && h->tc_min > 0 && dim % 32 == 0;
+    const int k_plan = std::max(k, keep_max);
     if (!h->plan_ws) h->plan_ws = new IvfPlan();
     IvfPlan& plan = *static_cast<IvfPlan*>(h->plan_ws);
+    std::vector<IvfPlan::Phase> dev_phases;
+    const std::vector<IvfPlan::Phase>* phases = &plan.phases;
+    size_t n_tc_items = 0, n_qrows = 0, n_tiles = 0;
+    int64_t pl_rows = 0, pl_pairs = 0, pl_distinct = 0, pl_tc_pairs = 0;
+    // (a handful of pairs is planned faster on the host than five more launches take)
+    bool dev_plan = h->device_plan && !safe && (int64_t)nq * nprobe < (int64_t)1 << 30 &&
+                    (h->device_plan > 1 || (int64_t)nq * nprobe >= 1024);
+    if (h->profile) FIP_CUDA(cudaStreamSynchronize(h->stream));   // "plan_us" then excludes the coarse quantizer
     const auto t0 = std::chrono::steady_clock::now();
-    const bool tc_ok = allow_tc && h->tc_min > 0 && dim % 32 == 0;
-    build_plan(h, h->h_probe.p, nq, nprobe, std::max(k, keep_max), cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
+    if (dev_plan) {
+        // ---- plan on the device (ivf_plan.cuh); the host only reads the work-list sizes back
+        const size_t pairs_max = (size_t)nq * nprobe;
+        const size_t zwords = sizeof(ivf::PlanCounts) / 4 + 3 * (size_t)nlist;
+        FIP_CUDA(h->plan_z.ensure(zwords));
+        FIP_CUDA(h->plan_take.ensure(pairs_max));
+        FIP_CUDA(h->plan_bases.ensure((size_t)ivf::PLAN_BASES * ((size_t)nlist + 1)));
+        FIP_CUDA(h->plan_tile0base.ensure(nq));
+        FIP_CUDA(h->h_counts.ensure(1));
+        FIP_CUDA(h->tile_q.ensure(pairs_max + (size_t)nq + 1));
+        if (!h->loff_valid) {
+            if (h->off.empty()) h->off.assign((size_t)nlist + 1, 0);
+            FIP_CUDA(h->loff.ensure((size_t)nlist + 1));
+            FIP_CUDA(cudaMemcpyAsync(h->loff.p, h->off.data(), sizeof(int64_t) * ((size_t)nlist + 1),
+                                     cudaMemcpyHostToDevice, h->stream));
+            FIP_CUDA(cudaStreamSynchronize(h->stream));   // h->off is pageable
+            h->loff_valid = true;
+        }
+        ivf::PlanCounts* d_counts = reinterpret_cast<ivf::PlanCounts*>(h->plan_z.p);
+        uint32_t* lcount = h->plan_z.p + sizeof(ivf::PlanCounts) / 4;
+        uint32_t* cur = lcount + nlist;
+        uint32_t* probed = cur + nlist;
+        const uint32_t target0 = (uint32_t)std::min<int64_t>(cap, std::max<int64_t>(4 * (int64_t)k_plan, 256));
+        const int tc_min = tc_ok ? h->tc_min : 0, qb_big = big_ok ? 16 : 4;
+        FIP_CUDA(cudaMemsetAsync(h->plan_z.p, 0, zwords * 4, h->stream));
+        ivf::plan_query_kernel<<<(nq + 127) / 128, 128, 0, h->stream>>>(
+            h->probe_i.p, nq, nprobe, nlist, h->loff.p, target0, h->plan_take.p, lcount, probed,
+            h->plan_tile0base.p, d_counts);
+        FIP_CUDA(cudaGetLastError());
+        ivf::plan_lists_kernel<<<1, ivf::PLAN_LIST_THREADS, 0, h->stream>>>(
+            lcount, probed, h->loff.p, nlist, tc_min, qb_big, h->plan_bases.p, d_counts);
+        FIP_CUDA(cudaGetLastError());
+        FIP_CUDA(cudaMemcpyAsync(h->h_counts.p, d_counts, sizeof(ivf::PlanCounts), cudaMemcpyDeviceToHost, h->stream));
+        FIP_CUDA(cudaStreamSynchronize(h->stream));
+        const ivf::PlanCounts c = *h->h_counts.p;
+        if (c.tiles_total + c.n_tiles0 >= (1ull << 30)) {
+            dev_plan = false;   // work lists beyond 32-bit indexing: let the host planner (64-bit) decide
+        } else {
+            n_tiles = (size_t)c.n_t16 + c.n_t4 + c.n_tiles0;
+            n_tc_items = c.n_items;
+            n_qrows = c.qrows;
+            FIP_CUDA(h->tiles.ensure(n_tiles + 1));
+            FIP_CUDA(h->tc_items.ensure(n_tc_items + 1));
+            FIP_CUDA(h->qmap.ensure(n_qrows + 1));
+            FIP_CUDA(h->qskip.ensure(n_qrows + 1));
+            ivf::Tile* t16 = h->tiles.p;
+            ivf::Tile* t4 = t16 + c.n_t16;
+            ivf::Tile* t0 = t4 + c.n_t4;
+            if (c.n_pairs1) {
+                ivf::plan_scatter_kernel<<<(unsigned)((pairs_max + 255) / 256), 256, 0, h->stream>>>(
+                    h->probe_i.p, h->plan_take.p, (int64_t)pairs_max, nprobe, h->loff.p, h->plan_bases.p, cur, h->tile_q.p);
+                FIP_CUDA(cudaGetLastError());
+                ivf::plan_emit_kernel<<<nlist, 128, 0, h->stream>>>(h->plan_bases.p, h->loff.p, nlist, tc_min, qb_big,
+                                                                   h->tile_q.p, t16, t4, h->tc_items.p, h->qmap.p, h->qskip.p);
+                FIP_CUDA(cudaGetLastError());
+                launches += 2;
+            }
+            ivf::plan_tiles0_kernel<<<(nq + 127) / 128, 128, 0, h->stream>>>(
+                h->probe_i.p, h->plan_take.p, nq, nprobe, h->loff.p, h->plan_tile0base.p, (uint32_t)pairs_max, t0, h->tile_q.p);
+            FIP_CUDA(cudaGetLastError());
+            launches += 3;
+            dev_phases.assign(2, IvfPlan::Phase{});
+            dev_phases[0].t16_begin = 0; dev_phases[0].t16_n = 0;
+            dev_phases[0].t4_begin = (size_t)c.n_t16 + c.n_t4; dev_phases[0].t4_n = c.n_tiles0;
+            dev_phases[1].t16_begin = 0; dev_phases[1].t16_n = c.n_t16;
+            dev_phases[1].t4_begin = c.n_t16; dev_phases[1].t4_n = c.n_t4;
+            phases = &dev_phases;
+            pl_rows = (int64_t)c.rows; pl_pairs = (int64_t)c.pairs; pl_distinct = (int64_t)c.distinct_rows;
+            pl_tc_pairs = (int64_t)c.tc_pairs;
+        }
+    }
+    if (!dev_plan) {
+        FIP_CUDA(cudaMemcpyAsync(h->h_probe.p, h->probe_i.p, sizeof(int64_t) * (size_t)nq * nprobe,
+                                 cudaMemcpyDeviceToHost, h->stream));
+        FIP_CUDA(cudaStreamSynchronize(h->stream));
+        build_plan(h, h->h_probe.p, nq, nprobe, k_plan, cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
+        const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
+        FIP_CUDA(h->h_plan.ensure(tile_bytes + tq_bytes + 16));
+        FIP_CUDA(h->tiles.ensure(plan.tiles.size() + 1));
+        FIP_CUDA(h->tile_q.ensure(plan.tile_q.size() + 1));
+        if (tile_bytes) {
+            memcpy(h->h_plan.p, plan.tiles.data(), tile_bytes);
+            FIP_CUDA(cudaMemcpyAsync(h->tiles.p, h->h_plan.p, tile_bytes, cudaMemcpyHostToDevice, h->stream));
+        }
+        if (tq_bytes) {
+            memcpy(h->h_plan.p + tile_bytes, plan.tile_q.data(), tq_bytes);
+            FIP_CUDA(cudaMemcpyAsync(h->tile_q.p, h->h_plan.p + tile_bytes, tq_bytes, cudaMemcpyHostToDevice, h->stream));
+        }
+        n_tc_items = plan.tc_items.size();
+        n_qrows = plan.qmap.size();
+        n_tiles = plan.tiles.size();
+        if (n_tc_items) {
+            FIP_CUDA(h->qmap.ensure(n_qrows));
+            FIP_CUDA(h->tc_items.ensure(n_tc_items));
+            FIP_CUDA(h->qskip.ensure(n_qrows));
+            FIP_CUDA(cudaMemcpyAsync(h->qmap.p, plan.qmap.data(), n_qrows * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+            FIP_CUDA(cudaMemcpyAsync(h->qskip.p, plan.qskip.data(), n_qrows * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+            FIP_CUDA(cudaMemcpyAsync(h->tc_items.p, plan.tc_items.data(), n_tc_items * sizeof(ivf::TcItem),
+                                     cudaMemcpyHostToDevice, h->stream));
+        }
+        pl_rows = plan.rows; pl_pairs = plan.pairs; pl_distinct = plan.distinct_rows; pl_tc_pairs = plan.tc_pairs;
+    }
     h->st_plan_us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
-    const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
-    FIP_CUDA(h->h_plan.ensure(tile_bytes + tq_bytes + 16));
-    FIP_CUDA(h->tiles.ensure(plan.tiles.size() + 1));
-    FIP_CUDA(h->tile_q.ensure(plan.tile_q.size() + 1));
-    if (tile_bytes) {
-        memcpy(h->h_plan.p, plan.tiles.data(), tile_bytes);
-        FIP_CUDA(cudaMemcpyAsync(h->tiles.p, h->h_plan.p, tile_bytes, cudaMemcpyHostToDevice, h->stream));
-    }
-    if (tq_bytes) {
-        memcpy(h->h_plan.p + tile_bytes, plan.tile_q.data(), tq_bytes);
-        FIP_CUDA(cudaMemcpyAsync(h->tile_q.p, h->h_plan.p + tile_bytes, tq_bytes, cudaMemcpyHostToDevice, h->stream));
-    }
-    const bool use_tc = !plan.tc_items.empty();
+    const bool use_tc = n_tc_items > 0;
     ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim, use_tc ? 1 : 0,
                                                                h->eps.p, h->ones.p);
     FIP_CUDA(cudaGetLastError());
     CUtensorMap tmap_qg{};
     if (use_tc) {   // prepared queries of the tensor-core groups + the item list
-        const size_t rows = plan.qmap.size();
-        FIP_CUDA(h->qmap.ensure(rows));
+        const size_t rows = n_qrows;
         FIP_CUDA(h->qprep.ensure(rows * (size_t)dim));
-        FIP_CUDA(h->tc_items.ensure(plan.tc_items.size()));
-        FIP_CUDA(h->qskip.ensure(rows));
-        FIP_CUDA(cudaMemcpyAsync(h->qmap.p, plan.qmap.data(), rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
-        FIP_CUDA(cudaMemcpyAsync(h->qskip.p, plan.qskip.data(), rows * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-        FIP_CUDA(cudaMemcpyAsync(h->tc_items.p, plan.tc_items.data(), plan.tc_items.size() * sizeof(ivf::TcItem),
-                                 cudaMemcpyHostToDevice, h->stream));
         const int64_t vecs = (int64_t)rows * (dim / 4);
         ivf::gather_queries_kernel<<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(q_dev, h->qmap.p, (int64_t)rows, dim, h->qprep.p);
         FIP_CUDA(cudaGetLastError());
@@ -569,9 +663,9 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     a.lists.nq = nq; a.lists.thr = h->thr.p; a.lists.cnt = h->cnt.p; a.lists.cand = h->cand.p;
     a.lists.cap = (uint32_t)cap; a.lists.k_thr = k;
     if (live) { a.lists.hist = h->hist.p; a.lists.hbase = h->hbase.p; a.lists.win_eps = h->eps.p; a.lists.win_scale = h->ones.p; }
-    const size_t n_phases = plan.phases.size();
+    const size_t n_phases = phases->size();
     for (size_t p = 0; p < n_phases; ++p) {
-        const IvfPlan::Phase& ph = plan.phases[p];
+        const IvfPlan::Phase& ph = (*phases)[p];
         a.dense = p == 0 ? 1 : 0;
         const bool timed = h->profile && p < 4;
         if (timed) {
@@ -580,7 +674,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         }
         if (p == 1 && use_tc) {   // heavily probed lists: tcgen05 tiles
             ivf::TcIvfArgs ta{};
-            ta.items = h->tc_items.p; ta.n_items = (int)plan.tc_items.size(); ta.qmap = h->qmap.p; ta.qskip = h->qskip.p;
+            ta.items = h->tc_items.p; ta.n_items = (int)n_tc_items; ta.qmap = h->qmap.p; ta.qskip = h->qskip.p;
             ta.xnorm = h->xnorm; ta.dim = dim; ta.lists = a.lists;
             constexpr int smem = tc::Cfg<2, 1, 1>::SMEM_BYTES;
             FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -623,10 +717,11 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     // some query's exactness window held more than keep_max candidates and was truncated; with the
     // tf32 filter in play the caller redoes the batch on the (much narrower) fp32 window
     *crowded = h->h_flags.p[1] != 0 && use_tc;
-    h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)plan.tiles.size();
-    h->st_rows = plan.rows; h->st_pairs = plan.pairs; h->st_cap = cap;
-    h->st_distinct_rows = plan.distinct_rows;
-    h->st_tc_items = (int64_t)plan.tc_items.size(); h->st_tc_pairs = plan.tc_pairs;
+    h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)n_tiles;
+    h->st_rows = pl_rows; h->st_pairs = pl_pairs; h->st_cap = cap;
+    h->st_distinct_rows = pl_distinct;
+    h->st_tc_items = (int64_t)n_tc_items; h->st_tc_pairs = pl_tc_pairs;
+    h->st_device_plan = dev_plan ? 1 : 0;
     h->st_scan_ns = 0;
     if (h->profile)
         for (size_t p = 0; p < n_phases && p < 4; ++p) {
@@ -635,7 +730,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
             h->st_scan_ns += (int64_t)(ms * 1e6);
         }
     h->st_tiles16 = 0;
-    for (const auto& ph : plan.phases) h->st_tiles16 += (int64_t)ph.t16_n;
+    for (const auto& ph : *phases) h->st_tiles16 += (int64_t)ph.t16_n;
     return FIP_OK;
 }
 
@@ -710,6 +805,7 @@ void fivf_destroy(fivf_index* h) {
     h->cent.release(); h->cnorm.release(); h->ckeys.release(); h->cand.release(); h->qnorm.release();
     h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
     h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
+    h->loff.release(); h->plan_z.release(); h->plan_take.release(); h->plan_bases.release(); h->plan_tile0base.release();
     h->doff.release(); h->assign.release(); h->tile_q.release(); h->cnt.release(); h->flags.release();
     h->hist.release(); h->hbase.release(); h->tiles.release(); h->tc_items.release(); h->qmap.release(); h->qskip.release(); h->qprep.release(); h->h_probe.release(); h->h_i.release();
     h->h_plan.release(); h->h_flags.release(); h->h_q.release(); h->h_d.release();
@@ -988,6 +1084,7 @@ int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
     else if (k == "max_queries_per_tile") h->qb_max = (int)value;
     else if (k == "profile_events") h->profile = (int)value;
     else if (k == "tensor_min_queries") h->tc_min = (int)value;
+    else if (k == "device_plan") h->device_plan = value < 0 ? 0 : (value > 2 ? 2 : (int)value);
     else return fail(FIP_ERR_INVALID, "unknown option " + k);
     return FIP_OK;
 }
@@ -1009,6 +1106,7 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "tensor_items") return h->st_tc_items;
     if (k == "tensor_pairs") return h->st_tc_pairs;
     if (k == "crowded_window") return h->st_crowded;
+    if (k == "device_plan") return h->st_device_plan;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
 }
