@@ -403,9 +403,10 @@ def run_ivf(args):
     (configs/retrieval_faiss_only.yaml: retrieval_batch_size / retrieval_k).  The quantizer is trained
     on 100 000 rows (the reference trains on 10 000, which on structure-free Gaussian data yields one
     545 k-row list that every query probes; `--ivf-train 10000` reproduces that).  value = QPS with
-    device-resident queries (wall clock: the call plans on the host and blocks), e2e = the host API.
+    device-resident queries (wall clock: the call blocks; it reads the plan's sizes back), e2e = the host API.
     roofline: HBM -- algorithmic bytes = the rows of every list probed by at least one query, read
-    once (fp32), over the device time of the scan launches.  cpu_baseline / --impl reference: the C
+    once (2 bytes per element when the fp16 filter copy is in use, else 4), over the device time of
+    the scan launches.  cpu_baseline / --impl reference: the C
     restatement of faiss's IVF search (oracle/faiss_ivf_restatement.c) on the same index and queries."""
     import numpy as np
     import torch
@@ -504,11 +505,14 @@ def run_ivf(args):
     clocks = sampler.stop()
     peaks = load_peaks()
     distinct = index.stat("distinct_rows")
-    alg_bytes = distinct * dim * 4 + nlist * dim * 4 + B * dim * 4 + B * k * 12
+    # the tensor-core filter reads the fp16 copy of the lists when it is in use (stat "tensor_f16")
+    ebytes = 2 if index.stat("tensor_f16") else 4
+    alg_bytes = distinct * dim * ebytes + nlist * dim * 4 + B * dim * 4 + B * k * 12
     scan_s = scan_ns / args.steps * 1e-9
     roof = {"bound": "hbm", "achieved": alg_bytes / scan_s / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
             "peak_source": f"{peaks['source']} (copy bandwidth)", "kernel": "ivf_scan_kernel",
             "launch": {"scan_ms_per_search": scan_s * 1e3, "distinct_probed_rows": distinct,
+                       "list_bytes_per_element": ebytes,
                        "rows_scanned": index.stat("rows_scanned"), "pairs_scored": index.stat("pairs_scored"),
                        "tiles": index.stat("tiles"), "tiles16": index.stat("tiles16")},
             "kernel_share_of_step": scan_s / dt, "whole_search_frac": alg_bytes / dt / 1e9 / peaks["hbm_gbs"],
@@ -527,7 +531,7 @@ def run_ivf(args):
             "e2e": {"value": B / dt_e2e, "unit": UNIT, "h2d_bytes_per_step": B * dim * 4,
                     "d2h_bytes_per_step": B * k * 12, "api": "IVFFlatL2Index.search (fivf_search, host buffers)"},
             "gpu_launches": launches, "roofline": roof, "cpu_baseline": cb,
-            "timing": "wall clock around the blocking search call (host plan and both synchronisations included)",
+            "timing": "wall clock around the blocking search call (planning and both synchronisations included)",
             "list_sizes": {"min": int(sizes.min()), "mean": float(sizes.mean()), "max": int(sizes.max())},
             "index_build_s": build_s, "verify": verify}
     index.close()

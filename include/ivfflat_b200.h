@@ -71,7 +71,11 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
 
 /* options: "force_safe", "live_thresholds", "max_queries_per_tile" (4 or 16), "profile_events"
  * (1: CUDA events around the scan launches, read back as "scan_ns"), "tensor_min_queries" (a list
- * probed by at least this many queries of a batch is scored on the tensor cores; default 8, 0 = never),
+ * probed by at least this many queries of a batch is scored on the tensor cores; default 1, 0 = never),
+ * "tensor_format" (0, default: the tensor-core filter reads an fp16 copy of the lists -- built on first
+ * use, +50 % device memory -- whenever every component of the lists and of the batch's queries is
+ * inside fp16's range; 1: always tf32 straight from the fp32 rows.  Results are identical either way:
+ * survivors are rescored exactly in fp32),
  * "device_plan" (default 1: for batches of >= 1024 (query, probe) pairs the probe table is inverted into
  * work lists by GPU kernels and only their sizes are read back; 2: for every batch; 0: always on the
  * host, which safe mode does anyway).
@@ -79,7 +83,8 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
  * "tensor_items", "tensor_pairs", "crowded_window" (1: the tf32 filter's exactness window overflowed
  * for some query and the batch was redone with the fp32 filter), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm",
- * "device_plan" (1: the last search was planned on the device). */
+ * "device_plan" (1: the last search was planned on the device), "tensor_f16" (1: the last search's
+ * tensor-core filter ran on the fp16 copy). */
 int fivf_set_option(fivf_index* h, const char* key, int64_t value);
 int64_t fivf_get_stat(const fivf_index* h, const char* key);
 

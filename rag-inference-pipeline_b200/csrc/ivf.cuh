@@ -431,18 +431,27 @@ __global__ void max_norm_kernel(const float* __restrict__ xnorm, int64_t n, floa
 // The selects keep every candidate within 2 eps of the k-th best (select.cuh, "exactness window"),
 // ivf_rescore_kernel then evaluates sum (q - x)^2 directly (what faiss's IVFFlatScannerL2 computes,
 // no cancellation) and the final select ranks by that.
-// With `tf32` set (some lists go through the tensor-core kernel, tc_ivf.cuh) the bound also covers
-// the truncation of both operands to tf32 (2^-9 + 2^-20 relative to ||q|| ||x||) and the tensor
-// core's fp32 accumulation, on the doubled inner product.
+// With `mode` 1 (some lists go through the tensor-core kernel on tf32, tc_ivf.cuh) the bound also
+// covers the truncation of both operands to tf32 (2^-9 + 2^-20 relative to ||q|| ||x||) and the
+// tensor core's fp32 accumulation, on the doubled inner product.  `mode` 2 (fp16 filter copy and
+// fp16-rounded queries): both operands rounded to nearest, 2^-10 + 2^-22 relative, plus the
+// absolute error of components that fall into fp16's subnormal range (at most 2^-25 each:
+// sqrt(dim) 2^-25 (||q|| + ||x||) on the inner product); overflow is excluded by the caller
+// (max ||x||^2 and every ||q||^2 below 4e9, i.e. every component below 65504).
 __global__ void ivf_eps_kernel(const float* __restrict__ qnorm, const float* __restrict__ x2max, int nq,
-                               int dim, int tf32, float* __restrict__ eps, float* __restrict__ ones) {
+                               int dim, int mode, float* __restrict__ eps, float* __restrict__ ones) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const float X2 = *x2max;
     float e = 1.01f * 5.9604645e-8f * (float)(dim + 1) * (2.0f * sqrtf(qnorm[q] * X2) + X2);
-    if (tf32) {
+    if (mode == 1) {
         const float rel = (float)dim * 1.1920929e-7f + 1.0f / 512 + 1.0f / 1048576;
         e = fmaxf(e, 1.01f * (2.0f * rel * sqrtf(qnorm[q] * X2) + 5.9604645e-8f * (float)(dim + 1) * X2));
+    } else if (mode == 2) {
+        const float rel = (float)dim * 1.1920929e-7f + 1.0f / 1024 + 1.0f / 4194304;
+        const float under = sqrtf((float)dim) * 2.9802322e-8f * (sqrtf(qnorm[q]) + sqrtf(X2)) + (float)dim * 8.9e-16f;
+        e = fmaxf(e, 1.01f * (2.0f * rel * sqrtf(qnorm[q] * X2) + 2.0f * under +
+                              5.9604645e-8f * (float)(dim + 1) * X2));
     }
     eps[q] = e;
     ones[q] = 1.0f;

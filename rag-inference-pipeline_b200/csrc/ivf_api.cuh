@@ -47,8 +47,15 @@ struct fivf_index {
     // options
     int force_safe = 0, live_thr = 1, qb_max = 16, profile = 0;
     int device_plan = 1;   // normal-mode searches are planned by the ivf_plan.cuh kernels (0: host planner, 1: batches of >= 1024 (query, probe) pairs, 2: always)
-    int tc_min = 8;    // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
+    int tc_min = 1;    // a list probed by >= tc_min queries of a batch goes to the tensor-core kernel (0 = never)
     CUtensorMap tmap_x128{};   // SWIZZLE_128B map of the sorted storage (tensor-core kernel)
+    // fp16 FILTER COPY of the sorted storage (tensor-core kernel, kind::f16): built on first use,
+    // dropped by every rebuild; the fp32 rows stay the truth (exact rescoring reads them)
+    __half* x16 = nullptr;
+    CUtensorMap tmap_x16{};
+    bool x16_failed = false;       // the copy did not fit: stay on tf32
+    float x2max_host = 0.f;        // max ||x||^2 (fp16 range check)
+    int tensor_format = 0;         // 0: fp16 filter copy when representable, 1: tf32 on the fp32 rows
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
     // workspace
     DevBuf<uint64_t> ckeys, cand;
@@ -66,6 +73,7 @@ struct fivf_index {
     bool loff_valid = false;
     DevBuf<uint32_t> plan_z, plan_take, plan_bases, plan_tile0base;   // device planner workspace
     PinnedBuf<ivf::PlanCounts> h_counts;
+    PinnedBuf<float> h_qnorm;
     PinnedBuf<int64_t> h_probe, h_i;
     PinnedBuf<uint8_t> h_plan;
     PinnedBuf<uint32_t> h_flags;
@@ -73,7 +81,7 @@ struct fivf_index {
     void* plan_ws = nullptr;   // IvfPlan: host plan workspace, reused by every search (build_plan)
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0, st_device_plan = 0;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0, st_device_plan = 0, st_f16 = 0;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -84,6 +92,7 @@ int fivf_use(const fivf_index* h) {
     return FIP_OK;
 }
 
+constexpr float kF16NormLimit = 4.0e9f;   // ||v||^2 below this => every component below 65504 (fp16 max)
 constexpr int kAssignChunk = 16384;   // rows per coarse-assignment chunk (keys: chunk * nlist * 8 B)
 
 // Nearest centroid of n device rows -> host `out` (chunked: coarse scores + row argmax).
@@ -176,7 +185,10 @@ int fivf_rebuild(fivf_index* h) {
     FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
     ivf::max_norm_kernel<<<h->num_sms * 4, 256, 0, h->stream>>>(h->xnorm, n_new, h->x2max.p);
     FIP_CUDA(cudaGetLastError());
+    FIP_CUDA(cudaMemcpyAsync(&h->x2max_host, h->x2max.p, sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     FIP_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->x16) { cudaFree(h->x16); h->x16 = nullptr; }
+    h->x16_failed = false;
     return FIP_OK;
 }
 
@@ -493,6 +505,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     const int k_plan = std::max(k, keep_max);
     if (!h->plan_ws) h->plan_ws = new IvfPlan();
     IvfPlan& plan = *static_cast<IvfPlan*>(h->plan_ws);
+    bool q_fits_f16 = false;   // known only on the device-plan path (PlanCounts::q_over)
     std::vector<IvfPlan::Phase> dev_phases;
     const std::vector<IvfPlan::Phase>* phases = &plan.phases;
     size_t n_tc_items = 0, n_qrows = 0, n_tiles = 0;
@@ -529,7 +542,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         FIP_CUDA(cudaMemsetAsync(h->plan_z.p, 0, zwords * 4, h->stream));
         ivf::plan_query_kernel<<<(nq + 127) / 128, 128, 0, h->stream>>>(
             h->probe_i.p, nq, nprobe, nlist, h->loff.p, target0, h->plan_take.p, lcount, probed,
-            h->plan_tile0base.p, d_counts);
+            h->plan_tile0base.p, h->qnorm.p, kF16NormLimit, d_counts);
         FIP_CUDA(cudaGetLastError());
         ivf::plan_lists_kernel<<<1, ivf::PLAN_LIST_THREADS, 0, h->stream>>>(
             lcount, probed, h->loff.p, nlist, tc_min, qb_big, h->plan_bases.p, d_counts);
@@ -571,12 +584,17 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
             phases = &dev_phases;
             pl_rows = (int64_t)c.rows; pl_pairs = (int64_t)c.pairs; pl_distinct = (int64_t)c.distinct_rows;
             pl_tc_pairs = (int64_t)c.tc_pairs;
+            q_fits_f16 = c.q_over == 0;
         }
     }
     if (!dev_plan) {
         FIP_CUDA(cudaMemcpyAsync(h->h_probe.p, h->probe_i.p, sizeof(int64_t) * (size_t)nq * nprobe,
                                  cudaMemcpyDeviceToHost, h->stream));
+        FIP_CUDA(h->h_qnorm.ensure(nq));
+        FIP_CUDA(cudaMemcpyAsync(h->h_qnorm.p, h->qnorm.p, sizeof(float) * (size_t)nq, cudaMemcpyDeviceToHost, h->stream));
         FIP_CUDA(cudaStreamSynchronize(h->stream));
+        q_fits_f16 = true;
+        for (int i = 0; i < nq; ++i) q_fits_f16 = q_fits_f16 && h->h_qnorm.p[i] < kF16NormLimit;
         build_plan(h, h->h_probe.p, nq, nprobe, k_plan, cap, safe, big_ok ? 16 : 4, tc_ok ? h->tc_min : 0, &plan);
         const size_t tile_bytes = plan.tiles.size() * sizeof(ivf::Tile), tq_bytes = plan.tile_q.size() * sizeof(ivf::TileQuery);
         FIP_CUDA(h->h_plan.ensure(tile_bytes + tq_bytes + 16));
@@ -606,25 +624,48 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     }
     h->st_plan_us = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
     const bool use_tc = n_tc_items > 0;
-    ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim, use_tc ? 1 : 0,
-                                                               h->eps.p, h->ones.p);
+    // tensor-core operand format: the fp16 filter copy when every component of the lists and of the
+    // batch's queries is inside fp16's range (norm test), else tf32 straight from the fp32 rows
+    bool use_f16 = use_tc && h->tensor_format == 0 && dim % 64 == 0 && q_fits_f16 &&
+                   h->x2max_host < kF16NormLimit && !h->x16_failed;
+    if (use_f16 && !h->x16) {
+        const size_t elems = (size_t)h->n_sorted * dim;
+        if (cudaMalloc((void**)&h->x16, elems * sizeof(__half)) != cudaSuccess) {
+            cudaGetLastError();
+            h->x16 = nullptr; h->x16_failed = true; use_f16 = false;
+        } else {
+            ivf::rows_to_f16_kernel<<<h->num_sms * 8, 256, 0, h->stream>>>(h->x, h->x16, (int64_t)(elems / 8));
+            FIP_CUDA(cudaGetLastError());
+            int rc16 = make_tmap(&h->tmap_x16, h->x16, kF16, dim, (uint64_t)h->n_sorted);
+            if (rc16) return rc16;
+        }
+    }
+    ivf::ivf_eps_kernel<<<(nq + 255) / 256, 256, 0, h->stream>>>(h->qnorm.p, h->x2max.p, nq, dim,
+                                                               use_tc ? (use_f16 ? 2 : 1) : 0, h->eps.p, h->ones.p);
     FIP_CUDA(cudaGetLastError());
     CUtensorMap tmap_qg{};
     if (use_tc) {   // prepared queries of the tensor-core groups + the item list
         const size_t rows = n_qrows;
         FIP_CUDA(h->qprep.ensure(rows * (size_t)dim));
         const int64_t vecs = (int64_t)rows * (dim / 4);
-        ivf::gather_queries_kernel<<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(q_dev, h->qmap.p, (int64_t)rows, dim, h->qprep.p);
+        if (use_f16)
+            ivf::gather_queries_kernel<__half><<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(
+                q_dev, h->qmap.p, (int64_t)rows, dim, reinterpret_cast<__half*>(h->qprep.p));
+        else
+            ivf::gather_queries_kernel<float><<<(unsigned)((vecs + 255) / 256), 256, 0, h->stream>>>(
+                q_dev, h->qmap.p, (int64_t)rows, dim, h->qprep.p);
         FIP_CUDA(cudaGetLastError());
         launches++;
-        {   // [rows, dim] fp32, box = 32 floats x 32 rows, SWIZZLE_128B
+        {   // [rows, dim], box = 128 bytes of K x 32 rows, SWIZZLE_128B
             EncodeTiledFn enc = get_encode_fn();
             if (!enc) return fail(FIP_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+            const int esize = use_f16 ? 2 : 4;
             cuuint64_t dims[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
-            cuuint64_t strides[1] = {(cuuint64_t)dim * 4};
-            cuuint32_t box[2] = {32u, 32u};
+            cuuint64_t strides[1] = {(cuuint64_t)dim * esize};
+            cuuint32_t box[2] = {(cuuint32_t)(tc::BK_BYTES / esize), 32u};
             cuuint32_t estr[2] = {1, 1};
-            CUresult r = enc(&tmap_qg, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, h->qprep.p, dims, strides, box, estr,
+            CUresult r = enc(&tmap_qg, use_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                             h->qprep.p, dims, strides, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (r != CUDA_SUCCESS)
@@ -677,9 +718,15 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
             ta.items = h->tc_items.p; ta.n_items = (int)n_tc_items; ta.qmap = h->qmap.p; ta.qskip = h->qskip.p;
             ta.xnorm = h->xnorm; ta.dim = dim; ta.lists = a.lists;
             constexpr int smem = tc::Cfg<2, 1, 1>::SMEM_BYTES;
-            FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            static_assert(tc::Cfg<0, 1, 1>::SMEM_BYTES == smem, "same ring for both formats");
             const int grid = std::min(ta.n_items, h->num_sms);
-            ivf::tc_ivf_kernel<<<grid, ivf::TCI_THREADS, smem, h->stream>>>(tmap_qg, h->tmap_x128, ta);
+            if (use_f16) {
+                FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                ivf::tc_ivf_kernel<0><<<grid, ivf::TCI_THREADS, smem, h->stream>>>(tmap_qg, h->tmap_x16, ta);
+            } else {
+                FIP_CUDA(cudaFuncSetAttribute(ivf::tc_ivf_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                ivf::tc_ivf_kernel<2><<<grid, ivf::TCI_THREADS, smem, h->stream>>>(tmap_qg, h->tmap_x128, ta);
+            }
             FIP_CUDA(cudaGetLastError());
             launches++;
         }
@@ -722,6 +769,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     h->st_distinct_rows = pl_distinct;
     h->st_tc_items = (int64_t)n_tc_items; h->st_tc_pairs = pl_tc_pairs;
     h->st_device_plan = dev_plan ? 1 : 0;
+    h->st_f16 = use_f16 ? 1 : 0;
     h->st_scan_ns = 0;
     if (h->profile)
         for (size_t p = 0; p < n_phases && p < 4; ++p) {
@@ -801,7 +849,7 @@ void fivf_destroy(fivf_index* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    cudaFree(h->x); cudaFree(h->ids); cudaFree(h->xnorm); cudaFree(h->pend_x);
+    cudaFree(h->x); cudaFree(h->ids); cudaFree(h->xnorm); cudaFree(h->pend_x); cudaFree(h->x16);
     h->cent.release(); h->cnorm.release(); h->ckeys.release(); h->cand.release(); h->qnorm.release();
     h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
     h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
@@ -1084,6 +1132,7 @@ int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
     else if (k == "max_queries_per_tile") h->qb_max = (int)value;
     else if (k == "profile_events") h->profile = (int)value;
     else if (k == "tensor_min_queries") h->tc_min = (int)value;
+    else if (k == "tensor_format") h->tensor_format = value ? 1 : 0;
     else if (k == "device_plan") h->device_plan = value < 0 ? 0 : (value > 2 ? 2 : (int)value);
     else return fail(FIP_ERR_INVALID, "unknown option " + k);
     return FIP_OK;
@@ -1107,6 +1156,7 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "tensor_pairs") return h->st_tc_pairs;
     if (k == "crowded_window") return h->st_crowded;
     if (k == "device_plan") return h->st_device_plan;
+    if (k == "tensor_f16") return h->st_f16;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
 }

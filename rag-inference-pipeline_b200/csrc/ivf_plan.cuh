@@ -29,7 +29,8 @@ struct PlanCounts {
     uint32_t n_items;     // tensor-core items
     uint32_t qrows;       // prepared-query rows (groups padded to 32)
     uint32_t n_pairs1;    // (query, list) pairs of phase 1 = bucket entries
-    uint32_t pad[2];
+    uint32_t q_over;      // 1: some query has ||q||^2 >= qlimit (no fp16 filter for this batch)
+    uint32_t pad;
     unsigned long long rows, pairs, tc_pairs, distinct_rows;
     unsigned long long tiles_total;   // 64-bit sum of all tile / item counts (overflow guard)
 };
@@ -74,9 +75,11 @@ __global__ void plan_query_kernel(const int64_t* __restrict__ probes, int nq, in
                                   const int64_t* __restrict__ off, uint32_t target0,
                                   uint32_t* __restrict__ take, uint32_t* __restrict__ lcount,
                                   uint32_t* __restrict__ probed, uint32_t* __restrict__ tile0base,
+                                  const float* __restrict__ qnorm, float qlimit,
                                   PlanCounts* __restrict__ counts) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
+    if (!(qnorm[q] < qlimit)) counts->q_over = 1u;
     uint32_t cum = 0, ntile0 = 0;
     for (int j = 0; j < nprobe; ++j) {
         const int64_t l = probes[(size_t)q * nprobe + j];

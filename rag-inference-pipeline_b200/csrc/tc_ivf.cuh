@@ -127,9 +127,13 @@ __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr,
 // loaded; the rest of the 128-row A tile keeps stale shared memory, whose (garbage) accumulator
 // lanes belong to no query.  tmap_x: sorted list storage [N, dim] fp32, make_tmap's
 // [32 floats x 128 rows] boxes.
+// kFmt = 2: both maps fp32, kind::tf32; kFmt = 0: both maps fp16 (the index's fp16 FILTER COPY of the
+// lists and fp16-rounded prepared queries), kind::f16 -- half the bytes and twice the tensor rate;
+// the fp32 rows are only touched by the exact rescoring of the survivors.
+template <int kFmt>
 __global__ void __launch_bounds__(TCI_THREADS, 1)
 tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, TcIvfArgs a) {
-    using C = tc::Cfg<2, 1, 1>;
+    using C = tc::Cfg<kFmt, 1, 1>;
     constexpr int STAGES = C::STAGES;
     constexpr int STAGE_BYTES = C::STAGE_BYTES;
     constexpr int B_OFF = tc::A_BYTES;
@@ -155,7 +159,7 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     __syncthreads();
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
-    const int nkb = a.dim / C::BK;   // 32 floats of K per stage
+    const int nkb = a.dim / C::BK;   // 128 bytes of K per stage: 32 floats or 64 halves
     // static round-robin over the items (adjacent items = adjacent row tiles of one list: L2 locality)
     const int first = (int)blockIdx.x, step = (int)gridDim.x;
 
@@ -180,7 +184,8 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
     } else if (warp == 1) {
         if (lane == 0) {  // ===================== MMA issuer
-            constexpr uint32_t idesc = tc::make_idesc(2, 2, tc::BM, tc::BN);
+            constexpr uint32_t idesc = tc::make_idesc(kFmt, kFmt, tc::BM, tc::BN);
+            constexpr int kKind = kFmt == 2 ? 1 : 0;
             int s = 0, n = 0;
             uint32_t ph = 0;
             for (int t = first; t < a.n_items; t += step, ++n) {
@@ -196,7 +201,7 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                     const uint64_t adesc = tc::make_sw128_desc(sa), bdesc = tc::make_sw128_desc(sa + B_OFF);
 #pragma unroll
                     for (int k = 0; k < C::MMAS_PER_STAGE; ++k)
-                        tc::umma<1, 1>(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (uint32_t)((kb | k) != 0));
+                        tc::umma<1, kKind>(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (uint32_t)((kb | k) != 0));
                     tc::umma_commit<1>(empty_bar(s));
                     if (++s == STAGES) { s = 0; ph ^= 1u; }
                 }
@@ -233,10 +238,12 @@ tc_ivf_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     }
 }
 
-// Prepared queries of the tensor-core groups: row r = q32[qmap[r]] (zeros for padding rows).
+// Prepared queries of the tensor-core groups: row r = q32[qmap[r]] (zeros for padding rows), as fp32
+// or rounded to fp16 (RNE).
+template <typename T>
 __global__ void gather_queries_kernel(const float* __restrict__ q32, const int32_t* __restrict__ qmap,
-                                      int64_t rows, int dim, float* __restrict__ out) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // one float4 each
+                                      int64_t rows, int dim, T* __restrict__ out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // four elements each
     const int vec = dim / 4;
     if (i >= rows * vec) return;
     const int64_t r = i / vec;
@@ -244,7 +251,29 @@ __global__ void gather_queries_kernel(const float* __restrict__ q32, const int32
     const int q = qmap[r];
     float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
     if (q >= 0) val = __ldg(reinterpret_cast<const float4*>(q32 + (size_t)q * dim) + v);
-    reinterpret_cast<float4*>(out)[i] = val;
+    if constexpr (sizeof(T) == 4) {
+        reinterpret_cast<float4*>(out)[i] = val;
+    } else {
+        const __half2 lo = __floats2half2_rn(val.x, val.y), hi = __floats2half2_rn(val.z, val.w);
+        uint2 packed;
+        packed.x = *reinterpret_cast<const uint32_t*>(&lo);
+        packed.y = *reinterpret_cast<const uint32_t*>(&hi);
+        reinterpret_cast<uint2*>(out)[i] = packed;
+    }
+}
+
+// fp32 rows -> the fp16 filter copy (RNE), 8 elements per thread.
+__global__ void rows_to_f16_kernel(const float* __restrict__ in, __half* __restrict__ out, int64_t n8) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 a = __ldcs(reinterpret_cast<const float4*>(in) + 2 * i);
+        const float4 b = __ldcs(reinterpret_cast<const float4*>(in) + 2 * i + 1);
+        const __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
+        const __half2 h2 = __floats2half2_rn(b.x, b.y), h3 = __floats2half2_rn(b.z, b.w);
+        uint4 o;
+        o.x = *reinterpret_cast<const uint32_t*>(&h0); o.y = *reinterpret_cast<const uint32_t*>(&h1);
+        o.z = *reinterpret_cast<const uint32_t*>(&h2); o.w = *reinterpret_cast<const uint32_t*>(&h3);
+        reinterpret_cast<uint4*>(out)[i] = o;
+    }
 }
 
 }  // namespace ivf

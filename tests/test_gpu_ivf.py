@@ -26,22 +26,22 @@ def _data(n, d, nq, seed=0, clustered=False):
     return x, q.astype(np.float32)
 
 
-def _stable_probe_rows(q, centroids, nprobe):
+def _stable_probe_rows(q, centroids, nprobe, scale=1.0):
     """Queries whose nprobe-th / (nprobe+1)-th centroid distances are not a near tie."""
     d = np.sort(ivf_oracle.sq_l2(q, centroids), axis=1)
     if nprobe >= centroids.shape[0]:
         return np.ones(len(q), dtype=bool)
-    return (d[:, nprobe] - d[:, nprobe - 1]) > 1e-3 + 2e-5 * d[:, nprobe]
+    return (d[:, nprobe] - d[:, nprobe - 1]) > 1e-3 * scale * scale + 2e-5 * d[:, nprobe]
 
 
-def _check(index, q, k, nprobe):
+def _check(index, q, k, nprobe, scale=1.0):
     sizes, codes, ids = index.export_lists()
     cent = index.centroids()
     D, I = index.search(q, k, nprobe=nprobe)
     Dr, Ir, _, D64 = ivf_oracle.ivf_search(q, cent, sizes, codes, ids, k + 1, nprobe)
-    ok = _stable_probe_rows(q, cent, nprobe)
+    ok = _stable_probe_rows(q, cent, nprobe, scale)
     assert ok.mean() > 0.9
-    res = ivf_oracle.compare_ivf(D[ok], I[ok], Dr[ok, :k], Ir[ok, :k], D64[ok])
+    res = ivf_oracle.compare_ivf(D[ok], I[ok], Dr[ok, :k], Ir[ok, :k], D64[ok], atol=1e-4 * scale * scale)
     assert res["dist_bad"] == 0 and res["pad_bad"] == 0 and res["id_mismatch_outside_ties"] == 0, res
     assert res["id_mismatch_total"] <= max(2, D.size // 200), res
     # rows are ascending and padding sits at the end
@@ -110,6 +110,12 @@ def test_ivf_tensor_core_path_for_heavily_probed_lists():
     index.add(x)
     D0, I0 = _check(index, q, 20, 16)
     assert index.stat("tensor_items") > 0 and index.stat("tensor_pairs") > 0
+    assert index.stat("tensor_f16") == 1          # default: fp16 filter copy of the lists (kind::f16)
+    index.set_option("tensor_format", 1)          # tf32 straight from the fp32 rows
+    D2, I2 = index.search(q, 20, nprobe=16)
+    assert index.stat("tensor_items") > 0 and index.stat("tensor_f16") == 0
+    assert np.array_equal(I0, I2) and np.array_equal(D0, D2)
+    index.set_option("tensor_format", 0)
     index.set_option("tensor_min_queries", 0)
     D1, I1 = index.search(q, 20, nprobe=16)
     assert index.stat("tensor_items") == 0
@@ -125,6 +131,39 @@ def test_ivf_tensor_core_path_for_heavily_probed_lists():
     assert index2.stat("tensor_items") > 0 or index2.stat("crowded_window") == 1
     index.close()
     index2.close()
+
+
+@pytest.mark.parametrize("scale,expect_f16", [(3.0e4, 0), (1.0e-3, None), (1.0, 1)])
+def test_ivf_fp16_filter_copy_respects_fp16_range(scale, expect_f16):
+    """The fp16 filter copy is used only when the lists and the queries fit fp16's range (norm test);
+    components in fp16's subnormal range are covered by the window's absolute term (or the crowded
+    fallback).  Results match the oracle at every magnitude, and the incremental add drops and
+    rebuilds the copy."""
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(30000, 128, 120, seed=77)
+    x = (x * scale).astype(np.float32)
+    q = (q * scale).astype(np.float32)
+    index = IVFFlatL2Index(128, 32)
+    index.train(x[:3000])
+    index.add(x[:20000])
+    _check(index, q, 10, 12, scale)
+    assert index.stat("device_plan") == 1
+    if expect_f16 is not None and not index.stat("crowded_window"):
+        assert index.stat("tensor_f16") == expect_f16
+    index.add(x[20000:])                       # rebuild: the copy is dropped and rebuilt on next use
+    _check(index, q, 10, 12, scale)
+    if expect_f16 is not None and not index.stat("crowded_window"):
+        assert index.stat("tensor_f16") == expect_f16
+    if scale == 1.0:                           # a query outside fp16's range switches the batch to tf32
+        qbig = q.copy()
+        qbig[3] *= 1.0e4
+        D, I = index.search(qbig, 10, nprobe=12)
+        assert index.stat("tensor_f16") == 0 or index.stat("crowded_window") == 1
+        D1, I1 = index.search(q, 10, nprobe=12)
+        keep = np.arange(len(q)) != 3
+        assert np.array_equal(I[keep], I1[keep]) and np.array_equal(D[keep], D1[keep])
+    index.close()
 
 
 def test_ivf_crowded_tf32_window_falls_back_to_fp32_filter():
