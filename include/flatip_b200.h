@@ -134,6 +134,9 @@ void fip_exchange_destroy(fip_exchange* x);
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
  * in the tensor-core variant), "cta_pair" (0 auto / 1 single-CTA MMAs / 2 cta_group::2 CTA pairs),
  * "certify" (1 default / 0: skip the exactness certificate of the tensor-core variant),
+ * "filter_copy" (fp32 storage only; 1 default: the tensor-core variant FILTERS on an fp16 copy of the
+ * corpus -- built on first search after a change, +50 % device memory, skipped when it does not fit or
+ * a row leaves fp16's range -- and rescoring stays exact on the fp32 rows; 0: tf32 on the fp32 rows),
  * "live_thresholds" (1 default: a filter launch raises its own per-query thresholds from a score
  * histogram, so one launch covers the shard; 0: thresholds move only between geometric phases),
  * "coalesce" (1 default / 0) and "coalesce_max_batch" (default 4096): fip_search calls that arrive
@@ -143,7 +146,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
  * "uncertified_queries" (queries the tensor-core filter could not certify exact and that were redone
  * with a tighter variant), "stream_redo_queries" (of those and the overflowed ones, how many ended
- * on the exact streaming kernel), "query_split_used",
+ * on the exact streaming kernel), "query_split_used", "filter_f16" (1: the last search filtered on the
+ * fp16 copy of an fp32 corpus),
  * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_ns_<i>" / "scan_rows_<i>" / "gap_ns_<i>" (per scan launch i: device time, corpus rows, time to the
  * next scan), "scan_time_ns" / "scan_launches" (device time and count of the scan
  * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches",

@@ -217,10 +217,24 @@ struct fip_index {
 
     CUtensorMap tmap_x{};
     bool tmap_x_valid = false;
+    uint64_t corpus_gen = 1;   // bumped by everything that changes the stored rows
+
+    // fp32 storage only: fp16 FILTER COPY of the corpus for the tensor-core variant.  The scan only
+    // filters (survivors are rescored exactly from the fp32 rows), so it may read 2 bytes per
+    // element instead of 4: half the HBM time and twice the tensor rate of the tf32 form.  Built on
+    // first use after a change of the corpus (+50 % device memory; skipped when it does not fit or
+    // when some row leaves fp16's range).
+    int filter_copy = 1;
+    __half* corpus16 = nullptr;
+    CUtensorMap tmap_x16{};
+    uint64_t c16_gen = 0;      // corpus_gen the copy (or the decision not to have one) belongs to
+    bool c16_usable = false;
+    float c16_xmax = 0.f;      // max row norm (host copy)
+    PinnedBuf<float> h_mn2;
 
     // stats
     int64_t st_launches = 0, st_variant = 0, st_phases = 0, st_overflow = 0, st_cap = 0, st_pair = 0;
-    int64_t st_uncert = 0, st_split = 0, st_stream_redo = 0;
+    int64_t st_uncert = 0, st_split = 0, st_stream_redo = 0, st_filter16 = 0;
     int64_t st_total_launches = 0, st_total_searches = 0;
 
     size_t row_bytes() const { return (size_t)cfg.dim * dtype_size(cfg.dtype); }
@@ -247,7 +261,7 @@ int reserve_rows(fip_index* idx, int64_t want) {
     }
     idx->corpus = p;
     idx->cap_rows = new_cap;
-    idx->tmap_x_valid = false;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
     return FIP_OK;
 }
 
@@ -305,6 +319,7 @@ struct SearchCtx {
     fip_index* idx;
     cudaStream_t stream;
     int launches = 0;
+    const CUtensorMap* tmap_scan = nullptr;   // corpus map of the tensor-core scan (storage or fp16 filter copy)
 };
 
 template <typename T, int QB, int R>
@@ -377,7 +392,7 @@ int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q,
     }
     groups = (int)std::min<int64_t>(groups, group_tiles);
     cfg.gridDim = dim3((unsigned)(groups * kCtas));
-    FIP_CUDA(cudaLaunchKernelEx(&cfg, kern, tmap_q, idx->tmap_x, a, n_qtiles));
+    FIP_CUDA(cudaLaunchKernelEx(&cfg, kern, tmap_q, c.tmap_scan ? *c.tmap_scan : idx->tmap_x, a, n_qtiles));
     c.launches++;
     return FIP_OK;
 }
@@ -437,7 +452,36 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
 }
 
 // One complete search of `nq` device-resident fp32 queries; results to device out_d / out_i.
-// Does not synchronise.
+// fp32 storage: make the fp16 filter copy current (see fip_index::corpus16).  *usable = the copy
+// exists and every stored row is inside fp16's range.  Synchronises `stream` once per corpus change.
+int ensure_filter_copy(fip_index* idx, cudaStream_t stream, bool* usable) {
+    *usable = false;
+    if (idx->c16_gen == idx->corpus_gen) { *usable = idx->c16_usable; return FIP_OK; }
+    idx->c16_gen = idx->corpus_gen;
+    idx->c16_usable = false;
+    if (idx->corpus16) { cudaFree(idx->corpus16); idx->corpus16 = nullptr; }
+    FIP_CUDA(idx->h_mn2.ensure(1));
+    FIP_CUDA(cudaMemcpyAsync(idx->h_mn2.p, idx->max_norm2.p, sizeof(float), cudaMemcpyDeviceToHost, stream));
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    const float mn2 = idx->h_mn2.p[0];
+    if (!(mn2 > 1e-30f && mn2 < 4.0e9f)) return FIP_OK;   // ||x||^2 < 4e9 => every component < 65504
+    const size_t elems = (size_t)idx->n_rows * idx->cfg.dim;
+    if (cudaMalloc((void**)&idx->corpus16, elems * sizeof(__half)) != cudaSuccess) {
+        cudaGetLastError();
+        idx->corpus16 = nullptr;
+        return FIP_OK;
+    }
+    convert_rows_kernel<__half><<<idx->num_sms * 16, 256, 0, stream>>>((const float*)idx->corpus, idx->corpus16, (int64_t)elems);
+    FIP_CUDA(cudaGetLastError());
+    int rc = make_tmap(&idx->tmap_x16, idx->corpus16, kF16, idx->cfg.dim, (uint64_t)idx->n_rows);
+    if (rc) return rc;
+    idx->c16_xmax = sqrtf(mn2);
+    idx->c16_usable = true;
+    *usable = true;
+    return FIP_OK;
+}
+
+// Does not synchronise (except once after a corpus change, to build the fp16 filter copy).
 int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
                Mode mode, SearchInfo* info) {
     fip_index* idx = c.idx;
@@ -455,7 +499,15 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         return FIP_OK;
     }
     int variant = idx->variant;
-    const bool tc_ok = (dim * dtype_size(dtype)) % tc::BK_BYTES == 0;
+    // fp32 storage: the tensor-core variant filters on the fp16 copy when there is one
+    bool copy16 = false;
+    if (dtype == kF32 && idx->filter_copy && mode.rigor == 0 && variant != FIP_VARIANT_STREAM &&
+        (dim * 2) % tc::BK_BYTES == 0) {
+        int rc16 = ensure_filter_copy(idx, c.stream, &copy16);
+        if (rc16) return rc16;
+    }
+    const int fdtype = copy16 ? (int)kF16 : dtype;   // operand type of the tensor-core filter
+    const bool tc_ok = (dim * dtype_size(fdtype)) % tc::BK_BYTES == 0;
     if (variant == FIP_VARIANT_AUTO) {
         // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
         // CUDA-core kernel (FMA + unpack + LDS per element) keeps up with HBM up to ~2 flop/byte
@@ -467,7 +519,10 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         // 256 / 768-byte rows): those go to the tensor-core kernel at any batch size.
         // stream_max_batch > 0 overrides the rule.
         const bool long_rows = (size_t)dim * dtype_size(dtype) >= 1024;
+        // (with the fp16 filter copy the tensor-core scan reads half the bytes the streaming kernel
+        // would: it wins at every batch size)
         const int stream_max = idx->stream_max_batch > 0 ? idx->stream_max_batch
+                               : copy16                  ? 0
                                                          : (long_rows ? dtype_size(dtype) : 0);
         variant = (tc_ok && nq > stream_max) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
     }
@@ -519,21 +574,24 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
                                       (n_qtiles % 2 == 0 || n_qtiles >= 7));
         if (pair) n_qtiles = (n_qtiles + 1) / 2 * 2;
         nq_pad = n_qtiles * tc::BM;
-        const size_t esize = dtype_size(dtype);
+        const size_t esize = dtype_size(fdtype);
         FIP_CUDA(idx->qprep.ensure((size_t)split * nq_pad * dim * esize));
         FIP_CUDA(idx->q_scale.ensure(nq));
         FIP_CUDA(idx->q_eps.ensure(nq));
         const unsigned pgrid = (nq_pad + 7) / 8;
         // what software cannot see: fp32 accumulation in the tensor core, tf32 operand truncation
-        const float rel = (float)dim * 1.1920929e-7f + (dtype == kF32 ? (1.0f / 512 + 1.0f / 1048576) : 0.f);
+        // ... and, for the fp16 filter copy, the rounding of the stored rows: 2^-11 relative per
+        // component, 2^-25 absolute for components in fp16's subnormal range
+        const float rel = (float)dim * 1.1920929e-7f + (fdtype == kF32 ? (1.0f / 512 + 1.0f / 1048576) : 0.f) +
+                          (copy16 ? 1.001f / 2048 + sqrtf((float)dim) * 2.9802322e-8f / idx->c16_xmax : 0.f);
         const float* mn2 = idx->max_norm2.p;
         float* sc = idx->q_scale.p;
         float* ep = idx->q_eps.p;
-        if (dtype == kBF16) {
+        if (fdtype == kBF16) {
             auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->qprep.p);
             if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
             else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
-        } else if (dtype == kF16) {
+        } else if (fdtype == kF16) {
             auto* dst = reinterpret_cast<__half*>(idx->qprep.p);
             if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
             else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
@@ -543,9 +601,10 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         }
         FIP_CUDA(cudaGetLastError());
         c.launches++;
-        int rc = make_tmap(&tmap_q, idx->qprep.p, dtype, dim, (uint64_t)split * nq_pad);
+        int rc = make_tmap(&tmap_q, idx->qprep.p, fdtype, dim, (uint64_t)split * nq_pad);
         if (rc) return rc;
-        if (!idx->tmap_x_valid) {
+        c.tmap_scan = copy16 ? &idx->tmap_x16 : &idx->tmap_x;
+        if (!copy16 && !idx->tmap_x_valid) {
             rc = make_tmap(&idx->tmap_x, idx->corpus, dtype, dim, (uint64_t)n);
             if (rc) return rc;
             idx->tmap_x_valid = true;
@@ -555,7 +614,8 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     }
 
     ScanArgs a{};
-    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.dtype = dtype; a.nq = nq;
+    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.nq = nq;
+    a.dtype = variant == FIP_VARIANT_TENSOR ? fdtype : dtype;   // (the streaming kernel reads the stored rows)
     a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
 
     auto scan_launch = [&]() -> int {
@@ -628,6 +688,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr);
         if (rc) return rc;
     }
+    idx->st_filter16 = (variant == FIP_VARIANT_TENSOR && copy16) ? 1 : 0;
     info->variant = variant; info->phases = phases; info->cap = cap; info->split = split;
     info->certified_path = certify;
     return FIP_OK;
@@ -806,6 +867,7 @@ void fip_destroy(fip_index* idx) {
     cudaSetDevice(idx->cfg.device);
     if (idx->stream) cudaStreamSynchronize(idx->stream);
     if (idx->corpus) cudaFree(idx->corpus);
+    if (idx->corpus16) cudaFree(idx->corpus16);
     idx->thr.release(); idx->q_scale.release(); idx->q_eps.release(); idx->max_norm2.release(); idx->q32.release(); idx->out_d.release();
     idx->cnt.release(); idx->hist.release(); idx->hbase.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
@@ -870,7 +932,7 @@ int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n) {
         FIP_CUDA(cudaStreamSynchronize(idx->stream));
         idx->n_rows += m;
     }
-    idx->tmap_x_valid = false;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
     return FIP_OK;
 }
 
@@ -896,7 +958,7 @@ int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtyp
     if (rc) return rc;
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows += n;
-    idx->tmap_x_valid = false;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
     return FIP_OK;
 }
 
@@ -921,7 +983,7 @@ int fip_add_synthetic(fip_index* idx, int64_t n, uint64_t seed, int64_t global_r
     if (rc) return rc;
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows += n;
-    idx->tmap_x_valid = false;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
     return FIP_OK;
 }
 
@@ -933,7 +995,7 @@ int fip_reset(fip_index* idx) {
     FIP_CUDA(cudaMemsetAsync(idx->max_norm2.p, 0, sizeof(float), idx->stream));
     FIP_CUDA(cudaStreamSynchronize(idx->stream));
     idx->n_rows = 0;
-    idx->tmap_x_valid = false;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
     return FIP_OK;
 }
 
@@ -1244,6 +1306,15 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         idx->live_thr = value != 0;
     } else if (k == "certify") {
         idx->certify = value != 0;
+    } else if (k == "filter_copy") {
+        idx->filter_copy = value != 0;
+        if (!idx->filter_copy && idx->corpus16) {
+            if (int rc = use_device(idx)) return rc;
+            cudaFree(idx->corpus16);
+            idx->corpus16 = nullptr;
+            idx->c16_gen = 0;
+            idx->c16_usable = false;
+        }
     } else if (k == "profile_events") {
         idx->profile = value != 0;
     } else if (k == "force_safe_mode") {
@@ -1264,6 +1335,7 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "uncertified_queries") return idx->st_uncert;
     if (k == "stream_redo_queries") return idx->st_stream_redo;
     if (k == "query_split_used") return idx->st_split;
+    if (k == "filter_f16") return idx->st_filter16;
     if (k == "candidate_capacity") return idx->st_cap;
     if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
