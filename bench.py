@@ -322,6 +322,8 @@ def run_b200(args, rank, local_rank, world):
         ms_per_step = ms_max / args.steps
         n_local = searcher.local_rows  # rank 0's shard (the largest)
         esize = 4 if dtype == "f32" else 2
+        if dtype == "f32" and searcher.index.stat("filter_f16") == 1:
+            esize = 2   # the tensor-core scan reads the fp16 FILTER COPY of the fp32 corpus
         scan_s = scan_ns_max * 1e-9
         scans = max(1, scan_launches)
         # dominant kernel = the scan launch that takes the longest (the last, geometrically
@@ -345,6 +347,7 @@ def run_b200(args, rank, local_rank, world):
         roof["kernel"] = "tc_scan_kernel" if variant == "tensor" else "stream_scan_kernel"
         roof["launch"] = {"phase": dom, "rows": dom_rows, "avg_ms": dom_s * 1e3,
                           "phases_per_search": len(per_scan)}
+        roof["scan_bytes_per_element"] = esize
         roof["launches_timed"] = scan_launches
         roof["all_scan_launches_ms_per_step"] = scan_s * 1e3 / args.steps
         roof["whole_search_frac"] = None

@@ -107,6 +107,46 @@ def test_parity_with_oracle(variant, dtype, n, dim, nq, k):
     idx.close()
 
 
+@pytest.mark.parametrize("scale,expect_copy", [(1.0, 1), (3.0e4, 0), (1.0e-3, 1)])
+def test_fp32_storage_filters_on_fp16_copy(scale, expect_copy):
+    """fp32 storage: the tensor-core scan reads an fp16 FILTER COPY of the corpus (half the bytes),
+    survivors are rescored exactly from the fp32 rows: same bits as the tf32 filter and the exact
+    streaming kernel; the copy follows adds and is skipped when a row leaves fp16's range."""
+    n, dim, k = 30000, 256, 20
+    corpus = (synthetic.synthetic_corpus(0, n + 5000, dim, "f32") * np.float32(scale)).astype(np.float32)
+    queries = (synthetic.synthetic_queries(40, dim) * np.float32(scale)).astype(np.float32)
+    idx = _index(dim, "f32")
+    idx.add(corpus[:n])
+    results = []
+    for batch in (40, 1):
+        q = queries[:batch]
+        Dr, Ir = flatip_oracle.flat_ip_search(q, corpus[:n], k + 1)
+        D, I = idx.search(q, k)
+        # (without the copy a single fp32 query stays on the exact streaming kernel)
+        assert idx.last_variant() == ("tensor" if expect_copy or batch > 4 else "stream")
+        assert idx.stat("filter_f16") == expect_copy
+        _check(D, I, Dr[:, :k], Ir[:, :k], "f32", Dr[:, k])
+        results.append((D, I))
+    idx.set_option("filter_copy", 0)
+    D1, I1 = idx.search(queries, k)
+    assert idx.stat("filter_f16") == 0
+    idx.set_variant("stream")
+    D2, I2 = idx.search(queries, k)
+    assert idx.last_variant() == "stream"
+    assert np.array_equal(I1, results[0][1]) and np.array_equal(D1, results[0][0])   # same rescoring kernel
+    assert np.array_equal(I2, results[0][1])
+    np.testing.assert_allclose(D2, results[0][0], rtol=2e-6, atol=1e-6 * scale * scale)
+    idx.set_variant("auto")
+    idx.set_option("filter_copy", 1)
+    idx.add(corpus[n:])                                    # the copy is rebuilt for the grown corpus
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k + 1)
+    D, I = idx.search(queries, k)
+    assert idx.stat("filter_f16") == expect_copy
+    _check(D, I, Dr[:, :k], Ir[:, :k], "f32", Dr[:, k])
+    assert I.max() >= n                                    # (new rows do show up)
+    idx.close()
+
+
 def test_auto_variant_follows_arithmetic_intensity():
     idx = _index(512, "f16")                   # 1 KB rows
     idx.add_synthetic(5000, 1, 0)
@@ -120,9 +160,15 @@ def test_auto_variant_follows_arithmetic_intensity():
     idx = _index(256, "f32")                   # 1 KB rows
     idx.add_synthetic(5000, 1, 0)
     idx.search(synthetic.synthetic_queries(64, 256), 5)
-    assert idx.last_variant() == "tensor"      # fp32 storage: tf32 filter + exact fp32 rescoring
+    assert idx.last_variant() == "tensor"      # fp32 storage: fp16 filter copy + exact fp32 rescoring
+    assert idx.stat("filter_f16") == 1
     idx.search(synthetic.synthetic_queries(3, 256), 5)
-    assert idx.last_variant() == "stream"
+    assert idx.last_variant() == "tensor"      # the copy halves the bytes: tensor path at any batch
+    idx.set_option("filter_copy", 0)
+    idx.search(synthetic.synthetic_queries(64, 256), 5)
+    assert idx.last_variant() == "tensor" and idx.stat("filter_f16") == 0   # tf32 on the fp32 rows
+    idx.search(synthetic.synthetic_queries(3, 256), 5)
+    assert idx.last_variant() == "stream"      # 4-byte elements: CUDA cores keep up to batch 4
     idx.close()
     idx = _index(128, "f16")                   # 256-byte rows: half a warp per row -> tensor
     idx.add_synthetic(5000, 1, 0)
