@@ -54,6 +54,10 @@ class B200FlatIPStore:
         self.storage_dtype = config.get("storage_dtype", os.environ.get("FLATIP_B200_DTYPE"))
         self.id_base = int(config.get("id_base", 0))
         self.variant = config.get("variant", os.environ.get("FLATIP_B200_VARIANT", "auto"))
+        # fp32 indexes (flat and IVF) filter on an fp16 copy of the rows (+50 % device memory, exact
+        # fp32 results either way); False keeps only the fp32 rows.
+        self.filter_copy = str(config.get("filter_copy", os.environ.get("FLATIP_B200_FILTER_COPY", "1"))
+                               ).lower() not in ("0", "false", "no")
 
     # ------------------------------------------------------------------------------- load
     def _load_synthetic(self) -> FlatIPIndex:
@@ -127,6 +131,11 @@ class B200FlatIPStore:
             index = self._load_synthetic() if synthetic else self._load_file()
             if self.variant != "auto" and hasattr(index, "set_variant"):
                 index.set_variant(self.variant)
+            if not self.filter_copy:
+                if hasattr(index, "set_variant"):
+                    index.set_option("filter_copy", 0)
+                else:
+                    index.set_option("tensor_format", 1)
             self._index = index
             self._is_loaded = True
             logger.info("FAISS index loaded successfully: %d vectors, dimension=%d (B200 %s, "
