@@ -37,7 +37,8 @@ struct TcIvfArgs {
     ScanArgs lists;          // thr / cnt / cand / cap / hist / hbase / k_thr / win_* (common.cuh)
 };
 
-constexpr int TCI_EPI_WARPS = 8;   // two per TMEM lane quarter: 4 chunks of 32 columns each
+constexpr int TCI_EPI_WARPS = 16;  // four per TMEM lane quarter: 2 chunks of 32 columns each (the epilogue,
+                                   // ~5 instructions per score with the norm bias, must keep up with kind::f16)
 constexpr int TCI_THREADS = (tc::EPI_WARP0 + TCI_EPI_WARPS) * 32;
 constexpr int TCI_CHUNKS = tc::BN / 32 / (TCI_EPI_WARPS / 4);
 
@@ -54,9 +55,14 @@ __device__ __forceinline__ void tci_load_chunk(const TcIvfArgs& a, uint32_t tadd
     }
     // every lane reads the same norm: one broadcast transaction per load (lists start at arbitrary
     // positions, so the norms cannot be fetched as aligned vectors); rows past the list are dropped
+    if (row_base + 32u <= row_end) {   // warp-uniform: the chunk lies inside the list (the common case)
 #pragma unroll
-    for (int j = 0; j < 32; ++j)
-        v[j] = row_base + j < row_end ? fmaf(2.0f, v[j], -__ldg(a.xnorm + row_base + j)) : kNegInf;
+        for (int j = 0; j < 32; ++j) v[j] = fmaf(2.0f, v[j], -__ldg(a.xnorm + row_base + j));
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            v[j] = row_base + j < row_end ? fmaf(2.0f, v[j], -__ldg(a.xnorm + row_base + j)) : kNegInf;
+    }
 }
 
 __device__ __forceinline__ void tci_epilogue(const TcIvfArgs& a, uint32_t taddr, int q, float thr, uint32_t hb,
