@@ -627,8 +627,15 @@ def test_store_dropin_on_gpu(tmp_path):
     Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
     _check(D, I, Dr, Ir, "f32")
     assert isinstance(I[0].tolist()[0], int) and isinstance(D[0].tolist()[0], float)
+    assert store._index.stat("filter_f16") == 1      # fp32 file: filtered on the fp16 copy, exact results
     store.unload()
     assert not store.is_loaded
+    lean = B200FlatIPStore(settings, {"filter_copy": False})   # keep only the fp32 rows
+    lean.load()
+    D1, I1 = lean.search(q, k)
+    assert lean._index.stat("filter_f16") == 0
+    assert np.array_equal(I1, I) and np.array_equal(D1, D)
+    lean.unload()
     # fp16 storage + synthetic URI
     s2 = types.SimpleNamespace(faiss_index_path=f"synthetic:{n}?dim={dim}&dtype=f16", faiss_dim=dim)
     st2 = B200FlatIPStore(s2)
