@@ -540,7 +540,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         const uint32_t target0 = (uint32_t)std::min<int64_t>(cap, std::max<int64_t>(4 * (int64_t)k_plan, 256));
         const int tc_min = tc_ok ? h->tc_min : 0, qb_big = big_ok ? 16 : 4;
         FIP_CUDA(cudaMemsetAsync(h->plan_z.p, 0, zwords * 4, h->stream));
-        ivf::plan_query_kernel<<<(nq + 127) / 128, 128, 0, h->stream>>>(
+        ivf::plan_query_kernel<<<(nq + 3) / 4, 128, 0, h->stream>>>(   // one warp per query
             h->probe_i.p, nq, nprobe, nlist, h->loff.p, target0, h->plan_take.p, lcount, probed,
             h->plan_tile0base.p, h->qnorm.p, kF16NormLimit, d_counts);
         FIP_CUDA(cudaGetLastError());

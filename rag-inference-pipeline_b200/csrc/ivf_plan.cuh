@@ -70,39 +70,55 @@ __device__ __forceinline__ ListShape list_shape(uint32_t m, uint32_t len, int tc
 }
 
 // probes [nq, nprobe] nearest first (-1 = none).  take[q, j] = rows of list probes[q, j] that q
-// scores in phase 0 (PLAN_NO_PAIR: no such list, or an empty one).
+// scores in phase 0 (PLAN_NO_PAIR: no such list, or an empty one).  One WARP per query: the lanes
+// take 32 consecutive probes per round and the running prefix of the list lengths (saturated at
+// target0, so it fits 32 bits) comes from a warp scan -- a single thread walking the probe
+// sequence paid one dependent L2 round trip per probe.
 __global__ void plan_query_kernel(const int64_t* __restrict__ probes, int nq, int nprobe, int nlist,
                                   const int64_t* __restrict__ off, uint32_t target0,
                                   uint32_t* __restrict__ take, uint32_t* __restrict__ lcount,
                                   uint32_t* __restrict__ probed, uint32_t* __restrict__ tile0base,
                                   const float* __restrict__ qnorm, float qlimit,
                                   PlanCounts* __restrict__ counts) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= nq) return;
-    if (!(qnorm[q] < qlimit)) counts->q_over = 1u;
-    uint32_t cum = 0, ntile0 = 0;
-    for (int j = 0; j < nprobe; ++j) {
-        const int64_t l = probes[(size_t)q * nprobe + j];
-        uint32_t t = PLAN_NO_PAIR;
-        if (l >= 0 && l < nlist) {
-            const uint32_t len = (uint32_t)(off[l + 1] - off[l]);
-            if (len > 0) {
-                probed[l] = 1u;
-                t = 0;
-                if (cum < target0) {
-                    t = min(len, target0 - cum);
-                    cum += t;
-                    ntile0 += (t + SC_ROWS - 1u) / SC_ROWS;
-                }
-                if (t < len) atomicAdd(&lcount[l], 1u);
-            }
+    const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (q >= nq) return;   // warp-uniform
+    if (lane == 0 && !(qnorm[q] < qlimit)) counts->q_over = 1u;
+    uint32_t cum = 0, ntile0 = 0;   // cum: rows taken by the probes of earlier rounds (<= target0), warp-uniform
+    for (int j0 = 0; j0 < nprobe; j0 += 32) {
+        const int j = j0 + lane;
+        int64_t l = -1;
+        uint32_t len = 0;
+        if (j < nprobe) {
+            l = probes[(size_t)q * nprobe + j];
+            if (l >= 0 && l < nlist) len = (uint32_t)(off[l + 1] - off[l]);
         }
-        take[(size_t)q * nprobe + j] = t;
+        const uint32_t capped = min(len, target0);
+        uint32_t incl = capped;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        const uint32_t before = min(target0, cum + (incl - capped));   // rows taken before this probe
+        uint32_t t = PLAN_NO_PAIR;
+        if (len > 0) {
+            probed[l] = 1u;
+            t = min(len, target0 - before);
+            ntile0 += (t + SC_ROWS - 1u) / SC_ROWS;
+            if (t < len) atomicAdd(&lcount[l], 1u);
+        }
+        if (j < nprobe) take[(size_t)q * nprobe + j] = t;
+        cum = min(target0, cum + __shfl_sync(0xFFFFFFFFu, incl, 31));
     }
-    tile0base[q] = ntile0 ? atomicAdd(&counts->n_tiles0, ntile0) : 0u;
-    if (cum) {
-        atomicAdd(&counts->rows, (unsigned long long)cum);
-        atomicAdd(&counts->pairs, (unsigned long long)cum);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ntile0 += __shfl_xor_sync(0xFFFFFFFFu, ntile0, o);
+    if (lane == 0) {
+        tile0base[q] = ntile0 ? atomicAdd(&counts->n_tiles0, ntile0) : 0u;
+        if (cum) {
+            atomicAdd(&counts->rows, (unsigned long long)cum);
+            atomicAdd(&counts->pairs, (unsigned long long)cum);
+        }
     }
 }
 
@@ -156,16 +172,42 @@ plan_lists_kernel(const uint32_t* __restrict__ lcount, const uint32_t* __restric
         if (s.v[2]) tc_pairs += (unsigned long long)len * m;
         tiles_total += (unsigned long long)s.v[2] + s.v[3] + s.v[4];
     }
+    // shapes of this thread's lists stay in registers across the five scans when there are few of
+    // them (nlist <= 4096), else they are recomputed
+    constexpr int kCache = 4;
+    ListShape sh[kCache];
+    const bool cached = per <= kCache;
+    if (cached) {
+#pragma unroll
+        for (int i = 0; i < kCache; ++i) {
+            const int l = l0 + i;
+            sh[i] = l < l1 ? list_shape(lcount[l], (uint32_t)(off[l + 1] - off[l]), tc_min, qb_big) : ListShape{};
+        }
+    }
+#pragma unroll
     for (int w = 0; w < PLAN_BASES; ++w) {
         uint32_t sum = 0;
-        for (int l = l0; l < l1; ++l)
-            sum += list_shape(lcount[l], (uint32_t)(off[l + 1] - off[l]), tc_min, qb_big).v[w];
+        if (cached) {
+#pragma unroll
+            for (int i = 0; i < kCache; ++i) sum += sh[i].v[w];
+        } else {
+            for (int l = l0; l < l1; ++l)
+                sum += list_shape(lcount[l], (uint32_t)(off[l + 1] - off[l]), tc_min, qb_big).v[w];
+        }
         uint32_t total;
         uint32_t b = block_excl_scan(sum, s_warp, &total);
         uint32_t* dst = bases + (size_t)w * (nlist + 1);
-        for (int l = l0; l < l1; ++l) {
-            dst[l] = b;
-            b += list_shape(lcount[l], (uint32_t)(off[l + 1] - off[l]), tc_min, qb_big).v[w];
+        if (cached) {
+#pragma unroll
+            for (int i = 0; i < kCache; ++i) {
+                if (l0 + i < l1) dst[l0 + i] = b;
+                b += sh[i].v[w];
+            }
+        } else {
+            for (int l = l0; l < l1; ++l) {
+                dst[l] = b;
+                b += list_shape(lcount[l], (uint32_t)(off[l + 1] - off[l]), tc_min, qb_big).v[w];
+            }
         }
         if (tid == 0) {
             dst[nlist] = total;
