@@ -47,9 +47,11 @@ __global__ void row_norm2_kernel(const float* __restrict__ x, int64_t n, int dim
 // Coarse quantizer: score[q][c] = 2 <x_q, c> - ||c||^2 for EVERY centroid, written as candidate
 // keys at keys[q * cap + c] (the layout select_topk_kernel reads after a dense phase).  Replaces
 // the IndexFlatL2 quantizer search of IndexIVF::search / add (faiss coarse assignment).
-// Classic 64 x 64 x 16 register-tiled fp32 GEMM (exact FMA; nlist is small, this is a few percent
-// of a search): 256 threads, 4 x 4 outputs per thread.
-constexpr int CO_T = 64, CO_K = 16;
+// Classic 64 x 64 x 32 register-tiled fp32 GEMM (exact FMA chain in k order per output; nlist is
+// small, this is a few percent of a search): 256 threads, 4 x 4 outputs per thread.  The next K
+// slab is fetched into registers while the current one is multiplied: a small batch launches fewer
+// CTAs than there are SMs, so nothing else hides the global-load latency of each step.
+constexpr int CO_T = 64, CO_K = 32;
 __global__ void __launch_bounds__(256)
 coarse_scores_kernel(const float* __restrict__ xq, int nq, const float* __restrict__ cent, int nlist,
                      const float* __restrict__ cnorm, int dim, uint64_t* __restrict__ keys, uint32_t cap) {
@@ -63,15 +65,31 @@ coarse_scores_kernel(const float* __restrict__ xq, int nq, const float* __restri
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    // loader mapping: thread loads one float4 along k for row (tid / 4) at k offset (tid % 4) * 4
+    // loader mapping: thread loads two float4 along k for row (tid / 4), at k offsets (tid % 4) * 4 and + 16
     const int lr = tid >> 2, lk = (tid & 3) * 4;
+    const bool qa = q0 + lr < nq, cb = c0 + lr < nlist;
+    const float* pa = xq + (size_t)(qa ? q0 + lr : 0) * dim + lk;
+    const float* pb = cent + (size_t)(cb ? c0 + lr : 0) * dim + lk;
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 va[2], vb[2];
+    auto fetch = [&](int k0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const bool in = k0 + lk + 16 * h < dim;   // dim % 4 == 0: a float4 is inside or outside as a whole
+            va[h] = (qa && in) ? __ldg(reinterpret_cast<const float4*>(pa + k0 + 16 * h)) : zero;
+            vb[h] = (cb && in) ? __ldg(reinterpret_cast<const float4*>(pb + k0 + 16 * h)) : zero;
+        }
+    };
+    fetch(0);
     for (int k0 = 0; k0 < dim; k0 += CO_K) {
-        float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
-        if (q0 + lr < nq && k0 + lk < dim) va = *reinterpret_cast<const float4*>(xq + (size_t)(q0 + lr) * dim + k0 + lk);
-        if (c0 + lr < nlist && k0 + lk < dim) vb = *reinterpret_cast<const float4*>(cent + (size_t)(c0 + lr) * dim + k0 + lk);
-        s_a[lk + 0][lr] = va.x; s_a[lk + 1][lr] = va.y; s_a[lk + 2][lr] = va.z; s_a[lk + 3][lr] = va.w;
-        s_b[lk + 0][lr] = vb.x; s_b[lk + 1][lr] = vb.y; s_b[lk + 2][lr] = vb.z; s_b[lk + 3][lr] = vb.w;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int kk = lk + 16 * h;
+            s_a[kk + 0][lr] = va[h].x; s_a[kk + 1][lr] = va[h].y; s_a[kk + 2][lr] = va[h].z; s_a[kk + 3][lr] = va[h].w;
+            s_b[kk + 0][lr] = vb[h].x; s_b[kk + 1][lr] = vb[h].y; s_b[kk + 2][lr] = vb[h].z; s_b[kk + 3][lr] = vb[h].w;
+        }
         __syncthreads();
+        if (k0 + CO_K < dim) fetch(k0 + CO_K);   // in flight during the multiply below
 #pragma unroll
         for (int k = 0; k < CO_K; ++k) {
             const float4 a = *reinterpret_cast<const float4*>(&s_a[k][tq]);
