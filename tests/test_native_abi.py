@@ -86,6 +86,19 @@ def test_init(tmp_path):
     assert "not loaded" in repr(store)
 
 
+def test_filter_copy_switch_from_config_and_env(tmp_path, monkeypatch):
+    """fp32 indexes filter on an fp16 copy of the rows unless the profile / environment says no."""
+    from rag_inference_pipeline_b200 import B200FlatIPStore
+
+    s = _settings(tmp_path / "faiss_index.bin")
+    assert B200FlatIPStore(s).filter_copy is True
+    assert B200FlatIPStore(s, {"filter_copy": False}).filter_copy is False
+    assert B200FlatIPStore(s, {"filter_copy": "0"}).filter_copy is False
+    monkeypatch.setenv("FLATIP_B200_FILTER_COPY", "false")
+    assert B200FlatIPStore(s).filter_copy is False
+    assert B200FlatIPStore(s, {"filter_copy": True}).filter_copy is True
+
+
 def test_load_file_not_found(tmp_path):
     from rag_inference_pipeline_b200 import B200FlatIPStore
 
