@@ -120,25 +120,47 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # CPU legs (oracle = test infrastructure; used ONLY as the reported baseline / reference arm)
 # ------------------------------------------------------------------------------------------
-def cpu_oracle_qps(total_rows, dim, dtype, batch, k, *, target_s=15.0, steps=1, warmup=0,
-                   max_rows=2_000_000):
-    """Times the C/OpenMP/BLAS restatement of faiss-cpu's IndexFlatIP.search (oracle/) on a bounded
-    sample of the workload and scales linearly in corpus rows (a flat scan is linear in N)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import numpy as np
+def host_mem_available_bytes():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 16 << 30
 
+
+def cpu_oracle_qps(total_rows, dim, dtype, batch, k, *, step_budget_s=12.0, steps=1, warmup=0,
+                   max_rows=10_000_000):
+    """Times the C/OpenMP/BLAS restatement of faiss-cpu's IndexFlatIP.search (oracle/) on a bounded
+    sample of the workload and scales linearly in corpus rows (a flat scan is linear in N).
+
+    Threads are set EXPLICITLY to every host core (torch.distributed.run exports OMP_NUM_THREADS=1,
+    which must not leak into the baseline); the reference's own default is min(16, cpu_count)
+    threads per node (/root/reference/src/pipeline/config/__init__.py:32-46, applied with
+    faiss.omp_set_num_threads, runtime.py:76) -- when that differs from all cores it is timed too
+    and reported as `reference_default_threads`.  The sample is the largest row count <= max_rows
+    (10 M: SURVEY 8(d)) that keeps one step within step_budget_s and the fp32 copy within 40 % of
+    the free host memory."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import c_oracle
     from rag_inference_pipeline_b200.synthetic import synthetic_queries
 
+    ncores = os.cpu_count() or 1
+    threads = c_oracle.set_threads(ncores)
     q = synthetic_queries(batch, dim)
-    pilot_rows = min(total_rows, 50_000)
+    pilot_rows = min(total_rows, 100_000)
     x = c_oracle.synthetic_corpus(0, pilot_rows, dim, dtype)
     c_oracle.knn_inner_product(q, x, k)  # warm (thread pool, BLAS init)
     t0 = time.perf_counter()
     c_oracle.knn_inner_product(q, x, k)
     pilot = time.perf_counter() - t0
-    rows = int(min(total_rows, max_rows, max(pilot_rows, pilot_rows * target_s / max(pilot, 1e-6))))
+    mem_rows = int(0.4 * host_mem_available_bytes() / (dim * 4))
+    rows = int(min(total_rows, max_rows, mem_rows,
+                   max(pilot_rows, pilot_rows * step_budget_s / max(pilot, 1e-6))))
     if rows != pilot_rows:
+        del x
         x = c_oracle.synthetic_corpus(0, rows, dim, dtype)
     for _ in range(warmup):
         c_oracle.knn_inner_product(q, x, k)
@@ -148,33 +170,58 @@ def cpu_oracle_qps(total_rows, dim, dtype, batch, k, *, target_s=15.0, steps=1, 
         c_oracle.knn_inner_product(q, x, k)
         times.append(time.perf_counter() - t0)
     t = sum(times) / len(times)
-    scaled = t * (total_rows / rows)
+    factor = total_rows / rows
+    scaled = t * factor
+    ref_default = None
+    ref_threads = min(16, ncores)
+    if ref_threads != ncores:
+        c_oracle.set_threads(ref_threads)
+        c_oracle.knn_inner_product(q, x, k)
+        t0 = time.perf_counter()
+        c_oracle.knn_inner_product(q, x, k)
+        t16 = time.perf_counter() - t0
+        ref_default = {"threads": ref_threads, "value": batch / (t16 * factor), "unit": UNIT}
+        c_oracle.set_threads(ncores)
+    else:
+        ref_default = {"threads": ref_threads, "value": batch / scaled, "unit": UNIT,
+                       "note": "equals all cores on this host"}
     return {
-        "value": batch / scaled, "unit": UNIT, "cores": c_oracle.max_threads(), "kind": "port",
-        "sample": (f"oracle/faiss_flat_restatement.c (faiss-cpu algorithm: sgemm blocks + "
-                   f"{'reservoir' if k >= 100 else 'heap'}, OpenBLAS) on {rows} of {total_rows} rows "
-                   f"(fp32 copies of the {dtype} values), batch {batch}, k {k}; {t:.2f} s per search, "
-                   f"scaled linearly to {total_rows} rows; host cpu_count={os.cpu_count()}"),
-        "ms_per_step_scaled": scaled * 1e3,
+        "value": batch / scaled, "unit": UNIT, "cores": threads, "kind": "port",
+        "sample": (f"oracle/faiss_flat_restatement.c (the builder's C port of faiss-cpu's algorithm: sgemm "
+                   f"blocks + {'reservoir' if k >= 100 else 'heap'}, OpenBLAS; NOT faiss itself) on {rows} of "
+                   f"{total_rows} rows (fp32 copies of the {dtype} values), batch {batch}, k {k}, "
+                   f"{threads} threads set explicitly; {t:.2f} s per search of the sample, scaled "
+                   f"linearly x{factor:.2f} to {total_rows} rows; host cpu_count={ncores}"),
+        "rows_timed": rows, "extrapolation_factor": factor, "ms_per_step_sample": t * 1e3,
+        "ms_per_step_scaled": scaled * 1e3, "reference_default_threads": ref_default,
+        "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
     }
+
+
+CPU_KEYS = ("value", "unit", "cores", "kind", "sample", "rows_timed", "extrapolation_factor",
+            "reference_default_threads", "omp_num_threads_env")
 
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU implementation of the path on the host cores.
     faiss-cpu cannot be installed here (no wheel, no network), so this is the oracle port of its
-    algorithm -- the one other place bench.py may execute oracle/."""
+    algorithm -- the one other place bench.py may execute oracle/.  Each step is one search of a
+    bounded row sample (sized so steps + warm-up fit ~200 s); `value` is scaled linearly to the full
+    corpus, `ms_per_step` is the time of one SAMPLE step as measured."""
     if rank != 0:
         return
     total_rows, dim, dtype, batch, k = workload(args)
-    r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, target_s=12.0, steps=args.steps,
-                       warmup=min(args.warmup, 1))
+    warm = min(args.warmup, 1)
+    r = cpu_oracle_qps(total_rows, dim, dtype, batch, k,
+                       step_budget_s=max(2.0, 200.0 / (args.steps + warm)), steps=args.steps, warmup=warm)
     line = {
         "impl": "reference", "metric": metric_name(args, total_rows, dim, dtype, batch, k), "value": r["value"], "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": r["ms_per_step_scaled"], "higher_is_better": True, "scaling": "strong",
+        "ms_per_step": r["ms_per_step_sample"], "ms_per_step_scaled_to_full_corpus": r["ms_per_step_scaled"],
+        "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
-        "cpu_baseline": {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k_: r[k_] for k_ in CPU_KEYS},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -297,25 +344,61 @@ def run_b200(args, rank, local_rank, world):
     phases = searcher.index.stat("phases")
     overflow = searcher.index.stat("overflow_queries")
 
-    # ---- sanity: sorted rows, ids in range, and a host spot check of returned scores ----
+    # ---- verification of the result the timed loop produced (rank 0 holds the GLOBAL result):
+    #   * rows best-first, ids in range and distinct per row;
+    #   * 9 returned scores recomputed in fp64 from regenerated rows;
+    #   * corpus blocks of 4096 rows regenerated on the host (first, middle, last and
+    #     every shard boundary region) and scored against ALL queries: no row outside the result
+    #     may beat the k-th returned score (beyond the dtype's tolerance), and every block row
+    #     that beats it by more than the tolerance must be IN the result;
+    #   * sha256 of the id matrix and of the distance matrix, so the N = 1/2/4/8 lines of a scaling
+    #     run can be compared with each other (rescoring is exact fp32 in a fixed order and the
+    #     tie-break is fixed, so sharding must not change a single bit).
     verify = None
     if rank == 0:
+        import hashlib
+
+        from rag_inference_pipeline_b200.synthetic import synthetic_corpus
         Dh, Ih = D.cpu().numpy(), I.cpu().numpy()
         ok_sorted = bool(np.all(np.diff(Dh, axis=1) <= 0))
         ok_range = bool(Ih.min() >= 0 and Ih.max() < total_rows) if total_rows >= k else True
-        from rag_inference_pipeline_b200.synthetic import synthetic_corpus
+        ok_distinct = all(len(set(r.tolist())) == len(r) for r in Ih[:: max(1, batch // 64)]) if total_rows >= k else True
         errs = []
         for qi in (0, batch // 2, batch - 1):
             for j in (0, k // 2, k - 1):
                 row = synthetic_corpus(int(Ih[qi, j]), 1, dim, dtype)[0].astype(np.float64)
                 errs.append(abs(float(row @ q_np[qi].astype(np.float64)) - float(Dh[qi, j])))
-        verify = {"sorted": ok_sorted, "ids_in_range": ok_range,
-                  "max_abs_err_of_9_recomputed_scores": max(errs)}
+        tol = 1e-5 if dtype == "f32" else 1e-3
+        blk = min(4096, total_rows)
+        starts = {0, max(0, total_rows // 2 - blk // 2), max(0, total_rows - blk)}
+        per = -(-total_rows // world)
+        for r_ in range(1, world):      # rows on both sides of every shard boundary
+            starts.add(max(0, min(total_rows - blk, r_ * per - blk // 2)))
+        missed = 0
+        rows_checked = 0
+        kth = Dh[:, -1].astype(np.float64)
+        margin = tol * np.maximum(1.0, np.abs(kth))
+        for b0 in sorted(starts):
+            xb = synthetic_corpus(b0, blk, dim, dtype).astype(np.float32)
+            sc = (q_np @ xb.T).astype(np.float64)                 # [batch, blk]
+            rows_checked += blk
+            better = sc > (kth + margin)[:, None]
+            for qi, ci in zip(*np.nonzero(better)):
+                if (b0 + int(ci)) not in set(Ih[qi].tolist()):
+                    missed += 1
+        verify = {"sorted": ok_sorted, "ids_in_range": ok_range, "ids_distinct_per_row": ok_distinct,
+                  "max_abs_err_of_9_recomputed_scores": max(errs),
+                  "h5_blocks": len(starts), "h5_rows_regenerated": rows_checked,
+                  "h5_rows_missed": missed,
+                  "ids_sha256": hashlib.sha256(np.ascontiguousarray(Ih).tobytes()).hexdigest(),
+                  "distances_sha256": hashlib.sha256(np.ascontiguousarray(Dh).tobytes()).hexdigest(),
+                  "ok": bool(ok_sorted and ok_range and ok_distinct and missed == 0
+                             and max(errs) <= 10 * tol)}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, target_s=12.0)
-        cpu_baseline = {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+        r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, step_budget_s=10.0)
+        cpu_baseline = {k_: r[k_] for k_ in CPU_KEYS}
 
     if rank == 0:
         peaks = load_peaks()

@@ -82,6 +82,34 @@ def max_threads() -> int:
     return int(load().oracle_max_threads())
 
 
+def set_threads(n: int) -> int:
+    """Pin BOTH thread pools of the port -- its own OpenMP loops and the OpenBLAS behind sgemm --
+    to `n` threads, whatever OMP_NUM_THREADS says (torch.distributed.run exports
+    OMP_NUM_THREADS=1 to every rank, which silently single-threaded the reference arm at N >= 2).
+    The reference does the same with ``faiss.omp_set_num_threads(settings.faiss_threads)``
+    (/root/reference/src/pipeline/runtime.py:76).  Returns the OpenBLAS thread count in effect."""
+    n = max(1, int(n))
+    lib = load()
+    lib.oracle_set_threads.argtypes = [ctypes.c_int]
+    lib.oracle_set_threads(n)
+    _find_openblas_sgemm()
+    got = n
+    if _blas_handle is not None:
+        for name in ("scipy_openblas_set_num_threads64_", "scipy_openblas_set_num_threads_64_"):
+            fn = getattr(_blas_handle, name, None)
+            if fn is not None:
+                fn.argtypes = [ctypes.c_int]
+                fn(n)
+                break
+        for name in ("scipy_openblas_get_num_threads64_", "scipy_openblas_get_num_threads_64_"):
+            fn = getattr(_blas_handle, name, None)
+            if fn is not None:
+                fn.restype = ctypes.c_int
+                got = int(fn())
+                break
+    return got
+
+
 def knn_inner_product(queries: np.ndarray, corpus: np.ndarray, k: int, *, id_base: int = 0,
                       nthreads: int = 0, use_blas: bool = True):
     """faiss-style CPU flat-IP search (fp32).  Returns (D float32 [B,k], I int64 [B,k])."""

@@ -263,6 +263,15 @@ int oracle_synthetic_rows(float* out, int64_t row0, int64_t nrows, int64_t dim, 
     return 0;
 }
 
+/* Pins the OpenMP team size of this library (independent of OMP_NUM_THREADS). */
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int oracle_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

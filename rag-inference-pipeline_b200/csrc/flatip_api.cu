@@ -190,6 +190,8 @@ struct fip_index {
     int cta_pair = 0;     // 0 = auto, 1 = single-CTA MMAs, 2 = CTA pairs (cta_group::2)
     int max_clusters = -1;  // co-resident 2-CTA clusters of the pair kernel (queried once)
     int profile = 0;      // 1: bracket every scan launch with CUDA events (bench roofline)
+    int debug_counts = 0; // 1: read the list lengths back after every filter launch (synchronises)
+    int64_t st_list_entries = 0, st_list_max = 0;
     std::vector<cudaEvent_t> ev;  // start/stop pairs
     int ev_used = 0;
     double st_scan_ms = 0.0;      // device time of the scan kernels of the last search
@@ -664,6 +666,12 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         m = std::min<int64_t>(m, n - pos);
         rc = scan(pos, pos + m, false);
         if (rc) return rc;
+        if (idx->debug_counts) {   // survivor statistics (synthetic-distribution study)
+            std::vector<uint32_t> h((size_t)nq);
+            FIP_CUDA(cudaMemcpyAsync(h.data(), idx->cnt.p, sizeof(uint32_t) * (size_t)nq, cudaMemcpyDeviceToHost, c.stream));
+            FIP_CUDA(cudaStreamSynchronize(c.stream));
+            for (uint32_t v : h) { idx->st_list_entries += v; idx->st_list_max = std::max<int64_t>(idx->st_list_max, v); }
+        }
         pos += m;
         phases++;
         rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max, live);
@@ -759,6 +767,7 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
         idx->ev.resize(128);
         for (auto& e : idx->ev) FIP_CUDA(cudaEventCreate(&e));
     }
+    idx->st_list_entries = 0; idx->st_list_max = 0;
     Mode m0;
     m0.safe = idx->force_safe != 0;
     SearchInfo info;
@@ -1317,6 +1326,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         }
     } else if (k == "profile_events") {
         idx->profile = value != 0;
+    } else if (k == "debug_counts") {
+        idx->debug_counts = value != 0;
     } else if (k == "force_safe_mode") {
         idx->force_safe = value != 0;
     } else {
@@ -1350,6 +1361,8 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
         const size_t i = (size_t)atoi(k.c_str() + (gap ? 7 : 8));
         return i < v.size() ? (int64_t)(v[i] * 1e6) : -1;
     }
+    if (k == "list_entries_after_filter") return idx->st_list_entries;
+    if (k == "list_max_after_filter") return idx->st_list_max;
     if (k == "host_batches") return idx->st_batches;
     if (k == "host_calls") return idx->st_calls;
     if (k == "coalesced_calls") return idx->st_coalesced_calls;

@@ -97,6 +97,10 @@ def test_parity_with_oracle(variant, dtype, n, dim, nq, k):
     Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, min(k + 1, max(n, 1)) if n > k else k)
     kplus1 = Dr[:, k] if Dr.shape[1] > k else None
     Dr, Ir = Dr[:, :k], Ir[:, :k]
+    # second, independently written checker on the same case: the C port of faiss's algorithm
+    # (sgemm blocks + heap / reservoir) must agree with the numpy fp64 oracle
+    Dc, Ic = c_oracle.knn_inner_product(queries, corpus, k)
+    _check(Dc, Ic, Dr, Ir, dtype, kplus1)
     idx = _index(dim, dtype)
     idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
     idx.set_variant(variant)
@@ -687,3 +691,97 @@ def test_large_scale_properties():
             better = np.nonzero(s[qi] > D[qi, -1] + 1e-3 * max(1.0, abs(D[qi, -1])))[0] + b0
             assert set(better.tolist()) <= set(I[qi].tolist())
     idx.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# The BASELINE configurations AT THEIR REAL SIZES.  The checker is the C port
+# of faiss's algorithm (fp32 sgemm blocks + heap / reservoir) run over row chunks and merged with
+# the numpy oracle's k-way merge; both sides accumulate exact products of the stored values in
+# fp32, so scores must agree to ~1e-5 and the near-tie windows of the id rule are tiny.
+# ---------------------------------------------------------------------------------------------
+FULL_RTOL = 2e-5
+
+
+def _c_oracle_chunked(q, row0, n, dim, dtype, k, chunk_rows):
+    c_oracle.set_threads(os.cpu_count() or 1)
+    Ds, Is = [], []
+    for r0 in range(0, n, chunk_rows):
+        m = min(chunk_rows, n - r0)
+        x = c_oracle.synthetic_corpus(row0 + r0, m, dim, dtype)
+        D, I = c_oracle.knn_inner_product(q, x, k, id_base=row0 + r0)
+        Ds.append(D)
+        Is.append(I)
+        del x
+    return flatip_oracle.merge_sorted_lists(np.stack(Ds), np.stack(Is), k)
+
+
+def _check_full(D, I, Dr, Ir, k):
+    """Dr / Ir hold k + 1 columns (the (k+1)-th closes the last near-tie window)."""
+    res = flatip_oracle.compare_with_oracle(D, I, Dr[:, :k], Ir[:, :k], rtol=FULL_RTOL,
+                                            kplus1_ref=Dr[:, k])
+    assert res["score_ok"], res
+    assert res["id_mismatch_outside_window"] == 0, res
+    assert res["id_mismatch_total"] <= max(2, I.size // 2000), res
+    assert np.all(np.diff(D, axis=1) <= 0)
+    return res
+
+
+def test_cfg2_full_size_all_variants():
+    """BASELINE configs[1] in full: 1 M x 768 fp32, batch 32, k = 10, against the fp64 oracle
+    (tolerance 1e-5 as north_star states for fp32), on every route the index can take: tensor-core
+    filter on the fp16 copy (default), tf32 filter on the fp32 rows (filter_copy = 0, the
+    memory-neutral configuration) and the exact streaming kernel K2."""
+    n, dim, nq, k = 1_000_000, 768, 32, 10
+    corpus = c_oracle.synthetic_corpus(0, n, dim, "f32")
+    q = synthetic.synthetic_queries(nq, dim)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k + 1)
+    Dc, Ic = c_oracle.knn_inner_product(q, corpus, k + 1)          # the two checkers agree
+    _check_full(Dc[:, :k], Ic[:, :k], Dr, Ir, k)
+    del corpus
+    idx = _index(dim, "f32", capacity_rows=n)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    got = {}
+    for name, opts in (("filter16", {}), ("tf32", {"filter_copy": 0}), ("stream", {"variant": "stream"})):
+        idx.set_variant(opts.get("variant", "auto"))
+        idx.set_option("filter_copy", opts.get("filter_copy", 1))
+        D, I = idx.search(q, k)
+        assert idx.last_variant() == ("stream" if name == "stream" else "tensor")
+        assert idx.stat("filter_f16") == (1 if name == "filter16" else 0)
+        res = flatip_oracle.compare_with_oracle(D, I, Dr[:, :k], Ir[:, :k], rtol=1e-5, kplus1_ref=Dr[:, k])
+        assert res["score_ok"] and res["id_mismatch_outside_window"] == 0, (name, res)
+        assert res["id_mismatch_total"] <= 2, (name, res)
+        got[name] = (D, I)
+    assert np.array_equal(got["filter16"][1], got["tf32"][1]) and np.array_equal(got["filter16"][0], got["tf32"][0])
+    assert np.array_equal(got["filter16"][1], got["stream"][1])
+    idx.close()
+
+
+def test_cfg3_shard_full_size():
+    """One 12.5 M x 768 fp16 shard of the headline configuration (BASELINE configs[2]: shard 3 of
+    8, global rows [37.5 M, 50 M)), batch 1024, k = 100: ONE filter launch over 1.25e7 rows with
+    live thresholds, exactly as the bench runs it, against the C port over the same rows."""
+    dim, n, nq, k, row0 = 768, 12_500_000, 1024, 100, 37_500_000
+    q = synthetic.synthetic_queries(nq, dim)
+    idx = _index(dim, "f16", capacity_rows=n, id_base=row0)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, row0)
+    D, I = idx.search(q, k)
+    assert idx.last_variant() == "tensor" and idx.stat("phases") == 2
+    assert idx.stat("overflow_queries") == 0
+    assert I.min() >= row0 and I.max() < row0 + n
+    idx.close()
+    Dr, Ir = _c_oracle_chunked(q, row0, n, dim, "f16", k + 1, 2_500_000)
+    _check_full(D, I, Dr, Ir, k)
+
+
+def test_cfg5_full_size():
+    """BASELINE configs[4] in full: 10 M x 384 fp16, batch 256, k = 1024 (the large-k selection
+    stress) against the C port (reservoir path, k >= 100)."""
+    dim, n, nq, k = 384, 10_000_000, 256, 1024
+    q = synthetic.synthetic_queries(nq, dim)
+    idx = _index(dim, "f16", capacity_rows=n)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    D, I = idx.search(q, k)
+    assert idx.last_variant() == "tensor" and idx.stat("overflow_queries") == 0
+    idx.close()
+    Dr, Ir = _c_oracle_chunked(q, 0, n, dim, "f16", k + 1, 5_000_000)
+    _check_full(D, I, Dr, Ir, k)
