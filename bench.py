@@ -283,41 +283,49 @@ def run_b200(args, rank, local_rank, world):
     if args.variant != "auto":
         searcher.index.set_variant(args.variant)
     searcher.index.set_option("profile_events", 1)
+    for kv in args.opt:
+        key, val = kv.split("=")
+        searcher.index.set_option(key, int(val))
 
     q_np = synthetic_queries(batch, dim)
     q_dev = torch.from_numpy(q_np).to(dev)
     q_pinned = torch.from_numpy(q_np).pin_memory()
 
     # ---- device-resident timing ("value") ----
+    # search_tensor only ENQUEUES (local search + K4 exchange/merge): the verdict on the searches
+    # (did any shard have to redo a query?) is read once, after the timed region, by check().
     for _ in range(max(args.warmup, 3)):
         D, I = searcher.search_tensor(q_dev, k)
+    warm_status = searcher.check()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches = 0
-    scan_ns = 0
-    scan_launches = 0
-    per_scan = {}   # scan launch index -> [rows, total ns, count]
     barrier()
     e0.record()
     for _ in range(args.steps):
         D, I = searcher.search_tensor(q_dev, k)
-        launches += searcher.index.stat("launches") + (1 if world > 1 else 0)   # + exchange/merge kernel
-        scan_ns += searcher.index.stat("scan_time_ns")
-        scan_launches += searcher.index.stat("scan_launches")
-        for i in range(64):
-            ns = searcher.index.stat(f"scan_ns_{i}")
-            if ns < 0:
-                break
-            rec = per_scan.setdefault(i, [searcher.index.stat(f"scan_rows_{i}"), 0, 0])
-            rec[1] += ns
-            rec[2] += 1
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
+    timed_status = searcher.check()   # synchronises; collects the per-launch CUDA-event times
+    if warm_status or timed_status:
+        # some search flagged a query: its result is only valid after a redo, which the timed loop
+        # did not pay for -- say so instead of reporting a number for skipped work
+        sys.exit(f"bench: a search was flagged (status warm={warm_status} timed={timed_status}); "
+                 "the asynchronous timing loop is not valid for this input")
+    launches = args.steps * (searcher.index.stat("launches") + (1 if world > 1 else 0))  # + exchange/merge kernel
+    scan_ns = searcher.index.stat("scan_time_ns")
+    scan_launches = searcher.index.stat("scan_launches")
+    searches_timed = max(1, searcher.index.stat("scan_searches"))
+    per_scan = {}   # scan launch index -> [rows, total ns, count]
+    for i in range(64):
+        ns = searcher.index.stat(f"scan_ns_{i}")
+        if ns < 0:
+            break
+        per_scan[i] = [searcher.index.stat(f"scan_rows_{i}"), ns, searches_timed]
 
     # ---- end-to-end timing through the host-buffer API ("e2e"): pinned host queries -> H2D ->
     #      search -> D2H of distances + ids, every step ----
@@ -325,7 +333,7 @@ def run_b200(args, rank, local_rank, world):
         if world == 1:
             return searcher.index.search(q_np, k)  # fip_search: pinned staging inside the C ABI
         qd = q_pinned.to(dev, non_blocking=True)
-        d, i = searcher.search_tensor(qd, k)
+        d, i = searcher.search_tensor_checked(qd, k)
         return d.cpu(), i.cpu()
 
     e2e_step()
@@ -432,7 +440,8 @@ def run_b200(args, rank, local_rank, world):
                           "phases_per_search": len(per_scan)}
         roof["scan_bytes_per_element"] = esize
         roof["launches_timed"] = scan_launches
-        roof["all_scan_launches_ms_per_step"] = scan_s * 1e3 / args.steps
+        roof["all_scan_launches_ms_per_step"] = scan_s * 1e3 / searches_timed
+        roof["searches_timed"] = searches_timed
         roof["whole_search_frac"] = None
         if tensor_bound and ms_per_step > 0:
             roof["whole_search_frac"] = (2.0 * batch * n_local * dim / (ms_per_step * 1e-3) / 1e12
@@ -440,7 +449,7 @@ def run_b200(args, rank, local_rank, world):
         elif ms_per_step > 0:
             roof["whole_search_frac"] = ((float(n_local) * dim * esize) / (ms_per_step * 1e-3) / 1e9
                                          / peaks["hbm_gbs"])
-        roof["kernel_share_of_step"] = scan_s * 1e3 / ms_max if ms_max > 0 else None
+        roof["kernel_share_of_step"] = (scan_s * 1e3 / searches_timed) / ms_per_step if ms_per_step > 0 else None
         traffic_path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         roof["traffic"] = None
         if os.path.exists(traffic_path):
@@ -463,6 +472,7 @@ def run_b200(args, rank, local_rank, world):
             "variant": variant, "phases_per_search": phases, "overflow_queries": overflow,
             "uncertified_queries": searcher.index.stat("uncertified_queries"),
             "cta_group": searcher.index.stat("cta_group"),
+            "deferred_epilogue": searcher.index.stat("deferred_epilogue"), "options": args.opt,
             "exchange": searcher.exchange_used,
             "corpus_load_s": load_s, "verify": verify,
         }
@@ -638,6 +648,7 @@ def main():
     ap.add_argument("--k", type=int, default=0)
     ap.add_argument("--variant", choices=["auto", "stream", "tensor"], default="auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="index option key=value (A/B runs)")
     ap.add_argument("--exchange", choices=["auto", "p2p", "nccl"], default="auto",
                     help="N > 1: fused peer-memory exchange + merge kernel, or NCCL all-gather + merge")
     args = ap.parse_args()

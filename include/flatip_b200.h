@@ -60,6 +60,10 @@ void fip_destroy(fip_index* idx);
 
 /* faiss Index::add(n, x): append n fp32 host rows, rounded (RNE) to the storage dtype. */
 int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n);
+/* Same for host rows in any fip_dtype: fp32 rows are rounded to the storage dtype, rows already in
+ * the storage dtype are uploaded as they are (a 16-bit corpus file crosses PCIe as 16 bits), 16-bit
+ * rows into an fp32 index are widened on the device.  Pinned, double-buffered staging. */
+int fip_add_host(fip_index* idx, const void* rows, int64_t n, int32_t dtype);
 /* Same, rows already on the device in `dtype` (fp32 is converted, equal dtypes are copied). */
 int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtype);
 /* Append n synthetic rows generated on the device: global rows [global_row0, global_row0+n) of
@@ -88,6 +92,23 @@ int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, floa
  * caller-supplied cudaStream_t (0 = the index's own stream).  Blocking on that stream. */
 int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
                       float* distances_dev, int64_t* ids_dev, void* cuda_stream);
+
+/*
+ * Asynchronous form: enqueues the whole search on `cuda_stream` and returns without waiting.  A
+ * search can, rarely (adversarial row order, near-tie clusters tighter than the tensor-core
+ * filter's resolution), need some queries redone; the blocking forms do that before they return,
+ * this one only records it on the device.  fip_search_status synchronises the stream of the last
+ * asynchronous search and reports whether ANY asynchronous search since the previous status call
+ * was flagged (bit 0: a candidate list overflowed, bit 1: a query could not be certified exact);
+ * the results of a flagged search must be recomputed with fip_search_device.  All asynchronous
+ * searches on one index must be ordered on one stream.  fip_search_flags_device returns the device
+ * address of the two summary words of the search enqueued last (consumed by fip_exchange_merge, so
+ * the status of every shard travels with its rows).
+ */
+int fip_search_device_async(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
+                            float* distances_dev, int64_t* ids_dev, void* cuda_stream);
+int fip_search_status(fip_index* idx, int32_t* flagged);
+const uint32_t* fip_search_flags_device(const fip_index* idx);
 
 /*
  * Cross-shard merge (K3): in_d / in_i are device buffers [g, nq, k_in] as an all-gather of the
@@ -128,7 +149,46 @@ int fip_exchange_connect_ipc(fip_exchange* x, const void* all_handles);
 int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all);
 int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
                        float* out_d, int64_t* out_i, void* cuda_stream);
+/* Same, and the shards' search statuses travel with the rows: flags_loc_dev = this rank's
+ * fip_search_flags_device() (or null), *out_status_dev (device word, OR-accumulated, may be null)
+ * receives bit 0 / bit 1 when ANY rank's local search overflowed / could not be certified. */
+int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq,
+                              int32_t k, float* out_d, int64_t* out_i, const uint32_t* flags_loc_dev,
+                              uint32_t* out_status_dev, void* cuda_stream);
 void fip_exchange_destroy(fip_exchange* x);
+
+/*
+ * fip_group: ONE corpus row-sharded over several GPUs of THIS process behind one blocking search
+ * call -- what lets the reference's single in-process call site
+ *     registry.get("faiss_store").search(embeddings, k)
+ *     (/root/reference/src/pipeline/services/retrieval/api.py:383-389)
+ * use every GPU of the box (north_star: "row-sharded across the 8 GPUs", same component API).
+ * Shard r lives on devices[r] and owns global rows [r * per, (r + 1) * per), per =
+ * ceil(planned_rows / n_devices); rows are added in global order.  fip_group_search: one host
+ * thread + stream per device, local search, K4 exchange + merge over NVLink peer memory, the global
+ * result is returned from devices[0].  Same contract, coalescing and error behaviour as fip_search.
+ * cfg->device is ignored; cfg->id_base is the global id of row 0.
+ */
+typedef struct fip_group fip_group;
+int fip_group_create(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
+                     int64_t planned_rows, fip_group** out);
+void fip_group_destroy(fip_group* g);
+int32_t fip_group_size(const fip_group* g);
+/* Shard r as a plain index (options, statistics, reconstruct; do not add rows through it). */
+fip_index* fip_group_shard(fip_group* g, int32_t r);
+int64_t fip_group_ntotal(const fip_group* g);
+/* Append the next n global rows: generated on the owning devices / uploaded from host rows in
+ * `dtype` (every device pulls its own slice through its own pinned staging, in parallel). */
+int fip_group_add_synthetic(fip_group* g, int64_t n, uint64_t seed);
+int fip_group_add_host(fip_group* g, const void* rows, int64_t n, int32_t dtype);
+int fip_group_reset(fip_group* g);
+int fip_group_search(fip_group* g, const float* queries, int64_t nq, int32_t k, float* distances,
+                     int64_t* ids);
+/* Options are applied to every shard ("coalesce*" at the group); statistics are summed over the
+ * shards' last searches, plus "devices", "rows_per_shard", "searches", "flagged_searches" (searches
+ * in which some shard had to redo a query, costing a second exchange), "exchange_launches". */
+int fip_group_set_option(fip_group* g, const char* key, int64_t value);
+int64_t fip_group_get_stat(const fip_group* g, const char* key);
 
 /* Options: "variant" (fip_variant), "stream_max_batch" (largest batch the AUTO rule gives to the
  * streaming kernel; 0 = default, by arithmetic intensity: batch <= sizeof(storage element)), "query_split" (0 auto / 1 / 2 sixteen-bit terms per query
@@ -148,9 +208,12 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value);
  * with a tighter variant), "stream_redo_queries" (of those and the overflowed ones, how many ended
  * on the exact streaming kernel), "query_split_used", "filter_f16" (1: the last search filtered on the
  * fp16 copy of an fp32 corpus),
- * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used), "scan_ns_<i>" / "scan_rows_<i>" / "gap_ns_<i>" (per scan launch i: device time, corpus rows, time to the
- * next scan), "scan_time_ns" / "scan_launches" (device time and count of the scan
- * kernels, when "profile_events" is on); cumulative: "total_launches", "total_searches",
+ * "candidate_capacity", "cta_group" (1 or 2: MMA CTA group the tensor variant used); with
+ * "profile_events" on, over the searches COLLECTED by the last blocking search / fip_search_status
+ * (asynchronous searches accumulate until their status is read): "scan_searches" (how many),
+ * "scan_time_ns" / "scan_launches" (device time and count of their scan kernels), "scan_ns_<i>" /
+ * "gap_ns_<i>" (summed over those searches per scan launch index i: device time, time to the next
+ * scan) and "scan_rows_<i>" (corpus rows of launch i); cumulative: "total_launches", "total_searches",
  * "host_calls" / "host_batches" (fip_search calls and the batches they were served in),
  * "coalesced_calls" (calls that shared a batch with another call); "last_batch_calls". */
 int64_t fip_get_stat(const fip_index* idx, const char* key);

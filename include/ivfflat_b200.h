@@ -82,7 +82,10 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
  * stats of the last search: "launches", "phases", "tiles", "tiles16", "rows_scanned",
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
  * "tensor_items", "tensor_pairs", "crowded_window" (1: the tf32 filter's exactness window overflowed
- * for some query and the batch was redone with the fp32 filter), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm",
+ * for some query and the batch was redone with the fp32 filter, then -- clusters of more than 2k + 64
+ * duplicates -- in safe mode with a window of half the list capacity), "crowded_window_unresolved"
+ * (1: even that window overflowed: over 8192 rows tie within fp32 rounding for some query, whose
+ * result is then exact only up to that rounding), "overflow", "candidate_capacity", "plan_us", "scan16_ctas_per_sm",
  * "device_plan" (1: the last search was planned on the device), "tensor_f16" (1: the last search's
  * tensor-core filter ran on the fp16 copy). */
 int fivf_set_option(fivf_index* h, const char* key, int64_t value);

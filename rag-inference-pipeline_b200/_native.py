@@ -37,7 +37,12 @@ EXPORTED_SYMBOLS = (
     "fip_search_device", "fip_merge_device", "fip_merge_strided_device", "fip_set_option", "fip_get_stat", "fip_last_error",
     "fip_abi_version", "fip_compiled_sm",
     "fip_exchange_create", "fip_exchange_ipc_handle", "fip_exchange_connect_ipc",
-    "fip_exchange_connect_local", "fip_exchange_merge", "fip_exchange_destroy",
+    "fip_exchange_connect_local", "fip_exchange_merge", "fip_exchange_merge_status",
+    "fip_exchange_destroy",
+    "fip_add_host", "fip_search_device_async", "fip_search_status", "fip_search_flags_device",
+    "fip_group_create", "fip_group_destroy", "fip_group_size", "fip_group_shard", "fip_group_ntotal",
+    "fip_group_add_synthetic", "fip_group_add_host", "fip_group_reset", "fip_group_search",
+    "fip_group_set_option", "fip_group_get_stat",
 )
 # include/ivfflat_b200.h (IVF-Flat L2 operator, same shared library)
 IVF_EXPORTED_SYMBOLS = (
@@ -129,6 +134,39 @@ def load_library():
         lib.fip_exchange_merge.restype = c.c_int
         lib.fip_exchange_destroy.argtypes = [P]
         lib.fip_exchange_destroy.restype = None
+        lib.fip_exchange_merge_status.argtypes = [P, P, P, c.c_int64, c.c_int32, P, P, P, P, P]
+        lib.fip_exchange_merge_status.restype = c.c_int
+        lib.fip_add_host.argtypes = [P, P, c.c_int64, c.c_int32]
+        lib.fip_add_host.restype = c.c_int
+        lib.fip_search_device_async.argtypes = [P, P, c.c_int64, c.c_int32, P, P, P]
+        lib.fip_search_device_async.restype = c.c_int
+        lib.fip_search_status.argtypes = [P, c.POINTER(c.c_int32)]
+        lib.fip_search_status.restype = c.c_int
+        lib.fip_search_flags_device.argtypes = [P]
+        lib.fip_search_flags_device.restype = P
+        lib.fip_group_create.argtypes = [c.POINTER(FipConfig), c.POINTER(c.c_int32), c.c_int32, c.c_int64,
+                                         c.POINTER(P)]
+        lib.fip_group_create.restype = c.c_int
+        lib.fip_group_destroy.argtypes = [P]
+        lib.fip_group_destroy.restype = None
+        lib.fip_group_size.argtypes = [P]
+        lib.fip_group_size.restype = c.c_int32
+        lib.fip_group_shard.argtypes = [P, c.c_int32]
+        lib.fip_group_shard.restype = P
+        lib.fip_group_ntotal.argtypes = [P]
+        lib.fip_group_ntotal.restype = c.c_int64
+        lib.fip_group_add_synthetic.argtypes = [P, c.c_int64, c.c_uint64]
+        lib.fip_group_add_synthetic.restype = c.c_int
+        lib.fip_group_add_host.argtypes = [P, P, c.c_int64, c.c_int32]
+        lib.fip_group_add_host.restype = c.c_int
+        lib.fip_group_reset.argtypes = [P]
+        lib.fip_group_reset.restype = c.c_int
+        lib.fip_group_search.argtypes = [P, P, c.c_int64, c.c_int32, P, P]
+        lib.fip_group_search.restype = c.c_int
+        lib.fip_group_set_option.argtypes = [P, c.c_char_p, c.c_int64]
+        lib.fip_group_set_option.restype = c.c_int
+        lib.fip_group_get_stat.argtypes = [P, c.c_char_p]
+        lib.fip_group_get_stat.restype = c.c_int64
         lib.fip_set_option.argtypes = [P, c.c_char_p, c.c_int64]
         lib.fip_set_option.restype = c.c_int
         lib.fip_get_stat.argtypes = [P, c.c_char_p]

@@ -24,6 +24,7 @@ sqlite is the storage engine on both sides and stays out of scope.
 """
 from __future__ import annotations
 
+import copy
 import sqlite3
 import threading
 from pathlib import Path
@@ -32,6 +33,9 @@ from typing import Any, Iterable, Sequence
 import numpy as np
 
 __all__ = ["CandidateDocument", "CandidateFeed", "create_candidate_feed"]
+
+
+CONFIGURED = object()   # sentinel: "use settings.truncate_length" (None means: do not truncate)
 
 
 class CandidateDocument:
@@ -147,12 +151,15 @@ class CandidateFeed:
         self.stats["selects"] += 1
         return {r[0]: CandidateDocument(r[0], r[1] or "", r[2] or "", r[3] or None) for r in rows}
 
-    def fetch(self, ids: np.ndarray | Sequence[Sequence[int]], truncate_length: int | None = None,
-              ) -> list[list[CandidateDocument]]:
+    def fetch(self, ids: np.ndarray | Sequence[Sequence[int]],
+              truncate_length: int | None | object = CONFIGURED) -> list[list[CandidateDocument]]:
         """ids ``[B, k]`` (or ragged lists) -> one document list per query, id-matrix order.
 
-        ``truncate_length=None`` uses the configured length (``settings.truncate_length``); pass 0
-        or a negative value to leave the text untouched.
+        ``truncate_length``: ``CONFIGURED`` (default) uses ``settings.truncate_length``; ``None``
+        leaves the text untouched; an integer truncates every field to that many characters --
+        ``0`` yields empty strings, exactly like the reference (``document_store.py:297-298``
+        tests ``is not None``).  Documents are copied per query: mutating one result list never
+        shows up in another.
         """
         if isinstance(ids, np.ndarray):
             mat = np.ascontiguousarray(ids, dtype=np.int64)
@@ -170,17 +177,17 @@ class CandidateFeed:
         distinct = np.unique(flat[flat >= 0])
         self.stats["distinct_ids"] += int(distinct.size)
         docs = self._fetch_distinct(distinct.tolist()) if distinct.size else {}
-        if truncate_length is None:
+        if truncate_length is CONFIGURED:
             truncate_length = self.truncate_length
-        if truncate_length is not None and truncate_length > 0:
-            docs = {i: d.truncate(truncate_length) for i, d in docs.items()}
+        if truncate_length is not None:
+            docs = {i: d.truncate(int(truncate_length)) for i, d in docs.items()}
         out = []
         for row in per_query:
-            out.append([docs[i] for i in row.tolist() if i in docs])
+            out.append([copy.copy(docs[i]) for i in row.tolist() if i in docs])
         return out
 
     def fetch_with_scores(self, distances: np.ndarray, ids: np.ndarray,
-                          truncate_length: int | None = None,
+                          truncate_length: int | None | object = CONFIGURED,
                           ) -> list[list[tuple[CandidateDocument, float]]]:
         """(D, I) of ``store.search`` -> per query ``[(document, score), ...]`` for the reranker
         (the pairing api.py:483-492 does with ``zip(docs, scores)``, except that a score stays with
@@ -201,14 +208,14 @@ class CandidateFeed:
         """document_store.py:193: documents of one id list, input order, untruncated."""
         if not doc_ids:
             return []
-        return self.fetch([doc_ids], truncate_length=0)[0]
+        return self.fetch([doc_ids], truncate_length=None)[0]
 
     def fetch_documents_batch(self, doc_ids_batch: list[list[int]], truncate_length: int | None = None,
                               ) -> list[list[CandidateDocument]]:
         """document_store.py:270: same result, one SELECT for the whole batch."""
         if not doc_ids_batch:
             return []
-        return self.fetch(doc_ids_batch, truncate_length=0 if truncate_length is None else truncate_length)
+        return self.fetch(doc_ids_batch, truncate_length=truncate_length)
 
     def clear_cache(self) -> None:
         """Nothing cached per id: the in-memory database IS the cache."""

@@ -127,11 +127,17 @@ int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t r
     return FIP_OK;
 }
 
-// flags: [0 .. nq] overflow (any, per query), [nq+1 .. 2nq+1] uncertified (any, per query)
-__global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* flags, int nq) {
+// flags: select.cuh flag_slot().  `sticky` (may be null): the summary words an earlier, never
+// checked (asynchronous) search left behind are folded into it before they are cleared, so
+// fip_search_status still sees them.  grid >= flag_words(nq) threads.
+__global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* flags, uint32_t* sticky, int nq) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nq) { thr[i] = kNegInf; cnt[i] = 0u; }
-    if (i <= nq) { flags[i] = 0u; flags[nq + 1 + i] = 0u; }
+    if (i < 2 && sticky && flags[i]) atomicOr(sticky, 1u << i);
+    if (i < 2 + 2 * nq) flags[i] = 0u;
+}
+__global__ void fold_sticky_kernel(uint32_t* flags, uint32_t* sticky) {
+    if (threadIdx.x < 2 && flags[threadIdx.x]) { atomicOr(sticky, 1u << threadIdx.x); flags[threadIdx.x] = 0u; }
 }
 __global__ void fill_padding_kernel(float* d, int64_t* id, int64_t n) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -157,6 +163,74 @@ __global__ void scatter_results_kernel(const float* sd, const int64_t* si, const
 
 }  // namespace
 
+// Request coalescing (fip_search, fip_group_search): host callers that arrive while a search is
+// running are queued; whoever finds no leader becomes one, takes every queued request with the same
+// k (up to max_batch queries) and runs them as ONE batch.  Below ~210 queries a flat scan is
+// HBM-bound -- its cost does not depend on the batch size -- so riding along is free.
+struct HostRequest {
+    const float* q; int64_t nq; int k; float* d; int64_t* i;
+    int rc = 0; bool done = false; std::string err;
+};
+struct Coalescer {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<HostRequest*> pending;
+    bool leader_active = false;
+    int enabled = 1;
+    int64_t max_batch = 4096;
+    int64_t st_batches = 0, st_calls = 0, st_coalesced_calls = 0, st_last_batch_calls = 0;
+    int64_t st_queries = 0, st_distinct = 0;   // in-batch dedupe: queries received / actually searched
+
+    void count(size_t calls) {
+        st_batches++;
+        st_calls += (int64_t)calls;
+        st_last_batch_calls = (int64_t)calls;
+        if (calls > 1) st_coalesced_calls += (int64_t)calls;
+    }
+    // run_batch(const std::vector<HostRequest*>&) -> int; its error text is taken from g_last_error
+    template <typename F>
+    int submit(HostRequest& me, F&& run_batch) {
+        if (!enabled) {
+            std::vector<HostRequest*> one{&me};
+            return run_batch(one);
+        }
+        std::unique_lock<std::mutex> lk(mu);
+        pending.push_back(&me);
+        while (!me.done) {
+            if (leader_active) {
+                cv.wait(lk);
+                continue;
+            }
+            // become the leader for one batch: the oldest request sets k; every queued request with
+            // that k rides along, in arrival order, while the batch stays within max_batch queries
+            leader_active = true;
+            std::vector<HostRequest*> batch;
+            const int bk = pending.front()->k;
+            int64_t total = 0;
+            for (auto it = pending.begin(); it != pending.end();) {
+                HostRequest* p = *it;
+                if (p->k == bk && (batch.empty() || total + p->nq <= max_batch)) {
+                    batch.push_back(p);
+                    total += p->nq;
+                    it = pending.erase(it);
+                } else {
+                    ++it;
+                }
+            }
+            lk.unlock();
+            const int brc = run_batch(batch);
+            const std::string berr = brc ? g_last_error : std::string();
+            lk.lock();
+            for (auto* p : batch) { p->rc = brc; p->err = berr; p->done = true; }
+            leader_active = false;
+            cv.notify_all();
+        }
+        lk.unlock();
+        if (me.rc) g_last_error = me.err;
+        return me.rc;
+    }
+};
+
 struct fip_index {
     fip_config cfg{};
     int num_sms = 0;
@@ -166,21 +240,7 @@ struct fip_index {
     int64_t cap_rows = 0;
     std::mutex mu;
 
-    // Request coalescing (fip_search): host callers that arrive while a search is running are
-    // queued; whoever finds no leader becomes one, takes every queued request with the same k (up
-    // to coalesce_max queries) and runs them as ONE batch.  Below ~210 queries a flat scan is
-    // HBM-bound -- its cost does not depend on the batch size -- so riding along is free.
-    struct Pending {
-        const float* q; int64_t nq; int k; float* d; int64_t* i;
-        int rc = 0; bool done = false; std::string err;
-    };
-    std::mutex qmu;
-    std::condition_variable qcv;
-    std::deque<Pending*> pending;
-    bool leader_active = false;
-    int coalesce = 1;
-    int64_t coalesce_max = 4096;
-    int64_t st_batches = 0, st_calls = 0, st_coalesced_calls = 0, st_last_batch_calls = 0;
+    Coalescer co;   // fip_search callers that arrive during a search share the next batch
 
     // options
     int variant = FIP_VARIANT_AUTO;
@@ -188,16 +248,24 @@ struct fip_index {
     int force_safe = 0;
     int query_split = 0;  // 0 = auto (1 for fp16 / fp32 storage, 2 for bf16)
     int cta_pair = 0;     // 0 = auto, 1 = single-CTA MMAs, 2 = CTA pairs (cta_group::2)
-    int max_clusters = -1;  // co-resident 2-CTA clusters of the pair kernel (queried once)
+    int max_clusters[2] = {-1, -1};  // co-resident 2-CTA clusters of the pair kernel (plain / deferred epilogue)
+    int defer_epilogue = 0;  // 0 = auto (k >= 256), 1 = never, 2 = always
+    int64_t st_deferred = 0;
     int profile = 0;      // 1: bracket every scan launch with CUDA events (bench roofline)
     int debug_counts = 0; // 1: read the list lengths back after every filter launch (synchronises)
     int64_t st_list_entries = 0, st_list_max = 0;
     std::vector<cudaEvent_t> ev;  // start/stop pairs
-    int ev_used = 0;
-    double st_scan_ms = 0.0;      // device time of the scan kernels of the last search
-    int64_t st_scan_launches = 0;
-    std::vector<float> st_scan_each, st_gap_each;  // per scan launch; gap = time to the next scan
-    std::vector<int64_t> st_scan_rows, st_scan_rows_pending;  // corpus rows of each timed scan
+    // The events form a ring; every search records which slice it used (EvSet).  Timings are
+    // COLLECTED when a search is finished / its status is read: asynchronous searches accumulate, so
+    // the statistics below cover every search since the previous collection (one search for the
+    // blocking calls): sums per scan-launch index, plus how many searches contributed.
+    struct EvSet { uint64_t start; int count; std::vector<int64_t> rows; int launches; };
+    uint64_t ev_head = 0;
+    std::vector<EvSet> ev_sets;
+    double st_scan_ms = 0.0;      // device time of the scan kernels of the collected searches
+    int64_t st_scan_launches = 0, st_scan_searches = 0;
+    std::vector<float> st_scan_each, st_gap_each;  // per scan launch index (summed); gap = time to the next scan
+    std::vector<int64_t> st_scan_rows;             // corpus rows of each timed scan
 
     // per-search workspace
     DevBuf<float> thr, q_scale, q_eps, q32, out_d;
@@ -205,7 +273,13 @@ struct fip_index {
     int certify = 1;          // 0: skip the exactness certificate of the tensor-core variant
     int live_thr = 1;         // 0: thresholds only move between scan launches (geometric phases)
     DevBuf<uint32_t> hist, hbase;   // live thresholds: [nq, 256] score histogram, [nq] bucket origin
-    DevBuf<uint32_t> cnt, overflow;
+    DevBuf<uint32_t> cnt, overflow;   // overflow = the flag words (select.cuh flag_slot)
+    DevBuf<uint32_t> sticky;          // [1] summary flags of asynchronous searches nobody checked yet
+    struct PendingSearch {            // the search enqueued last and not finished yet
+        const float* q32 = nullptr; int nq = 0, k = 0; float* out_d = nullptr; int64_t* out_i = nullptr;
+        cudaStream_t stream = nullptr; bool safe = false; bool active = false;
+        int variant = 0, phases = 0, cap = 0, split = 0, launches = 0;
+    } pend;
     DevBuf<uint64_t> cand;
     DevBuf<uint8_t> qprep;  // prepared query terms in the MMA operand type
     DevBuf<int64_t> out_i;
@@ -216,6 +290,7 @@ struct fip_index {
     PinnedBuf<int64_t> h_i;
     PinnedBuf<uint32_t> h_flags;
     DevBuf<float> add_stage;
+    PinnedBuf<uint8_t> h_add[2];   // fip_add_host: double-buffered pinned staging
 
     CUtensorMap tmap_x{};
     bool tmap_x_valid = false;
@@ -322,6 +397,7 @@ struct SearchCtx {
     cudaStream_t stream;
     int launches = 0;
     const CUtensorMap* tmap_scan = nullptr;   // corpus map of the tensor-core scan (storage or fp16 filter copy)
+    bool level0 = false;   // the caller's own search (not a redo of a subset): folds unchecked flags
 };
 
 template <typename T, int QB, int R>
@@ -365,11 +441,11 @@ int launch_stream_phase(SearchCtx& c, const ScanArgs& a, const float* q32) {
     return FIP_OK;
 }
 
-template <int kFmt, int kSplit, int kCtas>
+template <int kFmt, int kSplit, int kCtas, int kStage = 0>
 int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles) {
     fip_index* idx = c.idx;
-    auto kern = tc::tc_scan_kernel<kFmt, kSplit, kCtas>;
-    constexpr int smem = tc::Cfg<kFmt, kSplit, kCtas>::SMEM_BYTES;
+    auto kern = tc::tc_scan_kernel<kFmt, kSplit, kCtas, kStage>;
+    constexpr int smem = tc::Cfg<kFmt, kSplit, kCtas, kStage>::SMEM_BYTES;
     FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int64_t n_ctiles = ((int64_t)(a.row_end - a.row_begin) + tc::BN - 1) / tc::BN;
     const int64_t group_tiles = n_ctiles * (n_qtiles / kCtas);
@@ -384,13 +460,14 @@ int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q,
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        if (idx->max_clusters < 0) {
+        int& cached = idx->max_clusters[kStage > 0 ? 1 : 0];
+        if (cached < 0) {
             cfg.gridDim = dim3(idx->num_sms / 2 * 2);
             int n = 0;
             FIP_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-            idx->max_clusters = std::max(1, n);
+            cached = std::max(1, n);
         }
-        groups = std::min(groups, idx->max_clusters);
+        groups = std::min(groups, cached);
     }
     groups = (int)std::min<int64_t>(groups, group_tiles);
     cfg.gridDim = dim3((unsigned)(groups * kCtas));
@@ -399,8 +476,23 @@ int launch_tc_kernel(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q,
     return FIP_OK;
 }
 
+constexpr int kStageSlots = 8;   // survivor slots per epilogue thread and tile (deferred epilogue)
+
 int launch_tc_phase(SearchCtx& c, const ScanArgs& a, const CUtensorMap& tmap_q, int n_qtiles, int split,
-                    bool pair) {
+                    bool pair, bool deferred) {
+    if (deferred && split == 1 && !a.dense) {
+        switch (a.dtype) {
+            case kF32:
+                return pair ? launch_tc_kernel<2, 1, 2, kStageSlots>(c, a, tmap_q, n_qtiles)
+                            : launch_tc_kernel<2, 1, 1, kStageSlots>(c, a, tmap_q, n_qtiles);
+            case kBF16:
+                return pair ? launch_tc_kernel<1, 1, 2, kStageSlots>(c, a, tmap_q, n_qtiles)
+                            : launch_tc_kernel<1, 1, 1, kStageSlots>(c, a, tmap_q, n_qtiles);
+            default:
+                return pair ? launch_tc_kernel<0, 1, 2, kStageSlots>(c, a, tmap_q, n_qtiles)
+                            : launch_tc_kernel<0, 1, 1, kStageSlots>(c, a, tmap_q, n_qtiles);
+        }
+    }
     switch (a.dtype) {
         case kF32:
             return pair ? launch_tc_kernel<2, 1, 2>(c, a, tmap_q, n_qtiles)
@@ -441,13 +533,17 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
     s.out_scale = out_scale; s.overflow = idx->overflow.p; s.dense_count = (int)dense_count;
     if (keep_max > 0) {
         s.win_eps = idx->q_eps.p; s.win_scale = idx->q_scale.p; s.keep_max = keep_max;
-        s.uncert = idx->overflow.p + (nq + 1);
+        s.uncert = idx->overflow.p + 1;
     }
     if (live && !final_pass) { s.hist = idx->hist.p; s.hbase = idx->hbase.p; }
     size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
-    FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    select_topk_kernel<<<nq, kSelectThreads, smem, c.stream>>>(s);
+    if (select_wants_big(cap)) {
+        FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        select_topk_kernel_big<<<nq, kSelectThreadsBig, smem, c.stream>>>(s);
+    } else {
+        FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        select_topk_kernel<<<nq, kSelectThreads, smem, c.stream>>>(s);
+    }
     FIP_CUDA(cudaGetLastError());
     c.launches++;
     return FIP_OK;
@@ -491,12 +587,21 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     const int dim = idx->cfg.dim;
     const int dtype = idx->cfg.dtype;
     *info = SearchInfo{};
-    FIP_CUDA(idx->overflow.ensure(2 * ((size_t)nq + 1)));
+    if (flag_words(nq) > idx->overflow.n) {
+        // growing the flag buffer loses its contents: fold unchecked summary words first
+        if (idx->overflow.p && c.level0) {
+            fold_sticky_kernel<<<1, 32, 0, c.stream>>>(idx->overflow.p, idx->sticky.p);
+            FIP_CUDA(cudaStreamSynchronize(c.stream));
+        }
+        FIP_CUDA(idx->overflow.ensure(std::max<size_t>(flag_words(nq), flag_words(4096))));
+        FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, 2 * sizeof(uint32_t), c.stream));
+    }
     if (n == 0) {
         int64_t tot = (int64_t)nq * k;
         fill_padding_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c.stream>>>(out_d, out_i, tot);
         FIP_CUDA(cudaGetLastError());
-        FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, 2 * ((size_t)nq + 1) * sizeof(uint32_t), c.stream));
+        if (c.level0) fold_sticky_kernel<<<1, 32, 0, c.stream>>>(idx->overflow.p, idx->sticky.p);
+        FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, flag_words(nq) * sizeof(uint32_t), c.stream));
         c.launches++;
         return FIP_OK;
     }
@@ -556,11 +661,16 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     const int cap = cap_for_k(k_out, k_plan, certify, live, mode.safe, nq, n);
     const int keep_max = keep_max_for(cap, k_out, k_plan, certify);
     const int k_sel = certify ? k_out : k_plan;   // what the intermediate selects look for
+    // Deferred epilogue (tc_scan.cuh): pays off when most tiles hold survivors, i.e. for large k
+    // (survivors per query ~ k log(N / cap)); "defer_epilogue" 1 / 2 forces it off / on.
+    const bool deferred = idx->defer_epilogue == 2 || (idx->defer_epilogue == 0 && k_sel >= 256);
+    idx->st_deferred = (variant == FIP_VARIANT_TENSOR && deferred && split == 1) ? 1 : 0;
     FIP_CUDA(idx->thr.ensure(nq));
     FIP_CUDA(idx->cnt.ensure(nq));
     FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
 
-    init_lists_kernel<<<(nq + 256) / 256, 256, 0, c.stream>>>(idx->thr.p, idx->cnt.p, idx->overflow.p, nq);
+    init_lists_kernel<<<(unsigned)((flag_words(nq) + 255) / 256), 256, 0, c.stream>>>(
+        idx->thr.p, idx->cnt.p, idx->overflow.p, c.level0 ? idx->sticky.p : nullptr, nq);
     FIP_CUDA(cudaGetLastError());
     c.launches++;
 
@@ -621,7 +731,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = idx->cand.p; a.cap = (uint32_t)cap;
 
     auto scan_launch = [&]() -> int {
-        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, n_qtiles, split, pair);
+        if (variant == FIP_VARIANT_TENSOR) return launch_tc_phase(c, a, tmap_q, n_qtiles, split, pair, deferred);
         switch (dtype) {
             case kF32: return launch_stream_phase<float>(c, a, q32);
             case kF16: return launch_stream_phase<__half>(c, a, q32);
@@ -630,16 +740,19 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     };
     auto scan = [&](int64_t r0, int64_t r1, bool dense) -> int {
         a.row_begin = (uint32_t)r0; a.row_end = (uint32_t)r1; a.dense = dense ? 1 : 0;
-        const bool timed = idx->profile && idx->ev_used + 2 <= (int)idx->ev.size();
-        if (timed) FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_used], c.stream));
+        const bool timed = idx->profile && c.level0 && !idx->ev_sets.empty();
+        const size_t nev = idx->ev.size();
+        if (timed) FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_head % nev], c.stream));
         const int before = c.launches;
         int r = scan_launch();
         if (r) return r;
         if (timed) {
-            FIP_CUDA(cudaEventRecord(idx->ev[idx->ev_used + 1], c.stream));
-            idx->ev_used += 2;
-            idx->st_scan_launches += c.launches - before;
-            idx->st_scan_rows_pending.push_back(r1 - r0);
+            FIP_CUDA(cudaEventRecord(idx->ev[(idx->ev_head + 1) % nev], c.stream));
+            idx->ev_head += 2;
+            auto& set = idx->ev_sets.back();
+            set.count += 2;
+            set.launches += c.launches - before;
+            set.rows.push_back(r1 - r0);
         }
         return FIP_OK;
     };
@@ -680,7 +793,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (rescore) {
         // lists now hold the k' best by approximate score: recompute them exactly, then select k.
         const int k_res = certify ? keep_max : k_plan;   // list slots that may hold a candidate
-        const int64_t warps = (int64_t)nq * k_res;
+        const int64_t warps = (int64_t)nq * ((k_res + 3) / 4);   // a warp rescoring 4 candidates at a time
         const unsigned grid = (unsigned)std::min<int64_t>((warps + 7) / 8, (int64_t)idx->num_sms * 8);
         if (dtype == kBF16)
             rescore_kernel<__nv_bfloat16><<<grid, 256, 0, c.stream>>>(
@@ -702,23 +815,31 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     return FIP_OK;
 }
 
-// Reads the flags of the search just enqueued (synchronises) and appends the flagged queries,
-// translated through `ids` (null = identity), to `over` / `uncert`.
-int collect_flags(fip_index* idx, cudaStream_t stream, int nq, const int* ids, std::vector<int>* over,
-                  std::vector<int>* uncert) {
-    const size_t nflags = 2 * ((size_t)nq + 1);
-    FIP_CUDA(idx->h_flags.ensure(nflags));
+// Flags of the search just enqueued: copy_flags_async enqueues the D2H copy, parse_flags (after the
+// stream has been synchronised) appends the flagged queries, translated through `ids` (null =
+// identity), to `over` / `uncert`.  collect_flags = both with the synchronisation in between.
+int copy_flags_async(fip_index* idx, cudaStream_t stream, int nq) {
+    const size_t nflags = flag_words(nq);
+    FIP_CUDA(idx->h_flags.ensure(std::max<size_t>(nflags, flag_words(4096))));
     FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p, idx->overflow.p, sizeof(uint32_t) * nflags,
                              cudaMemcpyDeviceToHost, stream));
-    FIP_CUDA(cudaStreamSynchronize(stream));
+    return FIP_OK;
+}
+void parse_flags(const fip_index* idx, int nq, const int* ids, std::vector<int>* over, std::vector<int>* uncert) {
     const uint32_t* f = idx->h_flags.p;
-    const uint32_t* u = f + nq + 1;
-    if (!f[0] && !u[0]) return FIP_OK;
+    if (!f[0] && !f[1]) return;
     for (int q = 0; q < nq; ++q) {
         const int id = ids ? ids[q] : q;
-        if (f[1 + q]) over->push_back(id);
-        else if (u[1 + q]) uncert->push_back(id);
+        if (f[flag_slot(q)]) over->push_back(id);
+        else if (f[flag_slot(q) + 1]) uncert->push_back(id);
     }
+}
+int collect_flags(fip_index* idx, cudaStream_t stream, int nq, const int* ids, std::vector<int>* over,
+                  std::vector<int>* uncert) {
+    int rc = copy_flags_async(idx, stream, nq);
+    if (rc) return rc;
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    parse_flags(idx, nq, ids, over, uncert);
     return FIP_OK;
 }
 
@@ -753,19 +874,25 @@ int redo_subset(SearchCtx& c, const float* q32, const std::vector<int>& sel, int
     return collect_flags(idx, c.stream, ns, sel.data(), over, uncert);  // also keeps `sel` alive
 }
 
-// Search + checks.  Level 0 runs the configured variant.  Queries whose candidate list overflowed
-// are redone in safe mode, queries whose result could not be CERTIFIED exact (tensor-core filter,
-// see select.cuh) are redone with a tighter filter; whatever is still flagged after that goes to
-// the exact streaming kernel in safe mode, which cannot fail.  Synchronises the stream.
-int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
+// A search is ENQUEUED (search_enqueue: level 0, the configured variant, no synchronisation) and
+// later FINISHED (search_finish_synced, once the stream has been synchronised and the flags are on
+// the host): queries whose candidate list overflowed are redone in safe mode, queries whose result
+// could not be CERTIFIED exact (tensor-core filter, see select.cuh) are redone with a tighter
+// filter; whatever is still flagged after that goes to the exact streaming kernel in safe mode,
+// which cannot fail.  Between the two the caller may enqueue whatever consumes the result (the K4
+// exchange, the D2H copies): the flags come back with the results, one synchronisation per search.
+int search_enqueue(fip_index* idx, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
                    cudaStream_t stream) {
+    if (idx->pend.active && idx->pend.stream != stream) FIP_CUDA(cudaStreamSynchronize(idx->pend.stream));
     SearchCtx c{idx, stream};
-    idx->ev_used = 0;
-    idx->st_scan_launches = 0;
-    idx->st_scan_rows_pending.clear();
+    c.level0 = true;
     if (idx->profile && idx->ev.empty()) {
-        idx->ev.resize(128);
+        idx->ev.resize(1024);
         for (auto& e : idx->ev) FIP_CUDA(cudaEventCreate(&e));
+    }
+    if (idx->profile) {
+        if (idx->ev_sets.size() > 4096) idx->ev_sets.erase(idx->ev_sets.begin(), idx->ev_sets.begin() + 2048);
+        idx->ev_sets.push_back(fip_index::EvSet{idx->ev_head, 0, {}, 0});
     }
     idx->st_list_entries = 0; idx->st_list_max = 0;
     Mode m0;
@@ -773,19 +900,71 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
     SearchInfo info;
     int rc = run_search(c, q32, nq, k, out_d, out_i, m0, &info);
     if (rc) return rc;
+    idx->pend = fip_index::PendingSearch{q32, nq, k, out_d, out_i, stream, m0.safe, true, info.variant,
+                                         info.phases, info.cap, info.split, c.launches};
+    idx->st_launches = c.launches; idx->st_variant = info.variant; idx->st_phases = info.phases;
+    idx->st_cap = info.cap; idx->st_split = info.split;
+    idx->st_overflow = 0; idx->st_uncert = 0; idx->st_stream_redo = 0;
+    idx->st_total_launches += c.launches; idx->st_total_searches++;
+    return FIP_OK;
+}
+
+void collect_event_times(fip_index* idx) {
+    idx->st_scan_ms = 0.0;
+    idx->st_scan_launches = 0;
+    idx->st_scan_searches = 0;
+    idx->st_scan_each.clear();
+    idx->st_gap_each.clear();
+    idx->st_scan_rows.clear();
+    const size_t nev = idx->ev.size();
+    for (const auto& set : idx->ev_sets) {
+        if (!set.count || idx->ev_head - set.start > nev) continue;   // nothing timed / ring wrapped over it
+        bool ok = true;
+        std::vector<float> each, gaps;
+        for (int i = 0; i + 1 < set.count && ok; i += 2) {
+            float ms = 0.f;
+            ok = cudaEventElapsedTime(&ms, idx->ev[(set.start + i) % nev], idx->ev[(set.start + i + 1) % nev]) == cudaSuccess;
+            each.push_back(ms);
+            if (ok && i + 2 < set.count) {
+                ok = cudaEventElapsedTime(&ms, idx->ev[(set.start + i + 1) % nev], idx->ev[(set.start + i + 2) % nev]) == cudaSuccess;
+                gaps.push_back(ms);
+            }
+        }
+        if (!ok) { cudaGetLastError(); continue; }
+        if (idx->st_scan_each.size() < each.size()) idx->st_scan_each.resize(each.size(), 0.f);
+        if (idx->st_gap_each.size() < gaps.size()) idx->st_gap_each.resize(gaps.size(), 0.f);
+        for (size_t i = 0; i < each.size(); ++i) { idx->st_scan_each[i] += each[i]; idx->st_scan_ms += each[i]; }
+        for (size_t i = 0; i < gaps.size(); ++i) idx->st_gap_each[i] += gaps[i];
+        idx->st_scan_rows = set.rows;
+        idx->st_scan_launches += set.launches;
+        idx->st_scan_searches++;
+    }
+    idx->ev_sets.clear();
+}
+
+// The pending search's stream is synchronised and idx->h_flags holds its flags.  *redone = number of
+// queries that were searched again (their rows of out_d / out_i were rewritten on the device).
+int search_finish_synced(fip_index* idx, int* redone) {
+    *redone = 0;
+    if (!idx->pend.active) return FIP_OK;
+    const fip_index::PendingSearch p = idx->pend;
+    idx->pend.active = false;
+    collect_event_times(idx);
     std::vector<int> over, uncert, over2, uncert2;
-    rc = collect_flags(idx, stream, nq, nullptr, &over, &uncert);
-    if (rc) return rc;
-    int phases = info.phases;
+    parse_flags(idx, p.nq, nullptr, &over, &uncert);
+    if (over.empty() && uncert.empty()) return FIP_OK;
+    SearchCtx c{idx, p.stream};
+    int phases = p.phases;
     const size_t n_over = over.size(), n_uncert = uncert.size();
+    int rc;
     if (!over.empty()) {
-        Mode m; m.safe = true; m.rigor = m0.rigor;
-        rc = redo_subset(c, q32, over, k, out_d, out_i, m, &over2, &uncert2, &phases);
+        Mode m; m.safe = true; m.rigor = 0;
+        rc = redo_subset(c, p.q32, over, p.k, p.out_d, p.out_i, m, &over2, &uncert2, &phases);
         if (rc) return rc;
     }
     if (!uncert.empty()) {
-        Mode m; m.safe = m0.safe; m.rigor = 1;
-        rc = redo_subset(c, q32, uncert, k, out_d, out_i, m, &over2, &uncert2, &phases);
+        Mode m; m.safe = p.safe; m.rigor = 1;
+        rc = redo_subset(c, p.q32, uncert, p.k, p.out_d, p.out_i, m, &over2, &uncert2, &phases);
         if (rc) return rc;
     }
     over2.insert(over2.end(), uncert2.begin(), uncert2.end());
@@ -793,30 +972,32 @@ int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d
         std::sort(over2.begin(), over2.end());
         Mode m; m.safe = true; m.rigor = 2;
         std::vector<int> o3, u3;
-        rc = redo_subset(c, q32, over2, k, out_d, out_i, m, &o3, &u3, &phases);
+        rc = redo_subset(c, p.q32, over2, p.k, p.out_d, p.out_i, m, &o3, &u3, &phases);
         if (rc) return rc;
         if (!o3.empty() || !u3.empty())
             return fail(FIP_ERR_STATE, "internal error: the exact fallback path raised a flag");
     }
-    idx->st_scan_ms = 0.0;
-    idx->st_scan_each.clear();
-    idx->st_gap_each.clear();
-    idx->st_scan_rows = idx->st_scan_rows_pending;
-    for (int i = 0; i + 1 < idx->ev_used; i += 2) {
-        float ms = 0.f;
-        FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i], idx->ev[i + 1]));
-        idx->st_scan_ms += ms;
-        idx->st_scan_each.push_back(ms);
-        if (i + 2 < idx->ev_used) {
-            FIP_CUDA(cudaEventElapsedTime(&ms, idx->ev[i + 1], idx->ev[i + 2]));
-            idx->st_gap_each.push_back(ms);
-        }
-    }
-    idx->st_launches = c.launches; idx->st_variant = info.variant; idx->st_phases = phases;
+    // everything flagged has been dealt with: the summary words must not reach `sticky`
+    FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, 2 * sizeof(uint32_t), p.stream));
+    FIP_CUDA(cudaStreamSynchronize(p.stream));
+    *redone = (int)(n_over + n_uncert);
+    idx->st_launches = p.launches + c.launches; idx->st_phases = phases;
     idx->st_overflow = (int64_t)n_over; idx->st_uncert = (int64_t)n_uncert;
-    idx->st_stream_redo = (int64_t)over2.size(); idx->st_cap = info.cap; idx->st_split = info.split;
-    idx->st_total_launches += c.launches; idx->st_total_searches++;
+    idx->st_stream_redo = (int64_t)over2.size();
+    idx->st_total_launches += c.launches;
     return FIP_OK;
+}
+
+// Blocking search: enqueue, fetch the flags, finish.
+int search_checked(fip_index* idx, const float* q32, int nq, int k, float* out_d, int64_t* out_i,
+                   cudaStream_t stream) {
+    int rc = search_enqueue(idx, q32, nq, k, out_d, out_i, stream);
+    if (rc) return rc;
+    rc = copy_flags_async(idx, stream, nq);
+    if (rc) return rc;
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    int redone = 0;
+    return search_finish_synced(idx, &redone);
 }
 
 int check_search_args(const fip_index* idx, const void* q, int64_t nq, int32_t k, const void* d,
@@ -862,6 +1043,8 @@ int fip_create(const fip_config* cfg, fip_index** out) {
     if (e != cudaSuccess) { delete idx; FIP_CUDA(e); }
     e = idx->max_norm2.ensure(1);
     if (e == cudaSuccess) e = cudaMemset(idx->max_norm2.p, 0, sizeof(float));
+    if (e == cudaSuccess) e = idx->sticky.ensure(1);
+    if (e == cudaSuccess) e = cudaMemset(idx->sticky.p, 0, sizeof(uint32_t));
     if (e != cudaSuccess) { fip_destroy(idx); FIP_CUDA(e); }
     if (cfg->capacity_rows > 0) {
         int rc = reserve_rows(idx, cfg->capacity_rows);
@@ -877,11 +1060,11 @@ void fip_destroy(fip_index* idx) {
     if (idx->stream) cudaStreamSynchronize(idx->stream);
     if (idx->corpus) cudaFree(idx->corpus);
     if (idx->corpus16) cudaFree(idx->corpus16);
-    idx->thr.release(); idx->q_scale.release(); idx->q_eps.release(); idx->max_norm2.release(); idx->q32.release(); idx->out_d.release();
+    idx->sticky.release(); idx->thr.release(); idx->q_scale.release(); idx->q_eps.release(); idx->max_norm2.release(); idx->q32.release(); idx->out_d.release();
     idx->cnt.release(); idx->hist.release(); idx->hbase.release(); idx->overflow.release(); idx->cand.release(); idx->qprep.release();
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
-    idx->h_flags.release(); idx->add_stage.release();
+    idx->h_flags.release(); idx->add_stage.release(); idx->h_add[0].release(); idx->h_add[1].release();
     for (auto& e : idx->ev) cudaEventDestroy(e);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
@@ -919,30 +1102,76 @@ static int convert_append(fip_index* idx, const float* src_dev, int64_t n) {
     return FIP_OK;
 }
 
-int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n) {
+// Host rows in `dtype` -> the index.  Rows travel in their OWN width (a 16-bit corpus file is
+// uploaded as 16 bits, not widened to fp32 on the host) through two pinned staging buffers, so the
+// CPU copy of chunk c+1 overlaps the H2D transfer and conversion of chunk c.
+static int add_host_rows(fip_index* idx, const void* rows, int64_t n, int32_t dtype) {
+    const int sdt = idx->cfg.dtype;
+    if (dtype != FIP_F32 && dtype != FIP_F16 && dtype != FIP_BF16) return fail(FIP_ERR_INVALID, "unknown dtype");
+    if (dtype != sdt && dtype != FIP_F32 && sdt != FIP_F32)
+        return fail(FIP_ERR_INVALID, "fip_add_host: fp16 <-> bf16 conversion is not supported; pass fp32 "
+                                     "rows or rows in the index's storage dtype");
+    if (idx->n_rows + n >= (int64_t)0xFFFFFF00ll) return fail(FIP_ERR_INVALID, "shard limited to 2^32-256 rows");
+    int rc = reserve_rows(idx, idx->n_rows + n);
+    if (rc) return rc;
+    const int dim = idx->cfg.dim;
+    const size_t src_row = (size_t)dim * dtype_size(dtype);
+    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(32 << 20) / (int64_t)src_row);
+    const size_t chunk_bytes = (size_t)std::min(chunk_rows, n) * src_row;
+    FIP_CUDA(idx->h_add[0].ensure(chunk_bytes));
+    FIP_CUDA(idx->h_add[1].ensure(chunk_bytes));
+    const bool direct = dtype == sdt;
+    if (!direct) FIP_CUDA(idx->add_stage.ensure(2 * ((chunk_bytes + 3) / 4)));
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    for (auto& e : ev) FIP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    auto cleanup = [&]() { for (auto& e : ev) if (e) cudaEventDestroy(e); };
+    int64_t done = 0;
+    for (int64_t r = 0, c = 0; r < n; r += chunk_rows, ++c) {
+        const int64_t m = std::min(chunk_rows, n - r);
+        const int b = (int)(c & 1);
+        cudaError_t e = c >= 2 ? cudaEventSynchronize(ev[b]) : cudaSuccess;   // staging buffer b is free again
+        if (e == cudaSuccess) {
+            memcpy(idx->h_add[b].p, (const char*)rows + (size_t)r * src_row, (size_t)m * src_row);
+            char* dst = (char*)idx->corpus + (size_t)(idx->n_rows + done) * idx->row_bytes();
+            void* stage = direct ? (void*)dst : (void*)((char*)idx->add_stage.p + (size_t)b * ((chunk_bytes + 3) / 4) * 4);
+            e = cudaMemcpyAsync(stage, idx->h_add[b].p, (size_t)m * src_row, cudaMemcpyHostToDevice, idx->stream);
+            if (e == cudaSuccess && !direct) {
+                const int64_t tot = m * dim;
+                const unsigned grid = (unsigned)std::min<int64_t>((tot + 255) / 256, 148 * 32);
+                if (dtype == FIP_F32 && sdt == kF16) convert_rows_kernel<__half><<<grid, 256, 0, idx->stream>>>((const float*)stage, (__half*)dst, tot);
+                else if (dtype == FIP_F32) convert_rows_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((const float*)stage, (__nv_bfloat16*)dst, tot);
+                else if (dtype == FIP_F16) widen_rows_kernel<__half><<<grid, 256, 0, idx->stream>>>((const __half*)stage, (float*)dst, tot);
+                else widen_rows_kernel<__nv_bfloat16><<<grid, 256, 0, idx->stream>>>((const __nv_bfloat16*)stage, (float*)dst, tot);
+                e = cudaGetLastError();
+            }
+            if (e == cudaSuccess) e = cudaEventRecord(ev[b], idx->stream);
+        }
+        if (e != cudaSuccess) { cudaStreamSynchronize(idx->stream); cleanup(); FIP_CUDA(e); }
+        rc = update_row_norms(idx, idx->n_rows + done, m);
+        if (rc) { cudaStreamSynchronize(idx->stream); cleanup(); return rc; }
+        done += m;
+    }
+    cudaError_t e = cudaStreamSynchronize(idx->stream);
+    cleanup();
+    FIP_CUDA(e);
+    // rows become visible only once every chunk has landed; whatever reads the corpus through a
+    // cached view (tensor map, fp16 filter copy) is invalidated together with the row count
+    idx->n_rows += n;
+    idx->tmap_x_valid = false; idx->corpus_gen++;
+    return FIP_OK;
+}
+
+int fip_add_host(fip_index* idx, const void* rows, int64_t n, int32_t dtype) {
     if (!idx || (n > 0 && !rows) || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
     if (n == 0) return FIP_OK;
     std::lock_guard<std::mutex> lock(idx->mu);
     int rc = use_device(idx);
     if (rc) return rc;
-    if (idx->n_rows + n >= (int64_t)0xFFFFFF00ll) return fail(FIP_ERR_INVALID, "shard limited to 2^32-256 rows");
-    rc = reserve_rows(idx, idx->n_rows + n);
-    if (rc) return rc;
-    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(64 << 20) / ((int64_t)idx->cfg.dim * 4));
-    FIP_CUDA(idx->add_stage.ensure((size_t)std::min(chunk_rows, n) * idx->cfg.dim));
-    for (int64_t r = 0; r < n; r += chunk_rows) {
-        int64_t m = std::min(chunk_rows, n - r);
-        FIP_CUDA(cudaMemcpyAsync(idx->add_stage.p, rows + r * idx->cfg.dim, (size_t)m * idx->cfg.dim * 4,
-                                 cudaMemcpyHostToDevice, idx->stream));
-        rc = convert_append(idx, idx->add_stage.p, m);
-        if (rc) return rc;
-        rc = update_row_norms(idx, idx->n_rows, m);
-        if (rc) return rc;
-        FIP_CUDA(cudaStreamSynchronize(idx->stream));
-        idx->n_rows += m;
-    }
-    idx->tmap_x_valid = false; idx->corpus_gen++;
-    return FIP_OK;
+    return add_host_rows(idx, rows, n, dtype);
+}
+
+int fip_add_host_f32(fip_index* idx, const float* rows, int64_t n) {
+    return fip_add_host(idx, rows, n, FIP_F32);
 }
 
 int fip_add_device(fip_index* idx, const void* rows_dev, int64_t n, int32_t dtype) {
@@ -1039,7 +1268,7 @@ int32_t fip_dtype_of(const fip_index* idx) { return idx ? idx->cfg.dtype : -1; }
 
 // One host-buffer search over the concatenation of `batch` (all with the same k): pinned staging,
 // H2D, search, D2H, scatter back to every caller's buffers.
-static int run_host_batch(fip_index* idx, const std::vector<fip_index::Pending*>& batch) {
+static int run_host_batch(fip_index* idx, const std::vector<HostRequest*>& batch) {
     std::lock_guard<std::mutex> lock(idx->mu);
     int rc = use_device(idx);
     if (rc) return rc;
@@ -1060,21 +1289,28 @@ static int run_host_batch(fip_index* idx, const std::vector<fip_index::Pending*>
         off += (size_t)b->nq;
     }
     FIP_CUDA(cudaMemcpyAsync(idx->q32.p, idx->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, idx->stream));
-    rc = search_checked(idx, idx->q32.p, (int)nq, k, idx->out_d.p, idx->out_i.p, idx->stream);
+    // results and flags come back together: one synchronisation per search; only a flagged search
+    // (rare: overflow / uncertified queries) is finished on the host and copied again
+    rc = search_enqueue(idx, idx->q32.p, (int)nq, k, idx->out_d.p, idx->out_i.p, idx->stream);
     if (rc) return rc;
-    FIP_CUDA(cudaMemcpyAsync(idx->h_d.p, idx->out_d.p, on * sizeof(float), cudaMemcpyDeviceToHost, idx->stream));
-    FIP_CUDA(cudaMemcpyAsync(idx->h_i.p, idx->out_i.p, on * sizeof(int64_t), cudaMemcpyDeviceToHost, idx->stream));
-    FIP_CUDA(cudaStreamSynchronize(idx->stream));
+    for (int pass = 0; pass < 2; ++pass) {
+        FIP_CUDA(cudaMemcpyAsync(idx->h_d.p, idx->out_d.p, on * sizeof(float), cudaMemcpyDeviceToHost, idx->stream));
+        FIP_CUDA(cudaMemcpyAsync(idx->h_i.p, idx->out_i.p, on * sizeof(int64_t), cudaMemcpyDeviceToHost, idx->stream));
+        if (pass == 0) { rc = copy_flags_async(idx, idx->stream, (int)nq); if (rc) return rc; }
+        FIP_CUDA(cudaStreamSynchronize(idx->stream));
+        if (pass == 1) break;
+        int redone = 0;
+        rc = search_finish_synced(idx, &redone);
+        if (rc) return rc;
+        if (!redone) break;
+    }
     off = 0;
     for (auto* b : batch) {
         memcpy(b->d, idx->h_d.p + off * k, (size_t)b->nq * k * sizeof(float));
         memcpy(b->i, idx->h_i.p + off * k, (size_t)b->nq * k * sizeof(int64_t));
         off += (size_t)b->nq;
     }
-    idx->st_batches++;
-    idx->st_calls += (int64_t)batch.size();
-    idx->st_last_batch_calls = (int64_t)batch.size();
-    if (batch.size() > 1) idx->st_coalesced_calls += (int64_t)batch.size();
+    idx->co.count(batch.size());
     return FIP_OK;
 }
 
@@ -1083,45 +1319,8 @@ int fip_search(fip_index* idx, const float* queries, int64_t nq, int32_t k, floa
     int rc = check_search_args(idx, queries, nq, k, distances, ids);
     if (rc) return rc;
     if (nq == 0) return FIP_OK;
-    fip_index::Pending me{queries, nq, k, distances, ids};
-    if (!idx->coalesce) {
-        std::vector<fip_index::Pending*> one{&me};
-        return run_host_batch(idx, one);
-    }
-    std::unique_lock<std::mutex> lk(idx->qmu);
-    idx->pending.push_back(&me);
-    while (!me.done) {
-        if (idx->leader_active) {
-            idx->qcv.wait(lk);
-            continue;
-        }
-        // become the leader for one batch: the oldest request sets k; every queued request with
-        // that k rides along, in arrival order, while the batch stays within coalesce_max queries
-        idx->leader_active = true;
-        std::vector<fip_index::Pending*> batch;
-        const int bk = idx->pending.front()->k;
-        int64_t total = 0;
-        for (auto it = idx->pending.begin(); it != idx->pending.end();) {
-            fip_index::Pending* p = *it;
-            if (p->k == bk && (batch.empty() || total + p->nq <= idx->coalesce_max)) {
-                batch.push_back(p);
-                total += p->nq;
-                it = idx->pending.erase(it);
-            } else {
-                ++it;
-            }
-        }
-        lk.unlock();
-        const int brc = run_host_batch(idx, batch);
-        const std::string berr = brc ? g_last_error : std::string();
-        lk.lock();
-        for (auto* p : batch) { p->rc = brc; p->err = berr; p->done = true; }
-        idx->leader_active = false;
-        idx->qcv.notify_all();
-    }
-    lk.unlock();
-    if (me.rc) g_last_error = me.err;
-    return me.rc;
+    HostRequest me{queries, nq, k, distances, ids};
+    return idx->co.submit(me, [idx](const std::vector<HostRequest*>& batch) { return run_host_batch(idx, batch); });
 }
 
 int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
@@ -1135,6 +1334,44 @@ int fip_search_device(fip_index* idx, const float* queries_dev, int64_t nq, int3
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : idx->stream;
     return search_checked(idx, queries_dev, (int)nq, k, distances_dev, ids_dev, s);
 }
+
+int fip_search_device_async(fip_index* idx, const float* queries_dev, int64_t nq, int32_t k,
+                            float* distances_dev, int64_t* ids_dev, void* cuda_stream) {
+    int rc = check_search_args(idx, queries_dev, nq, k, distances_dev, ids_dev);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    rc = use_device(idx);
+    if (rc) return rc;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : idx->stream;
+    return search_enqueue(idx, queries_dev, (int)nq, k, distances_dev, ids_dev, s);
+}
+
+int fip_search_status(fip_index* idx, int32_t* flagged) {
+    if (!idx || !flagged) return fail(FIP_ERR_INVALID, "null argument");
+    *flagged = 0;
+    std::lock_guard<std::mutex> lock(idx->mu);
+    int rc = use_device(idx);
+    if (rc) return rc;
+    cudaStream_t s = idx->pend.stream ? idx->pend.stream : idx->stream;
+    if (!idx->overflow.p) return FIP_OK;   // never searched
+    FIP_CUDA(idx->h_flags.ensure(flag_words(4096)));
+    FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p, idx->overflow.p, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    FIP_CUDA(cudaMemcpyAsync(idx->h_flags.p + 2, idx->sticky.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    FIP_CUDA(cudaStreamSynchronize(s));
+    const uint32_t* f = idx->h_flags.p;
+    *flagged = (f[0] ? 1 : 0) | (f[1] ? 2 : 0) | (int32_t)f[2];
+    if (*flagged) {
+        FIP_CUDA(cudaMemsetAsync(idx->overflow.p, 0, 2 * sizeof(uint32_t), s));
+        FIP_CUDA(cudaMemsetAsync(idx->sticky.p, 0, sizeof(uint32_t), s));
+        FIP_CUDA(cudaStreamSynchronize(s));
+    }
+    idx->pend.active = false;
+    collect_event_times(idx);
+    return FIP_OK;
+}
+
+const uint32_t* fip_search_flags_device(const fip_index* idx) { return idx ? idx->overflow.p : nullptr; }
 
 int fip_merge_strided_device(int32_t device, const float* in_d, const int64_t* in_i, int64_t stride_d,
                              int64_t stride_i, int32_t g, int64_t nq, int32_t k_in, int32_t k_out,
@@ -1165,7 +1402,9 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
 // ------------------------------------------------------------------ fused exchange + merge (K4)
 struct fip_exchange {
     int device = 0, world = 1, rank = 0, nq_max = 0, k_max = 0;
-    int64_t slot_bytes = 0, flags_off = 0, total_bytes = 0;
+    int64_t slot_bytes = 0, flags_off = 0, status_off = 0, total_bytes = 0;
+    int resident_ctas[12] = {};   // per log2(block threads): co-resident CTAs of the kernel (0 = not queried)
+    int share = 1;                // ranks of the group living on THIS device (tests): they split the residency
     uint8_t* local = nullptr;
     uint8_t* peer[kMaxRanks] = {};
     bool ipc_opened[kMaxRanks] = {};
@@ -1191,7 +1430,8 @@ int fip_exchange_create(int32_t device, int32_t world, int32_t rank, int64_t nq_
     x->device = device; x->world = world; x->rank = rank; x->nq_max = (int)nq_max; x->k_max = k_max;
     x->slot_bytes = round_up16(round_up16(nq_max * k_max * 4) + nq_max * k_max * 8);
     x->flags_off = 2 * (int64_t)world * x->slot_bytes;
-    x->total_bytes = x->flags_off + round_up16(2 * (int64_t)world * nq_max * 4);
+    x->status_off = x->flags_off + round_up16(2 * (int64_t)world * nq_max * 4);
+    x->total_bytes = x->status_off + round_up16(2 * (int64_t)world * 4);
     cudaError_t e = cudaMalloc((void**)&x->local, (size_t)x->total_bytes);
     if (e == cudaSuccess) e = cudaMemset(x->local, 0, (size_t)x->total_bytes);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -1246,6 +1486,7 @@ int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all) {
             cudaGetLastError();
         }
         x->peer[r] = o->local;
+        if (o->device == x->device) x->share++;
     }
     x->connected = true;
     return FIP_OK;
@@ -1253,6 +1494,12 @@ int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all) {
 
 int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
                        float* out_d, int64_t* out_i, void* cuda_stream) {
+    return fip_exchange_merge_status(x, d_loc, i_loc, nq, k, out_d, out_i, nullptr, nullptr, cuda_stream);
+}
+
+int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
+                              float* out_d, int64_t* out_i, const uint32_t* flags_loc_dev,
+                              uint32_t* out_status_dev, void* cuda_stream) {
     if (!x || (nq > 0 && (!d_loc || !i_loc || !out_d || !out_i))) return fail(FIP_ERR_INVALID, "null argument");
     if (nq < 0 || nq > x->nq_max || k < 1 || k > x->k_max)
         return fail(FIP_ERR_INVALID, "nq / k exceed what the exchange was created for");
@@ -1270,12 +1517,23 @@ int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc
     a.slot_bytes = x->slot_bytes; a.flags_off = x->flags_off; a.nq_max = x->nq_max;
     a.off_i = (int)round_up16(nq * k * 4);
     a.d_loc = d_loc; a.i_loc = i_loc; a.out_d = out_d; a.out_i = out_i;
+    a.status_off = x->status_off; a.flags_loc = flags_loc_dev; a.out_status = out_status_dev;
     const int n = next_pow2(x->world * k);
     const size_t smem = (size_t)n * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)std::max<size_t>(smem, 1024)));
     const int threads = std::min(1024, std::max(64, n / 2));
-    exchange_merge_kernel<<<(unsigned)nq, threads, smem, (cudaStream_t)cuda_stream>>>(a);
+    // grid bounded by what is resident at once (every CTA loops over its queries)
+    int lg = 0;
+    while ((1 << lg) < threads) lg++;
+    if (!x->resident_ctas[lg]) {
+        int per_sm = 0, sms = 0;
+        FIP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, exchange_merge_kernel, threads, smem));
+        FIP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, x->device));
+        x->resident_ctas[lg] = std::max(1, per_sm * sms);
+    }
+    const unsigned grid = (unsigned)std::min<int64_t>(nq, std::max(1, x->resident_ctas[lg] / x->share));
+    exchange_merge_kernel<<<grid, threads, smem, (cudaStream_t)cuda_stream>>>(a);
     FIP_CUDA(cudaGetLastError());
     return FIP_OK;
 }
@@ -1307,10 +1565,10 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "cta_pair must be 0 (auto), 1 or 2");
         idx->cta_pair = (int)value;
     } else if (k == "coalesce") {
-        idx->coalesce = value != 0;
+        idx->co.enabled = value != 0;
     } else if (k == "coalesce_max_batch") {
         if (value < 1) return fail(FIP_ERR_INVALID, "coalesce_max_batch must be >= 1");
-        idx->coalesce_max = value;
+        idx->co.max_batch = value;
     } else if (k == "live_thresholds") {
         idx->live_thr = value != 0;
     } else if (k == "certify") {
@@ -1326,6 +1584,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         }
     } else if (k == "profile_events") {
         idx->profile = value != 0;
+    } else if (k == "defer_epilogue") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "defer_epilogue must be 0 (auto), 1 (off) or 2 (on)");
+        idx->defer_epilogue = (int)value;
     } else if (k == "debug_counts") {
         idx->debug_counts = value != 0;
     } else if (k == "force_safe_mode") {
@@ -1347,10 +1608,12 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     if (k == "stream_redo_queries") return idx->st_stream_redo;
     if (k == "query_split_used") return idx->st_split;
     if (k == "filter_f16") return idx->st_filter16;
+    if (k == "deferred_epilogue") return idx->st_deferred;
     if (k == "candidate_capacity") return idx->st_cap;
     if (k == "cta_group") return idx->st_pair;
     if (k == "scan_time_ns") return (int64_t)(idx->st_scan_ms * 1e6);
     if (k == "scan_launches") return idx->st_scan_launches;
+    if (k == "scan_searches") return idx->st_scan_searches;
     if (k.rfind("scan_rows_", 0) == 0) {
         const size_t i = (size_t)atoi(k.c_str() + 10);
         return i < idx->st_scan_rows.size() ? idx->st_scan_rows[i] : -1;
@@ -1363,10 +1626,12 @@ int64_t fip_get_stat(const fip_index* idx, const char* key) {
     }
     if (k == "list_entries_after_filter") return idx->st_list_entries;
     if (k == "list_max_after_filter") return idx->st_list_max;
-    if (k == "host_batches") return idx->st_batches;
-    if (k == "host_calls") return idx->st_calls;
-    if (k == "coalesced_calls") return idx->st_coalesced_calls;
-    if (k == "last_batch_calls") return idx->st_last_batch_calls;
+    if (k == "host_batches") return idx->co.st_batches;
+    if (k == "host_calls") return idx->co.st_calls;
+    if (k == "coalesced_calls") return idx->co.st_coalesced_calls;
+    if (k == "last_batch_calls") return idx->co.st_last_batch_calls;
+    if (k == "host_queries") return idx->co.st_queries;
+    if (k == "distinct_queries") return idx->co.st_distinct;
     if (k == "total_launches") return idx->st_total_launches;
     if (k == "total_searches") return idx->st_total_searches;
     return -1;
@@ -1380,3 +1645,5 @@ int32_t fip_compiled_sm(void) { return 100; }
 
 // IVF-Flat (L2) operator: include/ivfflat_b200.h
 #include "ivf_api.cuh"
+// Multi-GPU group behind one search call: include/flatip_b200.h (fip_group_*)
+#include "group_api.cuh"

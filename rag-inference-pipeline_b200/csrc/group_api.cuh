@@ -1,0 +1,436 @@
+// fip_group: ONE corpus row-sharded over several GPUs of THIS process, behind one blocking search
+// call -- the process model SURVEY 8(e) names ("one Python process, g devices, one host thread +
+// stream per device inside fip_search") and what lets the reference's single in-process call site
+//     faiss_store = self.registry.get("faiss_store"); faiss_store.search(embeddings, k)
+//     (/root/reference/src/pipeline/services/retrieval/api.py:383-389)
+// use all 8 GPUs of a box.  (Included at the end of flatip_api.cu: it uses the file's internals.)
+//
+// Layout: shard r lives on devices[r] and owns the contiguous global rows [r * per, (r + 1) * per)
+// (per = ceil(planned_rows / g); the last shard also takes whatever is added beyond the plan), so
+// "shard, then position" == "id ascending" and the fixed tie-break survives the merge.
+//
+// A search (run_group_batch):
+//   every rank, on its own persistent host thread and stream, in parallel:
+//     H2D of the (shared, pinned) query batch -> local search ENQUEUED (search_enqueue, no host
+//     round trip) -> K4 fused exchange + merge over NVLink peer memory (fip_exchange, wired with
+//     connect_local), which also ORs the shards' status words -> rank 0: D2H of the global result;
+//     every rank: D2H of the merged status -> ONE stream synchronisation.
+//   Only if some shard flagged a query (overflow / uncertified: rare) do the ranks finish their
+//   local searches on the host (redo of the flagged queries) and exchange + merge once more.
+#pragma once
+
+#include <functional>
+#include <thread>
+
+struct fip_group {
+    int world = 0;
+    int dim = 0, dtype = 0;
+    int64_t planned_rows = 0, per = 0;
+    std::vector<int> devices;
+    std::vector<fip_index*> shard;
+    std::vector<fip_exchange*> xchg;
+    int xchg_nq = 0, xchg_k = 0;
+    bool shared_device = false;   // test configuration: several shards on one GPU (see fip_group_create)
+
+    struct Rank {
+        cudaStream_t stream = nullptr;
+        DevBuf<float> q32, loc_d, out_d;
+        DevBuf<int64_t> loc_i, out_i;
+        DevBuf<uint32_t> status;          // [1] merged status of the exchange (device)
+        PinnedBuf<uint32_t> h_status;     // [1]
+        int rc = 0;
+        std::string err;
+    };
+    std::vector<Rank> ranks;
+    PinnedBuf<float> h_q, h_d;
+    PinnedBuf<int64_t> h_i;
+
+    // persistent workers: one host thread per device
+    std::vector<std::thread> workers;
+    std::mutex wmu;
+    std::condition_variable cv_job, cv_done;
+    uint64_t job_gen = 0;
+    int outstanding = 0;
+    bool stop = false;
+    std::function<int(int)> job;
+
+    std::mutex mu;      // serialises group operations
+    Coalescer co;
+    int64_t st_flagged_searches = 0, st_exchange_launches = 0, st_searches = 0;
+};
+
+namespace {
+
+void group_worker(fip_group* g, int r) {
+    cudaSetDevice(g->devices[r]);
+    uint64_t seen = 0;
+    for (;;) {
+        std::function<int(int)> fn;
+        {
+            std::unique_lock<std::mutex> lk(g->wmu);
+            g->cv_job.wait(lk, [&] { return g->stop || g->job_gen != seen; });
+            if (g->stop) return;
+            seen = g->job_gen;
+            fn = g->job;
+        }
+        g_last_error.clear();
+        const int rc = fn(r);
+        g->ranks[r].rc = rc;
+        g->ranks[r].err = rc ? g_last_error : std::string();
+        {
+            std::lock_guard<std::mutex> lk(g->wmu);
+            if (--g->outstanding == 0) g->cv_done.notify_all();
+        }
+    }
+}
+
+// Runs fn(r) on every rank's worker thread at once; returns the first failure (its message becomes
+// the calling thread's fip_last_error).
+int group_run(fip_group* g, std::function<int(int)> fn) {
+    {
+        std::lock_guard<std::mutex> lk(g->wmu);
+        g->job = std::move(fn);
+        g->outstanding = g->world;
+        g->job_gen++;
+    }
+    g->cv_job.notify_all();
+    {
+        std::unique_lock<std::mutex> lk(g->wmu);
+        g->cv_done.wait(lk, [&] { return g->outstanding == 0; });
+    }
+    for (int r = 0; r < g->world; ++r)
+        if (g->ranks[r].rc) return fail(g->ranks[r].rc, "device " + std::to_string(g->devices[r]) + ": " + g->ranks[r].err);
+    return FIP_OK;
+}
+
+// Global rows [g0, g0 + n) -> (shard, local count, offset into the caller's rows) pieces.
+struct GroupPiece { int r; int64_t first, count; };
+std::vector<GroupPiece> group_route(const fip_group* g, int64_t g0, int64_t n) {
+    std::vector<GroupPiece> out;
+    for (int r = 0; r < g->world && n > 0; ++r) {
+        const int64_t lo = (int64_t)r * g->per;
+        const int64_t hi = r + 1 == g->world ? INT64_MAX : lo + g->per;
+        const int64_t b = std::max(g0, lo), e = std::min(g0 + n, hi);
+        if (b < e) out.push_back({r, b - g0, e - b});
+    }
+    return out;
+}
+
+int64_t group_ntotal(const fip_group* g) {
+    int64_t t = 0;
+    for (auto* s : g->shard) t += s->n_rows;
+    return t;
+}
+
+int group_ensure_exchange(fip_group* g, int nq, int k) {
+    if (g->world == 1) return FIP_OK;
+    if (!g->xchg.empty() && nq <= g->xchg_nq && k <= g->xchg_k) return FIP_OK;
+    if ((int64_t)g->world * k > kMaxCap)
+        return fail(FIP_ERR_INVALID, "devices * k must be <= 16384 (capacity of the merge kernel)");
+    for (auto* x : g->xchg) fip_exchange_destroy(x);
+    g->xchg.clear();
+    const int nq_max = std::max(1024, next_pow2(nq));
+    const int k_max = std::min(std::max(128, next_pow2(k)), kMaxCap / g->world);
+    g->xchg.assign(g->world, nullptr);
+    for (int r = 0; r < g->world; ++r) {
+        int rc = fip_exchange_create(g->devices[r], g->world, r, nq_max, k_max, &g->xchg[r]);
+        if (rc) return rc;
+    }
+    for (int r = 0; r < g->world; ++r) {
+        int rc = fip_exchange_connect_local(g->xchg[r], g->xchg.data());
+        if (rc) return rc;
+    }
+    g->xchg_nq = nq_max; g->xchg_k = k_max;
+    return FIP_OK;
+}
+
+// One rank's share of a group search (runs on that rank's worker thread).  second = the exchange
+// is repeated after flagged queries were redone on the host.  stage: 0 = everything; 1 = local
+// search only, synchronised; 2 = exchange onwards (1 then 2 = the shared-device test configuration,
+// where a spinning exchange kernel must not hold the SMs another shard's search still needs).
+int group_rank_search(fip_group* g, int r, int nq, int k, bool second, int stage = 0) {
+    fip_index* idx = g->shard[r];
+    fip_group::Rank& R = g->ranks[r];
+    std::lock_guard<std::mutex> lock(idx->mu);
+    FIP_CUDA(cudaSetDevice(g->devices[r]));
+    const size_t qn = (size_t)nq * g->dim, on = (size_t)nq * k;
+    const bool multi = g->world > 1;
+    if (stage == 2) {
+        // stage 1 already ran the local part
+    } else if (!second) {
+        FIP_CUDA(R.q32.ensure(qn));
+        FIP_CUDA(R.loc_d.ensure(on));
+        FIP_CUDA(R.loc_i.ensure(on));
+        if (multi) { FIP_CUDA(R.out_d.ensure(on)); FIP_CUDA(R.out_i.ensure(on)); }
+        FIP_CUDA(R.status.ensure(1));
+        FIP_CUDA(R.h_status.ensure(1));
+        FIP_CUDA(cudaMemcpyAsync(R.q32.p, g->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, R.stream));
+        int rc = search_enqueue(idx, R.q32.p, nq, k, R.loc_d.p, R.loc_i.p, R.stream);
+        if (rc) return rc;
+    } else {
+        // finish the local search on the host: redo whatever this shard flagged
+        int rc = copy_flags_async(idx, R.stream, nq);
+        if (rc) return rc;
+        FIP_CUDA(cudaStreamSynchronize(R.stream));
+        int redone = 0;
+        rc = search_finish_synced(idx, &redone);
+        if (rc) return rc;
+    }
+    if (stage == 1) {
+        FIP_CUDA(cudaStreamSynchronize(R.stream));
+        return FIP_OK;
+    }
+    FIP_CUDA(cudaMemsetAsync(R.status.p, 0, sizeof(uint32_t), R.stream));
+    const float* fin_d = R.loc_d.p;
+    const int64_t* fin_i = R.loc_i.p;
+    if (multi) {
+        int rc = fip_exchange_merge_status(g->xchg[r], R.loc_d.p, R.loc_i.p, nq, k, R.out_d.p, R.out_i.p,
+                                           idx->overflow.p, R.status.p, R.stream);
+        if (rc) return rc;
+        fin_d = R.out_d.p; fin_i = R.out_i.p;
+        FIP_CUDA(cudaMemcpyAsync(R.h_status.p, R.status.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, R.stream));
+    } else {
+        // single device: the status is the shard's own summary words (fetched with all the flags)
+        int rc = copy_flags_async(idx, R.stream, nq);
+        if (rc) return rc;
+    }
+    if (r == 0) {
+        FIP_CUDA(cudaMemcpyAsync(g->h_d.p, fin_d, on * sizeof(float), cudaMemcpyDeviceToHost, R.stream));
+        FIP_CUDA(cudaMemcpyAsync(g->h_i.p, fin_i, on * sizeof(int64_t), cudaMemcpyDeviceToHost, R.stream));
+    }
+    FIP_CUDA(cudaStreamSynchronize(R.stream));
+    if (!multi) R.h_status.p[0] = (idx->h_flags.p[0] ? 1u : 0u) | (idx->h_flags.p[1] ? 2u : 0u);
+    return FIP_OK;
+}
+
+int run_group_batch(fip_group* g, const std::vector<HostRequest*>& batch) {
+    std::lock_guard<std::mutex> lock(g->mu);
+    const int k = batch[0]->k;
+    int64_t nq64 = 0;
+    for (auto* b : batch) nq64 += b->nq;
+    const int nq = (int)nq64;
+    const size_t dim = (size_t)g->dim;
+    FIP_CUDA(cudaSetDevice(g->devices[0]));
+    FIP_CUDA(g->h_q.ensure((size_t)nq * dim));
+    FIP_CUDA(g->h_d.ensure((size_t)nq * k));
+    FIP_CUDA(g->h_i.ensure((size_t)nq * k));
+    size_t off = 0;
+    for (auto* b : batch) {
+        memcpy(g->h_q.p + off * dim, b->q, (size_t)b->nq * dim * sizeof(float));
+        off += (size_t)b->nq;
+    }
+    int rc = group_ensure_exchange(g, nq, k);
+    if (rc) return rc;
+    auto all_ranks = [&](bool second) -> int {
+        if (!g->shared_device) return group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second); });
+        int rc1 = group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second, 1); });
+        if (rc1) return rc1;
+        return group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second, 2); });
+    };
+    rc = all_ranks(false);
+    if (rc) return rc;
+    g->st_searches++;
+    g->st_exchange_launches += g->world > 1 ? g->world : 0;
+    uint32_t status = 0;
+    for (auto& R : g->ranks) status |= R.h_status.p[0];   // identical on every rank when world > 1
+    if (status) {
+        g->st_flagged_searches++;
+        if (g->world > 1) {
+            rc = all_ranks(true);
+            g->st_exchange_launches += g->world;
+        } else {
+            // the flags are already on the host (copied with the results)
+            int redone = 0;
+            std::lock_guard<std::mutex> l0(g->shard[0]->mu);
+            rc = search_finish_synced(g->shard[0], &redone);
+            if (!rc && redone) {
+                cudaStream_t s = g->ranks[0].stream;
+                FIP_CUDA(cudaMemcpyAsync(g->h_d.p, g->ranks[0].loc_d.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+                FIP_CUDA(cudaMemcpyAsync(g->h_i.p, g->ranks[0].loc_i.p, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+                FIP_CUDA(cudaStreamSynchronize(s));
+            }
+        }
+        if (rc) return rc;
+    } else {
+        // nothing flagged: the pending searches are complete as they are
+        for (int r = 0; r < g->world; ++r) {
+            fip_index* idx = g->shard[r];
+            std::lock_guard<std::mutex> l(idx->mu);
+            if (idx->pend.active) { idx->pend.active = false; collect_event_times(idx); }
+        }
+    }
+    off = 0;
+    for (auto* b : batch) {
+        memcpy(b->d, g->h_d.p + off * k, (size_t)b->nq * k * sizeof(float));
+        memcpy(b->i, g->h_i.p + off * k, (size_t)b->nq * k * sizeof(int64_t));
+        off += (size_t)b->nq;
+    }
+    g->co.count(batch.size());
+    return FIP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fip_group_create(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
+                     int64_t planned_rows, fip_group** out) {
+    if (!cfg || !devices || !out) return fail(FIP_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > kMaxRanks) return fail(FIP_ERR_INVALID, "1 to 16 devices");
+    if (planned_rows < 0) return fail(FIP_ERR_INVALID, "planned_rows must be >= 0");
+    // A device listed more than once puts several shards on one GPU: only useful to exercise the
+    // whole group path (routing, per-shard id bases, K4, status words) on a single-GPU box.
+    bool shared = false;
+    for (int a = 0; a < n_devices; ++a)
+        for (int b = a + 1; b < n_devices; ++b)
+            if (devices[a] == devices[b]) shared = true;
+    if (shared && !getenv("FLATIP_B200_ALLOW_SHARED_DEVICE"))
+        return fail(FIP_ERR_INVALID, "a device may appear only once in a group "
+                                     "(FLATIP_B200_ALLOW_SHARED_DEVICE=1 lifts this for tests)");
+    fip_group* g = new (std::nothrow) fip_group();
+    if (!g) return fail(FIP_ERR_NOMEM, "host allocation failed");
+    g->shared_device = shared;
+    g->world = n_devices; g->dim = cfg->dim; g->dtype = cfg->dtype;
+    g->planned_rows = planned_rows;
+    g->per = std::max<int64_t>(1, (planned_rows + n_devices - 1) / n_devices);
+    g->devices.assign(devices, devices + n_devices);
+    g->ranks.resize(n_devices);
+    for (int r = 0; r < n_devices; ++r) {
+        fip_config c = *cfg;
+        c.device = devices[r];
+        c.id_base = cfg->id_base + (int64_t)r * g->per;
+        c.capacity_rows = planned_rows > 0 ? std::min<int64_t>(g->per, std::max<int64_t>(0, planned_rows - (int64_t)r * g->per)) : 0;
+        fip_index* idx = nullptr;
+        int rc = fip_create(&c, &idx);
+        if (rc == FIP_OK && cudaStreamCreateWithFlags(&g->ranks[r].stream, cudaStreamNonBlocking) != cudaSuccess)
+            rc = fail(FIP_ERR_CUDA, "cudaStreamCreate failed");
+        if (rc) {
+            const std::string msg = g_last_error;
+            if (idx) fip_destroy(idx);
+            fip_group_destroy(g);
+            return fail(rc, msg);
+        }
+        idx->co.enabled = 0;   // coalescing happens once, at the group level
+        g->shard.push_back(idx);
+    }
+    for (int r = 0; r < n_devices; ++r) g->workers.emplace_back(group_worker, g, r);
+    *out = g;
+    return FIP_OK;
+}
+
+void fip_group_destroy(fip_group* g) {
+    if (!g) return;
+    {
+        std::lock_guard<std::mutex> lk(g->wmu);
+        g->stop = true;
+    }
+    g->cv_job.notify_all();
+    for (auto& t : g->workers) if (t.joinable()) t.join();
+    for (auto* x : g->xchg) fip_exchange_destroy(x);
+    for (size_t r = 0; r < g->ranks.size(); ++r) {
+        cudaSetDevice(g->devices[r]);
+        auto& R = g->ranks[r];
+        if (R.stream) { cudaStreamSynchronize(R.stream); cudaStreamDestroy(R.stream); }
+        R.q32.release(); R.loc_d.release(); R.out_d.release(); R.loc_i.release(); R.out_i.release();
+        R.status.release(); R.h_status.release();
+    }
+    for (auto* s : g->shard) fip_destroy(s);
+    g->h_q.release(); g->h_d.release(); g->h_i.release();
+    cudaGetLastError();
+    delete g;
+}
+
+int32_t fip_group_size(const fip_group* g) { return g ? g->world : 0; }
+fip_index* fip_group_shard(fip_group* g, int32_t r) { return (g && r >= 0 && r < g->world) ? g->shard[r] : nullptr; }
+int64_t fip_group_ntotal(const fip_group* g) { return g ? group_ntotal(g) : 0; }
+
+int fip_group_add_synthetic(fip_group* g, int64_t n, uint64_t seed) {
+    if (!g || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(g->mu);
+    const int64_t g0 = group_ntotal(g);
+    const int64_t base = g->shard[0]->cfg.id_base;
+    const auto pieces = group_route(g, g0, n);
+    return group_run(g, [g, pieces, seed, g0, base](int r) {
+        for (const auto& p : pieces)
+            if (p.r == r) return fip_add_synthetic(g->shard[r], p.count, seed, base + g0 + p.first);
+        return (int)FIP_OK;
+    });
+}
+
+int fip_group_add_host(fip_group* g, const void* rows, int64_t n, int32_t dtype) {
+    if (!g || (n > 0 && !rows) || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
+    if (n == 0) return FIP_OK;
+    std::lock_guard<std::mutex> lock(g->mu);
+    const int64_t g0 = group_ntotal(g);
+    const auto pieces = group_route(g, g0, n);
+    const size_t src_row = (size_t)g->dim * dtype_size(dtype);
+    return group_run(g, [g, pieces, rows, dtype, src_row](int r) {
+        for (const auto& p : pieces)
+            if (p.r == r)
+                return fip_add_host(g->shard[r], (const char*)rows + (size_t)p.first * src_row, p.count, dtype);
+        return (int)FIP_OK;
+    });
+}
+
+int fip_group_reset(fip_group* g) {
+    if (!g) return fail(FIP_ERR_INVALID, "null group");
+    std::lock_guard<std::mutex> lock(g->mu);
+    for (auto* s : g->shard) { int rc = fip_reset(s); if (rc) return rc; }
+    return FIP_OK;
+}
+
+int fip_group_search(fip_group* g, const float* queries, int64_t nq, int32_t k, float* distances,
+                     int64_t* ids) {
+    if (!g) return fail(FIP_ERR_INVALID, "null group");
+    int rc = check_search_args(g->shard[0], queries, nq, k, distances, ids);
+    if (rc) return rc;
+    if (nq == 0) return FIP_OK;
+    HostRequest me{queries, nq, k, distances, ids};
+    return g->co.submit(me, [g](const std::vector<HostRequest*>& batch) { return run_group_batch(g, batch); });
+}
+
+int fip_group_set_option(fip_group* g, const char* key, int64_t value) {
+    if (!g || !key) return fail(FIP_ERR_INVALID, "bad argument");
+    const std::string k(key);
+    if (k == "coalesce") { g->co.enabled = value != 0; return FIP_OK; }
+    if (k == "coalesce_max_batch") {
+        if (value < 1) return fail(FIP_ERR_INVALID, "coalesce_max_batch must be >= 1");
+        g->co.max_batch = value;
+        return FIP_OK;
+    }
+    for (auto* s : g->shard) { int rc = fip_set_option(s, key, value); if (rc) return rc; }
+    return FIP_OK;
+}
+
+int64_t fip_group_get_stat(const fip_group* g, const char* key) {
+    if (!g || !key) return -1;
+    const std::string k(key);
+    if (k == "devices") return g->world;
+    if (k == "rows_per_shard") return g->per;
+    if (k == "searches") return g->st_searches;
+    if (k == "flagged_searches") return g->st_flagged_searches;
+    if (k == "exchange_launches") return g->st_exchange_launches;
+    if (k == "host_batches") return g->co.st_batches;
+    if (k == "host_calls") return g->co.st_calls;
+    if (k == "coalesced_calls") return g->co.st_coalesced_calls;
+    if (k == "last_batch_calls") return g->co.st_last_batch_calls;
+    if (k == "host_queries") return g->co.st_queries;
+    if (k == "distinct_queries") return g->co.st_distinct;
+    // everything else: summed over the shards' last searches (launches, overflow_queries, ...),
+    // except "variant"-like values which are taken from shard 0
+    if (k == "variant" || k == "phases" || k == "candidate_capacity" || k == "cta_group" || k == "filter_f16" ||
+        k == "query_split_used")
+        return fip_get_stat(g->shard[0], key);
+    int64_t sum = 0;
+    for (auto* s : g->shard) {
+        const int64_t v = fip_get_stat(s, key);
+        if (v < 0) return v;
+        sum += v;
+    }
+    if (k == "launches") sum += g->world > 1 ? g->world : 0;   // + one K4 launch per device
+    return sum;
+}
+
+}  // extern "C"

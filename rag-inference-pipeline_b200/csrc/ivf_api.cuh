@@ -81,7 +81,7 @@ struct fivf_index {
     void* plan_ws = nullptr;   // IvfPlan: host plan workspace, reused by every search (build_plan)
     // stats of the last search
     int64_t st_launches = 0, st_phases = 0, st_tiles = 0, st_rows = 0, st_pairs = 0, st_overflow = 0,
-            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0, st_device_plan = 0, st_f16 = 0;
+            st_cap = 0, st_plan_us = 0, st_tiles16 = 0, st_occ16 = -1, st_distinct_rows = 0, st_scan_ns = 0, st_tc_items = 0, st_tc_pairs = 0, st_crowded = 0, st_crowded_final = 0, st_device_plan = 0, st_f16 = 0;
     int64_t ntotal() const { return n_sorted + pend_n; }
 };
 
@@ -442,7 +442,7 @@ int launch_ivf_scan(fivf_index* h, const ivf::ScanIvfArgs& a, int* launches) {
 int ivf_select(fivf_index* h, int nq, int k, int cap, bool final_pass, bool live, int keep_max, int* launches) {
     SelectArgs s{};
     if (!final_pass) {   // exactness window (see ivf_eps_kernel)
-        s.win_eps = h->eps.p; s.win_scale = h->ones.p; s.keep_max = keep_max; s.uncert = h->flags.p + (nq + 1);
+        s.win_eps = h->eps.p; s.win_scale = h->ones.p; s.keep_max = keep_max; s.uncert = h->flags.p + 1;
     }
     s.cand = h->cand.p; s.cnt = h->cnt.p; s.thr = h->thr.p; s.cap = (uint32_t)cap; s.k = k;
     s.final_pass = final_pass ? 1 : 0; s.out_d = h->sc.p; s.out_i = h->pos.p; s.id_base = 0;
@@ -459,7 +459,7 @@ int ivf_select(fivf_index* h, int nq, int k, int cap, bool final_pass, bool live
 // One search of device-resident queries; results to device out_d / out_i.  Synchronises (the probe
 // table is planned on the host).  *overflowed = some candidate list overflowed (redo in safe mode).
 int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float* out_d, int64_t* out_i,
-             bool safe, bool allow_tc, bool* overflowed, bool* crowded) {
+             bool safe, bool allow_tc, bool* overflowed, bool* crowded, bool wide_window = false) {
     const int dim = h->dim, nlist = h->nlist;
     int launches = 0;
     nprobe = std::max(1, std::min(nprobe, nlist));
@@ -467,7 +467,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     FIP_CUDA(h->ckeys.ensure((size_t)nq * nlist));
     FIP_CUDA(h->probe_d.ensure((size_t)nq * nprobe));
     FIP_CUDA(h->probe_i.ensure((size_t)nq * nprobe));
-    FIP_CUDA(h->flags.ensure(2 * ((size_t)nq + 1)));
+    FIP_CUDA(h->flags.ensure(flag_words(nq)));
     FIP_CUDA(h->thr.ensure(nq));
     FIP_CUDA(h->cnt.ensure(nq));
     FIP_CUDA(h->sc.ensure((size_t)nq * k));
@@ -479,7 +479,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     if (h->n_sorted == 0) FIP_CUDA(cudaMemsetAsync(h->x2max.p, 0, sizeof(float), h->stream));
     ivf::row_norm2_kernel<<<(nq + 7) / 8, 256, 0, h->stream>>>(q_dev, nq, dim, h->qnorm.p);
     FIP_CUDA(cudaGetLastError());
-    init_lists_kernel<<<(nq + 256) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nq);
+    init_lists_kernel<<<(2 * nq + 2 + 255) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nullptr, nq);
     FIP_CUDA(cudaGetLastError());
     // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
     {
@@ -499,7 +499,9 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     }
     const int cap = safe ? kMaxCap : std::min(std::max(4096, 32 * next_pow2(k)), kMaxCap);
     const bool live = h->live_thr && !safe;
-    const int keep_max = std::min(cap / 2, 2 * k + 64);   // truncation limit of the exactness window
+    // truncation limit of the exactness window; wide_window (last resort for clusters of duplicates
+    // or near-ties larger than 2k + 64 rows): half the list capacity
+    const int keep_max = wide_window ? cap / 2 : std::min(cap / 2, 2 * k + 64);
     const bool big_ok = h->qb_max >= 16 && ivf::scan_stages(16, dim) >= 2;
     const bool tc_ok = allow_tc && h->tc_min > 0 && dim % 32 == 0;
     const int k_plan = std::max(k, keep_max);
@@ -695,7 +697,7 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
         h->tmap_valid = true;
     }
     // the coarse select used cnt / thr: reset the lists
-    init_lists_kernel<<<(nq + 256) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nq);
+    init_lists_kernel<<<(2 * nq + 2 + 255) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nullptr, nq);
     FIP_CUDA(cudaGetLastError());
     launches++;
 
@@ -757,13 +759,12 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     FIP_CUDA(cudaGetLastError());
     launches++;
     FIP_CUDA(h->h_flags.ensure(4));
-    FIP_CUDA(cudaMemcpyAsync(h->h_flags.p, h->flags.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
-    FIP_CUDA(cudaMemcpyAsync(h->h_flags.p + 1, h->flags.p + (nq + 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    FIP_CUDA(cudaMemcpyAsync(h->h_flags.p, h->flags.p, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
     FIP_CUDA(cudaStreamSynchronize(h->stream));
     *overflowed = h->h_flags.p[0] != 0;
-    // some query's exactness window held more than keep_max candidates and was truncated; with the
-    // tf32 filter in play the caller redoes the batch on the (much narrower) fp32 window
-    *crowded = h->h_flags.p[1] != 0 && use_tc;
+    // some query's exactness window held more than keep_max candidates and was truncated: the
+    // caller redoes the batch on the (much narrower) fp32 window, then with a wide window
+    *crowded = h->h_flags.p[1] != 0;
     h->st_launches = launches; h->st_phases = (int64_t)n_phases; h->st_tiles = (int64_t)n_tiles;
     h->st_rows = pl_rows; h->st_pairs = pl_pairs; h->st_cap = cap;
     h->st_distinct_rows = pl_distinct;
@@ -800,6 +801,16 @@ int fivf_search_checked(fivf_index* h, const float* q_dev, int nq, int k, int np
         if (rc) return rc;
         if (over) return fail(FIP_ERR_STATE, "internal error: IVF safe mode overflowed a candidate list");
     }
+    if (crowded) {
+        // more than 2k + 64 candidates inside the fp32 rounding window (large clusters of duplicate
+        // or nearly duplicate rows): safe mode with the window limit at half the list capacity
+        rc = fivf_run(h, q_dev, nq, k, nprobe, out_d, out_i, true, false, &over, &crowded, true);
+        if (rc) return rc;
+        if (over) return fail(FIP_ERR_STATE, "internal error: IVF safe mode overflowed a candidate list");
+    }
+    // still crowded: over 8192 rows tie within fp32 rounding of one another for some query; the
+    // result is then exact only up to that rounding (reported, never silent)
+    h->st_crowded_final = crowded ? 1 : 0;
     return FIP_OK;
 }
 
@@ -1155,6 +1166,7 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "tensor_items") return h->st_tc_items;
     if (k == "tensor_pairs") return h->st_tc_pairs;
     if (k == "crowded_window") return h->st_crowded;
+    if (k == "crowded_window_unresolved") return h->st_crowded_final;
     if (k == "device_plan") return h->st_device_plan;
     if (k == "tensor_f16") return h->st_f16;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;

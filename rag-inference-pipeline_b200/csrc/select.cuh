@@ -42,7 +42,7 @@ struct SelectArgs {
     int64_t* out_i;       // [nq, k]
     int64_t id_base;      // global id of local row 0
     const float* out_scale;  // [nq] or null: multiply reported scores (undoes the query scaling)
-    uint32_t* overflow;   // [1 + nq]: [0] = any overflow, [1+q] = query q overflowed
+    uint32_t* overflow;   // flag words (flag_slot): [0] = any overflow, [2 + 2q] = query q overflowed
     // Exactness window (tensor-core variant only; null = exact scores, keep exactly k).
     // The scan's scores are APPROXIMATE: |approx - exact| <= eps[q] for every stored row (see
     // prepare_queries_kernel).  Let A be the k-th best approximate score so far.  The k-th best
@@ -56,7 +56,7 @@ struct SelectArgs {
     const float* win_eps;     // [nq] eps in unscaled score units
     const float* win_scale;   // [nq] approx-score scale (out_scale of the scan)
     int keep_max;             // truncation limit for the window (<= cap)
-    uint32_t* uncert;         // [1 + nq] like `overflow`
+    uint32_t* uncert;         // like `overflow`; callers pass overflow + 1, which interleaves the two sets
     // Live thresholds (common.cuh, ScanArgs::hist): an intermediate pass re-seeds the query's score
     // histogram with the candidates it keeps and publishes the bucket origin.  Null = off.
     uint32_t* hist;           // [nq, 256]
@@ -65,13 +65,22 @@ struct SelectArgs {
 
 constexpr int kSelectThreads = 256;
 
+// Flag layout shared by the flat and IVF paths: F[0] = some list overflowed, F[1] = some query
+// could not be certified, then per query q: F[2 + 2q] overflow, F[3 + 2q] uncertified.  The two
+// summary words are adjacent so that ONE 8-byte read (K4, or the D2H copy that fetches the
+// results) tells whether anything has to be redone.
+__host__ __device__ inline size_t flag_slot(int q) { return 2 + 2 * (size_t)q; }
+__host__ __device__ inline size_t flag_words(int nq) { return 2 + 2 * (size_t)nq; }
+
 // k-th largest of the c distinct keys in s_keys (1 <= k <= c) by most-significant-digit radix
 // select, 8 bits per round, starting at the highest bit in which the keys differ at all.  Keys are
 // distinct (the low word encodes the row), so the answer is unique.  Whole CTA; returns the key.
+template <int kThreads>
 __device__ __forceinline__ uint64_t kth_largest_key(const uint64_t* s_keys, int c, int k,
-                                                    uint32_t* s_hist /*[256]*/, uint64_t* s_red /*[20]*/) {
+                                                    uint32_t* s_hist /*[256]*/, uint64_t* s_red /*[2 * warps + 4]*/) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int kWarps = kSelectThreads / 32;
+    constexpr int kWarps = kThreads / 32;
+    constexpr int kSelectThreads = kThreads;   // (shadows the default CTA size inside this function)
     // CTA-wide min / max -> the bits above `hi` are common to every key
     uint64_t mn = ~0ull, mx = 0ull;
     for (int i = tid; i < c; i += kSelectThreads) { uint64_t x = s_keys[i]; mn = min(mn, x); mx = max(mx, x); }
@@ -94,7 +103,7 @@ __device__ __forceinline__ uint64_t kth_largest_key(const uint64_t* s_keys, int 
     while (true) {
         const int shift = undecided > 8 ? undecided - 8 : 0;
         const int nbits = undecided - shift;             // 1..8 bits decided this round
-        s_hist[tid] = 0u;                                // kSelectThreads == 256 bins
+        if (tid < 256) s_hist[tid] = 0u;                 // 256 bins
         __syncthreads();
         for (int i = tid; i < c; i += kSelectThreads) {
             const uint64_t x = s_keys[i];
@@ -141,18 +150,21 @@ __device__ __forceinline__ uint64_t kth_largest_key(const uint64_t* s_keys, int 
     }
 }
 
-// One CTA (kSelectThreads threads) per query.  Dynamic smem: (cap + next_pow2(k)) * 8 bytes.
-// Intermediate passes only need the k best as a SET (any order) and the new threshold: radix
-// select + compaction.  The final pass sorts those k (bitonic over next_pow2(k) keys) and emits.
-__global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs a) {
+// One CTA (kThreads threads: 256, or 1024 for the long lists of large k) per query.  Dynamic smem:
+// (cap + next_pow2(k)) * 8 bytes.  Intermediate passes only need the k best as a SET (any order)
+// and the new threshold: radix select + compaction.  The final pass sorts those k (bitonic over
+// next_pow2(k) keys) and emits.
+template <int kThreads>
+__device__ __forceinline__ void select_topk_body(const SelectArgs& a) {
+    constexpr int kSelectThreads = kThreads;
     extern __shared__ __align__(16) uint64_t s_keys[];
     __shared__ uint32_t s_hist[256];
-    __shared__ uint64_t s_red[20];
+    __shared__ uint64_t s_red[2 * (kThreads / 32) + 4];
     __shared__ uint32_t s_count;
     const int q = blockIdx.x, tid = threadIdx.x;
     uint32_t c = a.dense_count >= 0 ? (uint32_t)a.dense_count : a.cnt[q];
     if (c > a.cap) {  // the scan dropped candidates: this query must be redone (host fallback)
-        if (tid == 0) { a.overflow[0] = 1u; a.overflow[1 + q] = 1u; }
+        if (tid == 0) { a.overflow[0] = 1u; a.overflow[flag_slot(q)] = 1u; }
         c = a.cap;
     }
     uint64_t* list = a.cand + (size_t)q * a.cap;
@@ -161,7 +173,7 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
     __syncthreads();
     const int keep = min((int)c, a.k);
     uint64_t kth = 0ull;  // every key >= kth is kept (all of them when c <= k)
-    if ((int)c > a.k) kth = kth_largest_key(s_keys, (int)c, a.k, s_hist, s_red);
+    if ((int)c > a.k) kth = kth_largest_key<kThreads>(s_keys, (int)c, a.k, s_hist, s_red);
     if (!a.final_pass) {
         // threshold and the limit key: candidates with key > lim stay in the list
         float t = kNegInf;
@@ -203,8 +215,8 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
             if ((int)kept > a.keep_max && a.win_eps) {
                 // the window is crowded: truncate to the keep_max best and flag the query
                 __syncthreads();
-                if (tid == 0) { s_count = 0u; a.uncert[0] = 1u; a.uncert[1 + q] = 1u; }
-                const uint64_t kth2 = kth_largest_key(s_keys, (int)c, a.keep_max, s_hist, s_red);
+                if (tid == 0) { s_count = 0u; a.uncert[0] = 1u; a.uncert[flag_slot(q)] = 1u; }
+                const uint64_t kth2 = kth_largest_key<kThreads>(s_keys, (int)c, a.keep_max, s_hist, s_red);
                 for (int i = tid; i < (int)c; i += kSelectThreads) {
                     const uint64_t x = s_keys[i];
                     if (x >= kth2) list[atomicAdd(&s_count, 1u)] = key_to_raw(x);
@@ -216,7 +228,7 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
         }
         if (a.hist) {
             __syncthreads();
-            s_hist[tid] = 0u;                 // kSelectThreads == kHistBins
+            if (tid < kHistBins) s_hist[tid] = 0u;
             __syncthreads();
             const uint32_t hb = orderable_f32(t);
             for (int i = tid; i < (int)c; i += kSelectThreads) {
@@ -227,7 +239,7 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
                 }
             }
             __syncthreads();
-            a.hist[(size_t)q * kHistBins + tid] = s_hist[tid];
+            if (tid < kHistBins) a.hist[(size_t)q * kHistBins + tid] = s_hist[tid];
             if (tid == 0) a.hbase[q] = hb;
         }
         if (tid == 0) {
@@ -256,6 +268,12 @@ __global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs 
         a.out_i[(size_t)q * a.k + i] = valid ? a.id_base + (int64_t)key_row(key) : -1;
     }
 }
+__global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs a) { select_topk_body<kSelectThreads>(a); }
+constexpr int kSelectThreadsBig = 1024;
+__global__ void __launch_bounds__(kSelectThreadsBig) select_topk_kernel_big(SelectArgs a) { select_topk_body<kSelectThreadsBig>(a); }
+// Lists of 8 K entries and more (k >= 256) get the 1024-thread form: one CTA per SM either way (the
+// list fills the shared memory), so the per-key passes run 4x wider.
+inline bool select_wants_big(int cap) { return cap >= 8192; }
 
 // Exact rescoring of the surviving candidates (tensor-core variant).  The tcgen05 scan sees the
 // fp32 queries rounded to 16 bits, so its scores carry ~1e-4 relative error; that is fine for
@@ -268,34 +286,54 @@ __global__ void rescore_kernel(uint64_t* __restrict__ cand, const uint32_t* __re
                                uint32_t cap, int nq, int kprime, const T* __restrict__ corpus,
                                const float* __restrict__ q32, int dim) {
     constexpr int EPV = 16 / sizeof(T);
+    constexpr int G = 4;    // candidates a warp keeps in flight: the kernel is latency-bound (one
+                            // scattered row per candidate), so memory-level parallelism is what counts
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int nvec = dim / EPV;
-    for (int64_t w = warp; w < (int64_t)nq * kprime; w += nwarps) {
-        const int q = (int)(w / kprime), slot = (int)(w - (int64_t)q * kprime);
-        if (slot >= (int)min(cnt[q], cap)) continue;  // warp-uniform
-        const uint64_t key = cand[(size_t)q * cap + slot];
-        const uint32_t row = key_row(key);
-        const T* x = corpus + (size_t)row * dim;
+    const int groups = (kprime + G - 1) / G;            // per query: slots [G g, G g + G)
+    for (int64_t w = warp; w < (int64_t)nq * groups; w += nwarps) {
+        const int q = (int)(w / groups), s0 = (int)(w - (int64_t)q * groups) * G;
+        const int have = (int)min(cnt[q], cap);
+        if (s0 >= have) continue;  // warp-uniform
         const float* qv = q32 + (size_t)q * dim;
-        float acc = 0.f;
-        for (int v = lane; v < nvec; v += 32) {
-            uint4 raw = *reinterpret_cast<const uint4*>(x + (size_t)v * EPV);
-            float xf[EPV];
-            VecOps<T>::unpack(raw, xf);
+        uint64_t key[G];
+        const T* x[G];
 #pragma unroll
-            for (int h = 0; h < EPV / 4; ++h) {
-                float4 qq = *reinterpret_cast<const float4*>(qv + (size_t)v * EPV + 4 * h);
-                acc = fmaf(xf[4 * h + 0], qq.x, acc);
-                acc = fmaf(xf[4 * h + 1], qq.y, acc);
-                acc = fmaf(xf[4 * h + 2], qq.z, acc);
-                acc = fmaf(xf[4 * h + 3], qq.w, acc);
+        for (int g = 0; g < G; ++g) {
+            key[g] = s0 + g < have ? cand[(size_t)q * cap + s0 + g] : 0ull;
+            x[g] = corpus + (size_t)key_row(key[g] ? key[g] : cand[(size_t)q * cap + s0]) * dim;
+        }
+        float acc[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) acc[g] = 0.f;
+        for (int v = lane; v < nvec; v += 32) {
+            uint4 raw[G];
+#pragma unroll
+            for (int g = 0; g < G; ++g) raw[g] = *reinterpret_cast<const uint4*>(x[g] + (size_t)v * EPV);
+            float4 qq[EPV / 4];
+#pragma unroll
+            for (int h = 0; h < EPV / 4; ++h) qq[h] = *reinterpret_cast<const float4*>(qv + (size_t)v * EPV + 4 * h);
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float xf[EPV];
+                VecOps<T>::unpack(raw[g], xf);
+#pragma unroll
+                for (int h = 0; h < EPV / 4; ++h) {
+                    acc[g] = fmaf(xf[4 * h + 0], qq[h].x, acc[g]);
+                    acc[g] = fmaf(xf[4 * h + 1], qq[h].y, acc[g]);
+                    acc[g] = fmaf(xf[4 * h + 2], qq[h].z, acc[g]);
+                    acc[g] = fmaf(xf[4 * h + 3], qq[h].w, acc[g]);
+                }
             }
         }
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);
-        if (lane == 0) cand[(size_t)q * cap + slot] = make_raw_key(acc, row);
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) acc[g] += __shfl_xor_sync(0xFFFFFFFFu, acc[g], off);
+            if (lane == 0 && key[g]) cand[(size_t)q * cap + s0 + g] = make_raw_key(acc[g], key_row(key[g]));
+        }
     }
 }
 

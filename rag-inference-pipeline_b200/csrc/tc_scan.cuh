@@ -53,15 +53,20 @@ constexpr int NUM_THREADS = (EPI_WARP0 + EPI_WARPS) * 32;
 // storage, 2 for bf16 storage (bf16 hi + lo, 2^-17).  tcgen05.mma needs A and B in the SAME format
 // (mixing fp16 x bf16 is an illegal instruction on sm_100a), hence bf16 queries for bf16 corpora.
 // The filter runs on these rounded products; survivors are rescored exactly (select.cuh).
-template <int kFmt, int kSplit, int kCtas> struct Cfg {
+// kStage = survivor slots per epilogue thread and tile in the shared-memory staging area of the
+// DEFERRED epilogue (0 = off: survivors are stored straight from TMEM in a second pass).
+template <int kFmt, int kSplit, int kCtas, int kStage = 0> struct Cfg {
     static constexpr int ELEM_BYTES = kFmt == 2 ? 4 : 2;
     static constexpr int BK = BK_BYTES / ELEM_BYTES;       // elements per stage
     static constexpr int MMAS_PER_STAGE = 4;               // 32 bytes of K per instruction
     static constexpr int B_LOCAL_BYTES = B_BYTES / kCtas;  // this CTA's share of the corpus tile
     static constexpr int STAGE_BYTES = kSplit * A_BYTES + B_LOCAL_BYTES;
-    static constexpr int STAGES = (225 * 1024) / STAGE_BYTES > 8 ? 8 : (225 * 1024) / STAGE_BYTES;
-    // operand ring + barriers (the epilogue works out of TMEM and registers)
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256;
+    // warps x slots x lanes x 8 B
+    static constexpr int STAGING_BYTES = EPI_WARPS * kStage * 32 * 8;
+    static constexpr int RING_BYTES = 225 * 1024 - STAGING_BYTES;
+    static constexpr int STAGES = RING_BYTES / STAGE_BYTES > 8 ? 8 : RING_BYTES / STAGE_BYTES;
+    // operand ring + barriers + staging (the epilogue otherwise works out of TMEM and registers)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 + STAGING_BYTES;
 };
 
 // Epilogue of one thread (= one query) over its EPI_CHUNKS chunks of 32 accumulator columns starting
@@ -153,6 +158,156 @@ __device__ __forceinline__ void epilogue_filter(const ScanArgs& a, uint32_t tadd
                                 (int)(threadIdx.x & 31));
 }
 
+// ---------------------------------------------------------------------------------------------
+// DEFERRED epilogue (kStage > 0; chosen for large k, where almost every tile has survivors).
+// With k = 1024 about half of all (warp, tile) pairs hold a survivor, so in the two-pass form
+// every tile pays  pass 1 -> atomicAdd round trip to L2 -> pass 2 (TMEM re-read + stores)  BEFORE
+// its accumulator is handed back: the tensor pipe waits (70 % active in the k = 1024 profile,
+// profiles/r02_ncu_full_cfg5_before_deferred_epilogue.csv).  Here pass 1 also copies the survivors'
+// keys into a small per-thread staging area in shared memory; the accumulator is released right
+// after pass 1, and only then does the warp reserve list slots (the atomicAdd round trip) and
+// copy the staged keys to the candidate list (epilogue_flush) -- off the tensor pipe's critical
+// path, in time the epilogue warps otherwise spend waiting for the next accumulator.
+// A tile in which some thread of the warp has more than kStage survivors (the first tiles after
+// the dense phase) takes the two-pass route for that warp.
+struct Pending {          // a tile's survivors, staged but not yet in the candidate list
+    uint32_t n = 0;       // this thread's survivors
+    int q = 0;
+    uint32_t hb = 0;
+    uint32_t stg = 0;     // shared-memory address of this thread's slot 0
+};
+
+__device__ __forceinline__ void stage_append_if(uint32_t& addr, uint32_t lo, uint32_t hi, uint32_t take) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %3, 0;\n\t"
+        "@p st.shared.v2.u32 [%0], {%1, %2};\n\t"
+        "@p add.u32 %0, %0, 256;\n\t"      // next slot of the same lane: 32 lanes x 8 bytes further
+        "}"
+        : "+r"(addr)
+        : "r"(lo), "r"(hi), "r"(take)
+        : "memory");
+}
+
+// Writes a pending tile's staged keys to its query's candidate list (all 32 lanes must call).
+template <int kStage>
+__device__ __forceinline__ void epilogue_flush(const ScanArgs& a, const Pending& p) {
+    if (!__any_sync(0xFFFFFFFFu, p.n != 0u)) return;
+    uint32_t slot = 0u;
+    if (p.n) slot = atomicAdd(a.cnt + p.q, p.n);
+    const bool fits = p.n != 0u && slot + p.n <= a.cap;   // else: overflow, flagged by the select pass
+    uint64_t* list = a.cand + (size_t)p.q * a.cap + slot;
+    uint32_t* hrow = a.hist ? a.hist + (size_t)p.q * kHistBins : nullptr;
+#pragma unroll
+    for (int s = 0; s < kStage; ++s) {
+        if (fits && (uint32_t)s < p.n) {
+            uint32_t lo, hi;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(p.stg + 256u * s));
+            asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(list + s), "r"(lo), "r"(hi) : "memory");
+            if (hrow) atomicAdd(hrow + hist_bucket(hi, p.hb), 1u);
+        }
+    }
+    if (a.hist)
+        refresh_thresholds_warp(a, fits && ((slot + p.n) / kRefreshEvery != slot / kRefreshEvery), p.q,
+                                (int)(threadIdx.x & 31));
+}
+
+// Pass 1 + staging.  Returns what is left pending (n == 0 when nothing survived, or when the warp
+// took the two-pass route and already stored everything).
+template <int kStage>
+__device__ __forceinline__ Pending epilogue_filter_deferred(const ScanArgs& a, uint32_t taddr, int q, float thr,
+                                                            uint32_t hb, uint32_t tile_row0, int c0,
+                                                            uint32_t stg_addr) {
+    static_assert(EPI_CHUNKS <= 4, "masks are packed into two 64-bit registers");
+    uint64_t m01 = 0ull, m23 = 0ull;
+    uint32_t n = 0;
+    uint32_t stg = stg_addr;
+    bool ovf = false;
+#pragma unroll 1
+    for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
+        const int c = c0 + ci;
+        const uint32_t row_base = tile_row0 + (uint32_t)c * 32;
+        if (row_base >= a.row_end) break;  // warp-uniform
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        if (row_base + 32 > a.row_end) {  // ragged last chunk (warp-uniform)
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (row_base + j >= a.row_end) v[j] = kNegInf;
+        }
+        uint32_t mask = 0u;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            float mx = fmaxf(fmaxf(v[8 * g], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3]));
+            mx = fmaxf(mx, fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+            if (mx > thr) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) mask_or_if_gt(mask, v[8 * g + j], thr, 1u << (8 * g + j));
+            }
+        }
+        if (mask) {
+            const uint32_t cnt = (uint32_t)__popc(mask);
+            if (!ovf && n + cnt <= (uint32_t)kStage) {
+                const uint32_t inv_row0 = 0xFFFFFFFFu - row_base;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    if ((mask >> (8 * g)) & 0xFFu) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            stage_append_if(stg, inv_row0 - (uint32_t)(8 * g + j), __float_as_uint(v[8 * g + j]),
+                                            mask & (1u << (8 * g + j)));
+                    }
+                }
+            } else {
+                ovf = true;
+            }
+            n += cnt;
+        }
+        const uint64_t shifted = (uint64_t)mask << (32 * (ci & 1));
+        if (ci & 2) m23 |= shifted; else m01 |= shifted;
+    }
+    Pending p;
+    p.q = q; p.hb = hb; p.stg = stg_addr;
+    if (!__any_sync(0xFFFFFFFFu, ovf)) {
+        p.n = n;      // slots are reserved and the keys copied after the accumulator's release
+        return p;
+    }
+    // two-pass route for this warp and tile (some thread has more survivors than staging slots)
+    uint32_t slot = 0u;
+    if (n) slot = atomicAdd(a.cnt + q, n);
+    const bool fits = n != 0u && slot + n <= a.cap;
+    uint64_t* list = a.cand + (size_t)q * a.cap + slot;
+    uint32_t* hrow = a.hist ? a.hist + (size_t)q * kHistBins : nullptr;
+#pragma unroll 1
+    for (int ci = 0; ci < EPI_CHUNKS; ++ci) {
+        const uint32_t cmask = (uint32_t)(((ci & 2) ? m23 : m01) >> (32 * (ci & 1)));
+        if (!__any_sync(0xFFFFFFFFu, cmask != 0u)) continue;  // warp-uniform
+        const uint32_t mask = fits ? cmask : 0u;
+        const int c = c0 + ci;
+        float v[32];
+        tmem_ld_32x32b_x32(taddr + (uint32_t)c * 32, v);
+        const uint32_t inv_row0 = 0xFFFFFFFFu - (tile_row0 + (uint32_t)c * 32);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if ((mask >> (8 * g)) & 0xFFu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t bits = __float_as_uint(v[8 * g + j]);
+                    const uint32_t take = mask & (1u << (8 * g + j));
+                    list_append_if(list, inv_row0 - (uint32_t)(8 * g + j), bits, take);
+                    if (take && hrow) atomicAdd(hrow + hist_bucket(bits, hb), 1u);
+                }
+            }
+        }
+    }
+    if (a.hist)
+        refresh_thresholds_warp(a, fits && ((slot + n) / kRefreshEvery != slot / kRefreshEvery), q,
+                                (int)(threadIdx.x & 31));
+    p.n = 0u;
+    return p;
+}
+
 // Phase 0: every score of the tile is written at slot = row - row_begin (no threshold yet).
 __device__ __forceinline__ void epilogue_dense(const ScanArgs& a, uint32_t taddr, int q, bool active,
                                                uint32_t tile_row0, int c0, int c1) {
@@ -174,11 +329,11 @@ __device__ __forceinline__ void epilogue_dense(const ScanArgs& a, uint32_t taddr
 // tmap_q covers the prepared query matrix [kSplit * nq_pad, dim] (term t of query q at row
 // t * nq_pad + q); tmap_x the corpus shard [n_rows, dim].  Both use [BK x 128]-element boxes.
 // Launch with a (2,1,1) cluster when kCtas == 2; gridDim.x must then be even.
-template <int kFmt, int kSplit, int kCtas>
+template <int kFmt, int kSplit, int kCtas, int kStage = 0>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                ScanArgs a, int n_qtiles) {
-    using C = Cfg<kFmt, kSplit, kCtas>;
+    using C = Cfg<kFmt, kSplit, kCtas, kStage>;
     constexpr int STAGES = C::STAGES;
     constexpr int STAGE_BYTES = C::STAGE_BYTES;
     constexpr int B_OFF = kSplit * A_BYTES;
@@ -191,6 +346,7 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
     auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    const uint32_t stg_base = bar_base + 256u;   // deferred epilogue: [EPI_WARPS][kStage][32 lanes] keys
     volatile uint32_t* tmem_slot_ptr =
         reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -302,29 +458,34 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         const uint32_t tempty0 = kCtas == 2 ? mapa_shared(tempty_bar(0), 0) : tempty_bar(0);
         // Threshold and histogram origin of a thread's query come from L2 (thresholds are raised
         // live by whoever appends candidates) and are fetched ONE TILE AHEAD, so the round trip is
-        // never on the epilogue's critical path.
-        auto query_of = [&](int t) { return ((t % n_qgroups) * kCtas + (int)cta_rank) * BM + w * 32 + lane; };
+        // never on the epilogue's critical path.  Tile coordinates advance incrementally (no
+        // integer division per tile).
+        auto query_at = [&](int qg_) { return (qg_ * kCtas + (int)cta_rank) * BM + w * 32 + lane; };
         auto load_thr = [&](int qq) { return qq < a.nq ? __ldcg(a.thr + qq) : __builtin_huge_valf(); };
         auto load_hb = [&](int qq) { return (qq < a.nq && a.hist) ? __ldcg(a.hbase + qq) : 0u; };
+        int ct = t_begin / n_qgroups, qg = t_begin - ct * n_qgroups;
         float thr_next = 0.f;
         uint32_t hb_next = 0u;
-        if (t_begin < t_end) { thr_next = load_thr(query_of(t_begin)); hb_next = load_hb(query_of(t_begin)); }
+        if (t_begin < t_end) { thr_next = load_thr(query_at(qg)); hb_next = load_hb(query_at(qg)); }
+        const uint32_t stg_warp = stg_base + (uint32_t)(warp - EPI_WARP0) * (kStage * 32 * 8) + (uint32_t)lane * 8u;
         int it = 0;
         for (int t = t_begin; t < t_end; ++t, ++it) {
-            const int ct = t / n_qgroups, qg = t - ct * n_qgroups;
-            const int qt = qg * kCtas + (int)cta_rank;
             const int buf = it & 1;
             const uint32_t aph = (uint32_t)(it >> 1) & 1u;
-            const int q = qt * BM + w * 32 + lane;
+            const int q = query_at(qg);
             const bool active = q < a.nq;
             const float thr = thr_next;
             const uint32_t hb = hb_next;
-            if (t + 1 < t_end) { thr_next = load_thr(query_of(t + 1)); hb_next = load_hb(query_of(t + 1)); }
             const uint32_t tile_row0 = a.row_begin + (uint32_t)ct * BN;
+            if (++qg == n_qgroups) { qg = 0; ++ct; }
+            if (t + 1 < t_end) { thr_next = load_thr(query_at(qg)); hb_next = load_hb(query_at(qg)); }
             mbar_wait(tfull_bar(buf), aph);
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(w * 32) << 16) + (uint32_t)buf * BN;
+            Pending cur;
             if (a.dense) epilogue_dense(a, taddr, q, active, tile_row0, c0, c0 + EPI_CHUNKS);
+            else if (kStage > 0)
+                cur = epilogue_filter_deferred<kStage>(a, taddr, q, thr, hb, tile_row0, c0, stg_warp);
             else epilogue_filter(a, taddr, q, thr, hb, tile_row0, c0);
             tcgen05_fence_before();
             __syncwarp();
@@ -332,6 +493,9 @@ tc_scan_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
                 if (kCtas == 2) mbar_arrive_cluster(tempty0 + 8u * buf);
                 else mbar_arrive(tempty_bar(buf));
             }
+            // the accumulator is back with the MMA warp: reserve list slots and write out what this
+            // tile staged
+            if (kStage > 0) epilogue_flush<(kStage > 0 ? kStage : 1)>(a, cur);
         }
     }
 

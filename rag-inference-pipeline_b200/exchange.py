@@ -51,6 +51,16 @@ class PeerExchange:
         _native.check(self._lib.fip_exchange_merge(self._h, P(d_ptr), P(i_ptr), int(nq), int(k),
                                                    P(out_d_ptr), P(out_i_ptr), P(stream)))
 
+    def merge_status(self, d_ptr: int, i_ptr: int, nq: int, k: int, out_d_ptr: int, out_i_ptr: int,
+                     flags_ptr: int, status_ptr: int, stream: int = 0) -> None:
+        """``merge`` with the shards' search statuses travelling with the rows: ``flags_ptr`` = the
+        local index's ``flags_device_ptr()``; the device word at ``status_ptr`` is OR-ed with bit 0 /
+        bit 1 when ANY rank's local search overflowed / could not be certified."""
+        P = ctypes.c_void_p
+        _native.check(self._lib.fip_exchange_merge_status(
+            self._h, P(d_ptr), P(i_ptr), int(nq), int(k), P(out_d_ptr), P(out_i_ptr), P(flags_ptr),
+            P(status_ptr), P(stream)))
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._lib.fip_exchange_destroy(self._h)

@@ -58,6 +58,11 @@ class FlatIPIndex:
             raise ValueError(f"expected rows of shape (n, {self.d}), got {x.shape}")
         _native.check(self._lib.fip_add_host_f32(self._handle(), x.ctypes.data, x.shape[0]))
 
+    def add_raw(self, x: np.ndarray, dtype: str) -> None:
+        """Host rows in their OWN storage width: ``x`` is float32 / float16 [n, d], or uint16 [n, d]
+        holding bf16 bit patterns (``dtype="bf16"``).  16-bit rows cross PCIe as 16 bits."""
+        _native.check(self._lib.fip_add_host(self._handle(), *raw_rows(x, dtype, self.d)))
+
     def add_device(self, ptr: int, n: int, dtype: str) -> None:
         _native.check(self._lib.fip_add_device(self._handle(), ctypes.c_void_p(ptr), int(n),
                                                _native.DTYPE_CODES[dtype]))
@@ -94,6 +99,23 @@ class FlatIPIndex:
             self._handle(), ctypes.c_void_p(q_ptr), int(nq), int(k), ctypes.c_void_p(d_ptr),
             ctypes.c_void_p(i_ptr), ctypes.c_void_p(stream)))
 
+    def search_device_async(self, q_ptr: int, nq: int, k: int, d_ptr: int, i_ptr: int,
+                            stream: int = 0) -> None:
+        """Enqueue only (no host round trip).  ``search_status()`` later tells whether any such
+        search must be redone with the blocking call; see include/flatip_b200.h."""
+        _native.check(self._lib.fip_search_device_async(
+            self._handle(), ctypes.c_void_p(q_ptr), int(nq), int(k), ctypes.c_void_p(d_ptr),
+            ctypes.c_void_p(i_ptr), ctypes.c_void_p(stream)))
+
+    def search_status(self) -> int:
+        """Synchronises; nonzero when some asynchronous search since the last call was flagged."""
+        flagged = ctypes.c_int32(0)
+        _native.check(self._lib.fip_search_status(self._handle(), ctypes.byref(flagged)))
+        return int(flagged.value)
+
+    def flags_device_ptr(self) -> int:
+        return int(self._lib.fip_search_flags_device(self._handle()) or 0)
+
     # -- knobs / counters --------------------------------------------------------------------
     def set_option(self, key: str, value: int) -> None:
         _native.check(self._lib.fip_set_option(self._handle(), key.encode(), int(value)))
@@ -106,6 +128,30 @@ class FlatIPIndex:
 
     def last_variant(self) -> str:
         return _native.VARIANT_NAMES.get(self.stat("variant"), "none")
+
+
+CUDA_STREAM_LEGACY = 1   # cudaStreamLegacy: explicit handle of the legacy default stream
+
+
+def torch_stream_handle(device=None) -> int:
+    """Handle of torch's current stream for the ``stream`` arguments of this package.  torch's
+    default stream has handle 0, which the C ABI reads as "the index's own stream"; naming the
+    legacy default stream explicitly keeps the search ordered with the caller's torch work."""
+    import torch
+
+    return torch.cuda.current_stream(device).cuda_stream or CUDA_STREAM_LEGACY
+
+
+def raw_rows(x: np.ndarray, dtype: str, dim: int):
+    """(pointer, n, dtype code) of host rows handed over in their own width."""
+    code = _native.DTYPE_CODES[dtype]
+    want = {0: np.float32, 1: np.float16, 2: np.uint16}[code]
+    x = np.ascontiguousarray(x)
+    if x.dtype != want:
+        raise ValueError(f"{dtype} rows must be {np.dtype(want).name} (bf16 as uint16 bit patterns), got {x.dtype}")
+    if x.ndim != 2 or x.shape[1] != dim:
+        raise ValueError(f"expected rows of shape (n, {dim}), got {x.shape}")
+    return x.ctypes.data, x.shape[0], code
 
 
 def merge_device(device: int, in_d_ptr: int, in_i_ptr: int, g: int, nq: int, k_in: int, k_out: int,

@@ -16,7 +16,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from .index import FlatIPIndex, merge_strided_device
+from .index import FlatIPIndex, merge_strided_device, torch_stream_handle
 
 
 def shard_range(total_rows: int, rank: int, world_size: int) -> tuple[int, int]:
@@ -62,6 +62,8 @@ class ShardedFlatIPSearcher:
             raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
         self.exchange_mode = exchange
         self._xchg = None
+        self._xchg_failed = False   # an attempt to map the peers' buffers failed: stay on NCCL
+        self._status = None         # device word: OR of every shard's search status (p2p path)
         self.exchange_used = "none"
         self.dim = int(dim)
         self.dtype = dtype
@@ -100,24 +102,36 @@ class ShardedFlatIPSearcher:
             raise ValueError("queries must be a 2-D float32 CUDA tensor")
         queries = queries.contiguous()
         B = queries.shape[0]
-        stream = torch.cuda.current_stream(queries.device).cuda_stream
+        stream = torch_stream_handle(queries.device)
         off_i, total = pack_layout(B, k)
         pack = torch.empty((total,), dtype=torch.uint8, device=queries.device)
         d_loc = pack[:B * k * 4].view(torch.float32).view(B, k)
         i_loc = pack[off_i:off_i + B * k * 8].view(torch.int64).view(B, k)
-        self.index.search_device(queries.data_ptr(), B, k, d_loc.data_ptr(), i_loc.data_ptr(),
-                                 stream)
-        if self.world_size == 1:
-            return d_loc, i_loc
-        xchg = self._ensure_exchange(B, k)
-        if xchg is not None:
+        xchg = self._ensure_exchange(B, k) if self.world_size > 1 else None
+        if self.world_size == 1 or xchg is not None:
+            # Nothing between the local search and its consumer needs the host: the search is only
+            # ENQUEUED, the K4 kernel ships every shard's status words with its rows, and check()
+            # (one synchronisation, whenever the caller wants the verdict) says whether a search
+            # since the last check has to be redone.  The GPU queue never drains between searches.
+            self.index.search_device_async(queries.data_ptr(), B, k, d_loc.data_ptr(),
+                                           i_loc.data_ptr(), stream)
+            if self.world_size == 1:
+                self._last = (d_loc, i_loc)
+                return d_loc, i_loc
+            if self._status is None:
+                self._status = torch.zeros((1,), dtype=torch.int32, device=queries.device)
             d_out = torch.empty((B, k), dtype=torch.float32, device=queries.device)
             i_out = torch.empty((B, k), dtype=torch.int64, device=queries.device)
-            xchg.merge(d_loc.data_ptr(), i_loc.data_ptr(), B, k, d_out.data_ptr(), i_out.data_ptr(),
-                       stream)
+            xchg.merge_status(d_loc.data_ptr(), i_loc.data_ptr(), B, k, d_out.data_ptr(),
+                              i_out.data_ptr(), self.index.flags_device_ptr(),
+                              self._status.data_ptr(), stream)
             pack.record_stream(torch.cuda.current_stream(queries.device))
             self.exchange_used = "p2p"
+            self._last = (d_out, i_out)
             return d_out, i_out
+        # NCCL exchange: the local search is the blocking, self-checking form
+        self.index.search_device(queries.data_ptr(), B, k, d_loc.data_ptr(), i_loc.data_ptr(),
+                                 stream)
         self.exchange_used = "nccl"
 
         def all_gather(t):
@@ -132,23 +146,63 @@ class ShardedFlatIPSearcher:
             i_out = torch.empty((B, k), dtype=torch.int64, device=queries.device)
             merge_strided_device(self.device, all_pack.data_ptr(), all_pack.data_ptr() + off,
                                  tot // 4, tot // 8, self.world_size, B, k, k,
-                                 d_out.data_ptr(), i_out.data_ptr(),
-                                 torch.cuda.current_stream(queries.device).cuda_stream)
+                                 d_out.data_ptr(), i_out.data_ptr(), stream)
             return d_out, i_out
 
         return gather_and_merge(pack, B, k, world_size=self.world_size, all_gather=all_gather,
                                 merge=merge)
 
+    # ------------------------------------------------------------------ deferred verdict
+    _last = None
+
+    def check(self) -> int:
+        """Synchronises this rank's device and returns the OR of the search statuses since the last
+        check (0 = every result stands; bit 0: some shard's candidate list overflowed, bit 1: some
+        query could not be certified exact).  On the p2p path the status is GLOBAL (every rank sees
+        the same value, it travelled with the rows), so every rank takes the same branch.  A
+        nonzero status means the searches since the last check must be redone with
+        ``search_tensor_checked`` -- ``search`` (the host-buffer path) does that itself."""
+        import torch
+
+        local = self.index.search_status()
+        status = local
+        if self._status is not None:
+            status |= int(self._status.item())
+            if status:
+                self._status.zero_()
+        elif self.world_size > 1:
+            torch.cuda.synchronize(self.device)
+        return status
+
+    def search_tensor_checked(self, queries, k: int):
+        """``search_tensor`` + ``check``; a flagged search is redone with the blocking local search
+        (which redoes the flagged queries on its own) and exchanged again.  Collective on p2p."""
+        d, i = self.search_tensor(queries, k)
+        if self.exchange_used == "nccl" or not self.check():
+            return d, i
+        import torch
+
+        B = queries.shape[0]
+        stream = torch_stream_handle(queries.device)
+        d_loc = torch.empty((B, k), dtype=torch.float32, device=queries.device)
+        i_loc = torch.empty((B, k), dtype=torch.int64, device=queries.device)
+        self.index.search_device(queries.data_ptr(), B, k, d_loc.data_ptr(), i_loc.data_ptr(), stream)
+        if self.world_size == 1:
+            return d_loc, i_loc
+        d_out = torch.empty_like(d_loc)
+        i_out = torch.empty_like(i_loc)
+        self._xchg.merge(d_loc.data_ptr(), i_loc.data_ptr(), B, k, d_out.data_ptr(), i_out.data_ptr(), stream)
+        torch.cuda.synchronize(self.device)
+        return d_out, i_out
+
     # ------------------------------------------------------------------ peer-memory exchange
     def _ensure_exchange(self, nq: int, k: int):
         """Collective: (re)creates the K4 exchange when this search does not fit the current one.
         Every rank sees the same (nq, k), so every rank takes the same branch."""
-        if self.exchange_mode == "nccl":
-            return None
+        if self.exchange_mode == "nccl" or self._xchg_failed:
+            return None                  # (an earlier attempt failed on some rank: stay on NCCL)
         if self._xchg is not None and self._xchg.fits(nq, k):
             return self._xchg
-        if self._xchg is False:          # an earlier attempt failed on some rank: stay on NCCL
-            return None
         import torch
         import torch.distributed as dist
 
@@ -181,12 +235,15 @@ class ShardedFlatIPSearcher:
                 x.connect_ipc(handles)
             except Exception as e:  # noqa: BLE001
                 err = f"{type(e).__name__}: {e}"
-        ok = torch.tensor([0 if err else 1], dtype=torch.int32, device=torch.device("cuda", self.device))
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
-        if int(ok.item()) == 0:
+        # agreement on the host (one-time set-up, no device work): everybody learns whether every
+        # rank could map every peer
+        oks = [None] * self.world_size
+        dist.all_gather_object(oks, not err, group=self.group)
+        if not all(oks):
             if x is not None:
                 x.close()
-            self._xchg = False
+            self._xchg = None
+            self._xchg_failed = True
             if self.exchange_mode == "p2p":
                 raise RuntimeError(f"peer-memory exchange unavailable on rank {self.rank}: {err or 'a peer failed'}")
             return None
@@ -200,11 +257,11 @@ class ShardedFlatIPSearcher:
 
         dev = torch.device("cuda", self.device)
         q = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float32)).to(dev)
-        d, i = self.search_tensor(q, k)
+        d, i = self.search_tensor_checked(q, k)
         return d.cpu().numpy(), i.cpu().numpy()
 
     def close(self) -> None:
-        if self._xchg:
+        if self._xchg is not None:
             import torch
             import torch.distributed as dist
 

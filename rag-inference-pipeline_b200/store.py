@@ -16,6 +16,12 @@ It is looked up by the retrieval service under the registry name ``faiss_store``
     it is served by the IVF-Flat operator (``ivf.py``) with ``nprobe = settings.faiss_nprobe``,
   * a FIPB corpus file written by ``index_io.write_fipb`` (fp32 / fp16 / bf16 rows), or
   * ``synthetic:<rows>[?dim=..&dtype=..&seed=..]`` -- a Philox corpus generated on the device.
+
+Multi-GPU: ``config["devices"] = [0, 1, ...]`` (or ``FLATIP_B200_DEVICES=0,1,...`` / ``all``)
+row-shards the corpus over those GPUs INSIDE this one component (``FlatIPGroup``, C ABI
+``fip_group_*``): the reference's single call site ``registry.get("faiss_store").search(...)``
+(``api.py:383-389``) then runs one host thread + stream per device, the K4 exchange + merge over
+NVLink and returns the global ``(distances, indices)`` -- nothing changes for the caller.
 """
 
 from __future__ import annotations
@@ -30,7 +36,8 @@ from urllib.parse import parse_qs
 import numpy as np
 
 from . import index_io
-from .index import FlatIPIndex
+from .group import FlatIPGroup
+from .index import FlatIPIndex, torch_stream_handle
 from .synthetic import CORPUS_SEED
 
 logger = logging.getLogger(__name__)
@@ -38,8 +45,23 @@ logger = logging.getLogger(__name__)
 _UPLOAD_CHUNK_BYTES = 256 << 20
 
 
+def _parse_devices(spec) -> list[int] | None:
+    """None / "" -> single device; "all" -> every visible GPU; "0,1,2" or a list -> those."""
+    if spec is None or spec == "":
+        return None
+    if isinstance(spec, str):
+        if spec.strip().lower() == "all":
+            import torch  # only to count devices
+
+            return list(range(torch.cuda.device_count()))
+        spec = [p for p in spec.replace(" ", "").split(",") if p]
+    devs = [int(d) for d in spec]
+    return devs or None
+
+
 class B200FlatIPStore:
-    """Exact flat inner-product store on one B200 (same surface as the reference FAISSStore)."""
+    """Exact flat inner-product store on one or several B200s of this process (same surface as the
+    reference FAISSStore)."""
 
     def __init__(self, settings, config: dict | None = None) -> None:
         config = dict(config or {})
@@ -50,6 +72,10 @@ class B200FlatIPStore:
         self._is_loaded = False
         self._lock = threading.Lock()
         self.device = int(config.get("device", os.environ.get("FLATIP_B200_DEVICE", 0)))
+        # several devices = one corpus row-sharded over them behind this one component
+        self.devices = _parse_devices(config.get("devices", os.environ.get("FLATIP_B200_DEVICES")))
+        if self.devices:
+            self.device = self.devices[0]
         # None = keep the dtype the file holds (fp32 for faiss files, like the reference).
         self.storage_dtype = config.get("storage_dtype", os.environ.get("FLATIP_B200_DTYPE"))
         self.id_base = int(config.get("id_base", 0))
@@ -60,7 +86,12 @@ class B200FlatIPStore:
                                ).lower() not in ("0", "false", "no")
 
     # ------------------------------------------------------------------------------- load
-    def _load_synthetic(self) -> FlatIPIndex:
+    def _new_index(self, dim: int, dtype: str, nrows: int, id_base: int):
+        if self.devices and len(self.devices) > 1:
+            return FlatIPGroup(dim, dtype, self.devices, nrows, id_base=id_base)
+        return FlatIPIndex(dim, dtype, self.device, id_base=id_base, capacity_rows=nrows)
+
+    def _load_synthetic(self):
         spec = self._raw_path[len("synthetic:"):]
         rows_s, _, query = spec.partition("?")
         opts = {k: v[0] for k, v in parse_qs(query).items()}
@@ -69,7 +100,7 @@ class B200FlatIPStore:
         seed = int(opts.get("seed", CORPUS_SEED))
         row0 = int(opts.get("row0", self.id_base))
         nrows = int(float(rows_s))
-        index = FlatIPIndex(dim, dtype, self.device, id_base=row0, capacity_rows=nrows)
+        index = self._new_index(dim, dtype, nrows, row0)
         index.add_synthetic(nrows, seed, row0)
         return index
 
@@ -103,14 +134,22 @@ class B200FlatIPStore:
                              f"{info.metric.upper()} index)")
         dtype = self.storage_dtype or info.dtype
         rows = index_io.open_rows(str(self.index_path), info)
-        index = FlatIPIndex(info.dim, dtype, self.device, id_base=info.id_base + self.id_base,
-                            capacity_rows=info.ntotal)
-        step = max(1, _UPLOAD_CHUNK_BYTES // (info.dim * 4))
+        index = self._new_index(info.dim, dtype, info.ntotal, info.id_base + self.id_base)
+        # Rows go to the device(s) in the width the file holds: a 16-bit corpus crosses PCIe as 16
+        # bits (no fp32 widening on the host), each device pulling its own slice of the mapped file
+        # through its own pinned, double-buffered staging (fip_add_host / fip_group_add_host).
+        esize = 4 if info.dtype == "f32" else 2
+        same_width = info.dtype == dtype or "f32" in (info.dtype, dtype)
+        ndev = len(self.devices) if self.devices and len(self.devices) > 1 else 1
+        step = max(1, ndev * _UPLOAD_CHUNK_BYTES // (info.dim * esize))
         for r0 in range(0, info.ntotal, step):
             chunk = rows[r0:r0 + step]
-            if info.dtype == "bf16":
-                chunk = (np.asarray(chunk).astype(np.uint32) << np.uint32(16)).view(np.float32)
-            index.add(np.asarray(chunk, dtype=np.float32))
+            if same_width:
+                index.add_raw(chunk, info.dtype)
+            else:   # fp16 file into a bf16 index or vice versa: through fp32
+                if info.dtype == "bf16":
+                    chunk = (np.asarray(chunk).astype(np.uint32) << np.uint32(16)).view(np.float32)
+                index.add(np.asarray(chunk, dtype=np.float32))
         return index
 
     def load(self) -> None:
@@ -139,7 +178,9 @@ class B200FlatIPStore:
             self._index = index
             self._is_loaded = True
             logger.info("FAISS index loaded successfully: %d vectors, dimension=%d (B200 %s, "
-                        "device %d)", index.ntotal, index.d, index.dtype, self.device)
+                        "device%s %s)", index.ntotal, index.d, index.dtype,
+                        "s" if isinstance(index, FlatIPGroup) else "",
+                        self.devices if isinstance(index, FlatIPGroup) else self.device)
             if index.ntotal > 0:
                 logger.info("Warming up FAISS index...")
                 index.search(np.zeros((1, index.d), dtype=np.float32), 1)
@@ -205,6 +246,10 @@ class B200FlatIPStore:
         if not embeddings.is_cuda or embeddings.device.index != self.device:
             msg = f"search_device needs a CUDA tensor on device {self.device}"
             raise ValueError(msg)
+        if isinstance(self._index, FlatIPGroup):
+            # several devices: the queries have to reach every GPU anyway -- go through the host path
+            d, i = self._index.search(embeddings.to(torch.float32).cpu().numpy(), int(k))
+            return torch.from_numpy(d).to(embeddings.device), torch.from_numpy(i).to(embeddings.device)
         q = embeddings.to(torch.float32).contiguous()
         batch = q.shape[0]
         distances = torch.empty((batch, int(k)), dtype=torch.float32, device=q.device)
@@ -214,7 +259,7 @@ class B200FlatIPStore:
         try:
             self._index.search_device(q.data_ptr(), batch, int(k), distances.data_ptr(),
                                       indices.data_ptr(),
-                                      torch.cuda.current_stream(q.device).cuda_stream)
+                                      torch_stream_handle(q.device))
         except Exception:
             logger.exception("FAISS search failed")
             raise
@@ -241,7 +286,7 @@ class B200FlatIPStore:
         return int(self._index.ntotal)
 
     @property
-    def native_index(self) -> FlatIPIndex | None:
+    def native_index(self):
         return self._index
 
     def __repr__(self) -> str:

@@ -41,7 +41,8 @@ def main():
         idx.set_option(key, int(val))
     idx.set_option("profile_events", 1)
     es = 4 if args.dtype == "f32" else 2
-    s = torch.cuda.current_stream().cuda_stream
+    from rag_inference_pipeline_b200.index import torch_stream_handle
+    s = torch_stream_handle()
     for B in (int(b) for b in args.batches.split(",")):
         q = torch.from_numpy(synthetic_queries(B, args.dim)).cuda()
         D = torch.empty((B, args.k), dtype=torch.float32, device="cuda")

@@ -169,3 +169,19 @@ def test_feed_matches_reference_document_store(tmp_path):
     res = json.loads(out.stdout.strip().splitlines()[-1])
     assert res["ok"], res
     assert res["queries"] == 300 and res["selects_feed"] == 1
+
+
+def test_truncate_length_zero_and_no_aliasing(tmp_path):
+    """Reference semantics (document_store.py:297-298): truncate_length=0 empties every field
+    (`is not None` test), None leaves the text alone; documents are not shared between queries."""
+    db = make_db(tmp_path, 50)
+    feed = CandidateFeed(db_path=db / "documents.db", truncate_length=None)
+    ids = [[1, 2, 3], [3, 2, 7]]
+    empty = feed.fetch_documents_batch(ids, truncate_length=0)
+    assert all(d.title == "" and d.content == "" for row in empty for d in row)
+    full = feed.fetch_documents_batch(ids, truncate_length=None)
+    assert all(len(d.content) > 0 for row in full for d in row)
+    assert full[0][2] == full[1][0] and full[0][2] is not full[1][0]
+    full[0][2].title = "mutated"
+    assert full[1][0].title != "mutated"
+    assert feed.fetch_documents([3])[0].title != "mutated"

@@ -184,6 +184,27 @@ def test_ivf_crowded_tf32_window_falls_back_to_fp32_filter():
     index.close()
 
 
+def test_ivf_duplicate_cluster_larger_than_the_window():
+    """more than 2k + 64 EXACT duplicates of one row crowd even the fp32 window.  The
+    batch must then be redone with the wide window (not silently truncated by approximate score):
+    the k results of a query sitting on the cluster are the k lowest ids of the duplicates."""
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    rng = np.random.default_rng(5)
+    n, d, k = 20000, 64, 10
+    x = (3.0 * rng.standard_normal((n, d))).astype(np.float32)
+    dup = np.sort(rng.choice(n, size=300, replace=False))      # 300 > 2k + 64 = 84
+    x[dup] = x[dup[0]]
+    q = np.concatenate([x[dup[:1]], x[rng.integers(0, n, 15)] + 0.5 * rng.standard_normal((15, d)).astype(np.float32)])
+    index = IVFFlatL2Index(d, 16)
+    index.train(x[:3000])
+    index.add(x)
+    D, I = _check(index, q.astype(np.float32), k, 4)
+    assert index.stat("crowded_window") == 1 and index.stat("crowded_window_unresolved") == 0
+    assert I[0].tolist() == dup[:k].tolist() and np.all(np.abs(D[0]) < 1e-3)
+    index.close()
+
+
 @pytest.mark.parametrize("n,d,nlist,nq,k,nprobe,tc_min,qb", [
     (30000, 128, 256, 200, 10, 64, 8, 16),     # tensor items + small FFMA2 tiles
     (30000, 128, 256, 200, 10, 64, 0, 16),     # FFMA2 only: 16-query tiles with remainders

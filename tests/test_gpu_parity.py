@@ -721,7 +721,15 @@ def _check_full(D, I, Dr, Ir, k):
                                             kplus1_ref=Dr[:, k])
     assert res["score_ok"], res
     assert res["id_mismatch_outside_window"] == 0, res
-    assert res["id_mismatch_total"] <= max(2, I.size // 2000), res
+    # Both sides sum exact products in fp32 in different orders, so neighbours closer than ~1e-6
+    # may swap (0.2 % of the positions at k = 1024 of 1e7 rows).  Swaps must stay swaps: wherever
+    # the k-th and (k+1)-th oracle scores are clearly apart, the two id SETS of a row are equal.
+    assert res["id_mismatch_total"] <= max(2, I.size // 200), res
+    tol = FULL_RTOL * np.maximum(1.0, np.abs(Dr[:, k - 1].astype(np.float64)))
+    clear = (Dr[:, k - 1].astype(np.float64) - Dr[:, k].astype(np.float64)) > 2 * tol
+    assert clear.mean() > 0.9
+    for r in np.nonzero(clear)[0]:
+        assert set(I[r].tolist()) == set(Ir[r, :k].tolist()), r
     assert np.all(np.diff(D, axis=1) <= 0)
     return res
 

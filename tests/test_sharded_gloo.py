@@ -99,3 +99,61 @@ def test_two_rank_gather_and_merge(tmp_path):
         got = np.load(tmp_path / f"rank{rank}.npz")
         assert np.array_equal(got["I"], Ir)      # every rank holds the global answer
         assert np.array_equal(got["D"], Dr)
+
+
+def _xchg_fail_worker(rank, world, port, out_dir):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    from rag_inference_pipeline_b200 import exchange as exchange_mod
+    from rag_inference_pipeline_b200.sharded import ShardedFlatIPSearcher
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    attempts = []
+
+    class Boom:
+        def __init__(self, *a, **kw):
+            attempts.append(1)
+            if rank == 1:   # only ONE rank fails: the others must follow it onto NCCL
+                raise RuntimeError("no peer mapping on this box")
+
+        def ipc_handle(self):
+            return b"\x01" * 64
+
+        def connect_ipc(self, handles):
+            pass
+
+        def close(self):
+            pass
+
+    exchange_mod.PeerExchange = Boom
+    s = object.__new__(ShardedFlatIPSearcher)   # no GPU here: only the exchange set-up is under test
+    s.exchange_mode, s._xchg, s._xchg_failed, s._status = "auto", None, False, None
+    s.device, s.world_size, s.rank, s.group = 0, world, rank, None
+    first = s._ensure_exchange(8, 10)
+    second = s._ensure_exchange(8, 10)     # used to raise AttributeError ('bool' has no 'fits')
+    third = s._ensure_exchange(4096, 100)
+    ok = first is None and second is None and third is None and len(attempts) == 1 and s._xchg_failed
+    s2 = object.__new__(ShardedFlatIPSearcher)
+    s2.exchange_mode, s2._xchg, s2._xchg_failed, s2._status = "p2p", None, False, None
+    s2.device, s2.world_size, s2.rank, s2.group = 0, world, rank, None
+    try:
+        s2._ensure_exchange(8, 10)
+        ok = False                         # an explicit "p2p" request must fail loudly
+    except RuntimeError as e:
+        ok = ok and "peer-memory exchange unavailable" in str(e)
+    with open(os.path.join(out_dir, f"ok{rank}"), "w") as f:
+        f.write("1" if ok else "0")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_failed_peer_mapping_falls_back_to_nccl_for_good(tmp_path):
+    """after a failed peer-memory attempt in exchange="auto" every later search must stay
+    on NCCL (no second attempt, no crash), on EVERY rank, also when only one rank failed."""
+    world = 2
+    mp.spawn(_xchg_fail_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for rank in range(world):
+        assert (tmp_path / f"ok{rank}").read_text() == "1"
