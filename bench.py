@@ -275,10 +275,27 @@ def run_b200(args, rank, local_rank, world):
             dist.barrier()
         torch.cuda.synchronize()
 
-    searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=rank, world_size=world,
-                                     device=local_rank, exchange=args.exchange)
+    # The component a user of the reference talks to: registry.get("faiss_store").search(...)
+    # (api.py:383-389).  One GPU: the store is built first and the device-resident timing loop
+    # drives the very index it holds.  N GPUs (torchrun): the timing loop runs one rank per GPU;
+    # the end-to-end leg afterwards runs the store in ONE process over all N devices.
+    import types as _types
+
+    from rag_inference_pipeline_b200 import B200FlatIPStore
+    store_settings = _types.SimpleNamespace(
+        faiss_index_path=f"synthetic:{total_rows}?dim={dim}&dtype={dtype}&seed={CORPUS_SEED}", faiss_dim=dim)
+    gloo = dist.new_group(backend="gloo") if world > 1 else None   # host-only barriers for the e2e leg
     t0 = time.time()
-    searcher.load_synthetic(CORPUS_SEED)
+    store = None
+    if world == 1:
+        store = B200FlatIPStore(store_settings, {"device": local_rank})
+        store.load()
+        searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=0, world_size=1, device=local_rank,
+                                         index=store.native_index)
+    else:
+        searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=rank, world_size=world,
+                                         device=local_rank, exchange=args.exchange)
+        searcher.load_synthetic(CORPUS_SEED)
     load_s = time.time() - t0
     if args.variant != "auto":
         searcher.index.set_variant(args.variant)
@@ -327,30 +344,11 @@ def run_b200(args, rank, local_rank, world):
             break
         per_scan[i] = [searcher.index.stat(f"scan_rows_{i}"), ns, searches_timed]
 
-    # ---- end-to-end timing through the host-buffer API ("e2e"): pinned host queries -> H2D ->
-    #      search -> D2H of distances + ids, every step ----
-    def e2e_step():
-        if world == 1:
-            return searcher.index.search(q_np, k)  # fip_search: pinned staging inside the C ABI
-        qd = q_pinned.to(dev, non_blocking=True)
-        d, i = searcher.search_tensor_checked(qd, k)
-        return d.cpu(), i.cpu()
-
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        De, Ie = e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-
-    tms = torch.tensor([ms, e2e_s * 1e3, float(scan_ns)], dtype=torch.float64, device=dev)
+    tms = torch.tensor([ms, float(scan_ns)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms_max, e2e_ms_max, scan_ns_max = (float(v) for v in tms.tolist())
+    ms_max, scan_ns_max = (float(v) for v in tms.tolist())
     variant = searcher.index.last_variant()
-    phases = searcher.index.stat("phases")
-    overflow = searcher.index.stat("overflow_queries")
 
     # ---- verification of the result the timed loop produced (rank 0 holds the GLOBAL result):
     #   * rows best-first, ids in range and distinct per row;
@@ -403,6 +401,55 @@ def run_b200(args, rank, local_rank, world):
                   "ok": bool(ok_sorted and ok_range and ok_distinct and missed == 0
                              and max(errs) <= 10 * tol)}
 
+    # ---- end-to-end ("e2e"): the same metric through the component's public call,
+    #      B200FlatIPStore.search(numpy queries, k) -> numpy (distances, ids): host buffers, H2D and
+    #      D2H inside the timed region, every step.  N > 1: the torchrun ranks release their shards,
+    #      rank 0 loads the corpus into ONE store over all N devices (fip_group: a host thread +
+    #      stream per device, K4 exchange + merge) and times it alone; the others wait on a
+    #      host-side (gloo) barrier so that no NCCL kernel occupies an SM meanwhile.
+    st = {"variant": searcher.index.last_variant(), "phases": searcher.index.stat("phases"),
+          "overflow": searcher.index.stat("overflow_queries"),
+          "uncertified": searcher.index.stat("uncertified_queries"),
+          "cta_group": searcher.index.stat("cta_group"),
+          "deferred": searcher.index.stat("deferred_epilogue"),
+          "filter_f16": searcher.index.stat("filter_f16"), "local_rows": searcher.local_rows,
+          "exchange": searcher.exchange_used}
+    e2e = None
+    if world > 1:
+        searcher.close()
+        searcher = None
+        torch.cuda.empty_cache()
+        dist.barrier(group=gloo)
+        if rank == 0:
+            store = B200FlatIPStore(store_settings, {"devices": list(range(world))})
+            store.load()
+    if rank == 0:
+        for kv in args.opt:
+            key, val = kv.split("=")
+            store.native_index.set_option(key, int(val))
+        if args.variant != "auto":
+            store.native_index.set_variant(args.variant)
+        for _ in range(2):
+            De, Ie = store.search(q_np, k)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            De, Ie = store.search(q_np, k)
+        e2e_s = time.perf_counter() - t0
+        e2e = {"value": batch / (e2e_s / args.steps), "unit": UNIT,
+               "h2d_bytes_per_step": batch * dim * 4 * world, "d2h_bytes_per_step": batch * k * 12,
+               "api": ("B200FlatIPStore.search (fip_search, host buffers)" if world == 1 else
+                       f"B200FlatIPStore.search, devices 0..{world - 1} in ONE process (fip_group_search: "
+                       "per-device H2D of the queries, local search, K4 exchange + merge, D2H from device 0)"),
+               "ms_per_step": e2e_s / args.steps * 1e3,
+               "result_equals_device_loop": bool(np.array_equal(Ie, I.cpu().numpy())
+                                                 and np.array_equal(De, D.cpu().numpy()))}
+        if world > 1:
+            e2e["flagged_searches"] = store.native_index.stat("flagged_searches")
+            store.unload()
+            store = None
+    if world > 1:
+        dist.barrier(group=gloo)
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         r = cpu_oracle_qps(total_rows, dim, dtype, batch, k, step_budget_s=10.0)
@@ -411,9 +458,9 @@ def run_b200(args, rank, local_rank, world):
     if rank == 0:
         peaks = load_peaks()
         ms_per_step = ms_max / args.steps
-        n_local = searcher.local_rows  # rank 0's shard (the largest)
+        n_local = st["local_rows"]  # rank 0's shard (the largest)
         esize = 4 if dtype == "f32" else 2
-        if dtype == "f32" and searcher.index.stat("filter_f16") == 1:
+        if dtype == "f32" and st["filter_f16"] == 1:
             esize = 2   # the tensor-core scan reads the fp16 FILTER COPY of the fp32 corpus
         scan_s = scan_ns_max * 1e-9
         scans = max(1, scan_launches)
@@ -462,27 +509,25 @@ def run_b200(args, rank, local_rank, world):
             "vs_baseline": None, "dtype": {"f16": "f16", "bf16": "bf16", "f32": "f32"}[dtype],
             "data": "synthetic", "config": workload_config(args, world),
             "clocks": clocks,
-            "e2e": {"value": batch / (e2e_ms_max * 1e-3 / args.steps), "unit": UNIT,
-                    "h2d_bytes_per_step": batch * dim * 4, "d2h_bytes_per_step": batch * k * 12,
-                    "api": "FlatIPIndex.search (fip_search, host buffers)" if world == 1 else
-                           "ShardedFlatIPSearcher.search_tensor + pinned H2D / D2H"},
+            "e2e": e2e,
             "gpu_launches": launches,
             "roofline": roof,
             "cpu_baseline": cpu_baseline,
-            "variant": variant, "phases_per_search": phases, "overflow_queries": overflow,
-            "uncertified_queries": searcher.index.stat("uncertified_queries"),
-            "cta_group": searcher.index.stat("cta_group"),
-            "deferred_epilogue": searcher.index.stat("deferred_epilogue"), "options": args.opt,
-            "exchange": searcher.exchange_used,
+            "variant": variant, "phases_per_search": st["phases"], "overflow_queries": st["overflow"],
+            "uncertified_queries": st["uncertified"], "cta_group": st["cta_group"],
+            "deferred_epilogue": st["deferred"], "options": args.opt, "exchange": st["exchange"],
             "corpus_load_s": load_s, "verify": verify,
         }
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         print(json.dumps(line), flush=True)
         os.dup2(2, 1)
-    searcher.close()
+    if store is not None:
+        store.unload()
+    elif searcher is not None:
+        searcher.close()
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=gloo)
         dist.destroy_process_group()
 
 

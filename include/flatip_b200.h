@@ -201,7 +201,12 @@ int64_t fip_group_get_stat(const fip_group* g, const char* key);
  * histogram, so one launch covers the shard; 0: thresholds move only between geometric phases),
  * "coalesce" (1 default / 0) and "coalesce_max_batch" (default 4096): fip_search calls that arrive
  * from other threads while a search is running are queued and served together as ONE batch, "profile_events" (0/1: time every scan launch with CUDA events),
- * "force_safe_mode" (0/1, testing the overflow fallback). */
+ * "force_safe_mode" (0/1, testing the overflow fallback), "defer_epilogue" (0 auto: k >= 256 / 1 off /
+ * 2 on: the tensor-core scan releases an accumulator right after the filter pass and writes the
+ * survivors out from a shared-memory staging area afterwards, csrc/tc_scan.cuh), "dedupe" (1 default:
+ * bit-identical queries inside a COALESCED host batch are searched once, on the device; 2: in every
+ * host batch; 0: off), "debug_counts" (0/1: read the candidate-list lengths back after every filter
+ * launch -> stats "list_entries_after_filter" / "list_max_after_filter"). */
 int fip_set_option(fip_index* idx, const char* key, int64_t value);
 /* Counters of the last search: "launches", "variant", "phases", "overflow_queries",
  * "uncertified_queries" (queries the tensor-core filter could not certify exact and that were redone
@@ -215,7 +220,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value);
  * "gap_ns_<i>" (summed over those searches per scan launch index i: device time, time to the next
  * scan) and "scan_rows_<i>" (corpus rows of launch i); cumulative: "total_launches", "total_searches",
  * "host_calls" / "host_batches" (fip_search calls and the batches they were served in),
- * "coalesced_calls" (calls that shared a batch with another call); "last_batch_calls". */
+ * "coalesced_calls" (calls that shared a batch with another call); "last_batch_calls";
+ * "host_queries" / "distinct_queries" (queries received by fip_search and how many were actually
+ * searched after duplicate elimination); "deferred_epilogue" (1: the last search used it). */
 int64_t fip_get_stat(const fip_index* idx, const char* key);
 
 const char* fip_last_error(void);

@@ -20,6 +20,7 @@
 
 #include "../../include/flatip_b200.h"
 #include "common.cuh"
+#include "dedupe.cuh"
 #include "exchange.cuh"
 #include "select.cuh"
 #include "stream_scan.cuh"
@@ -289,6 +290,14 @@ struct fip_index {
     PinnedBuf<float> h_q, h_d;
     PinnedBuf<int64_t> h_i;
     PinnedBuf<uint32_t> h_flags;
+    // in-batch duplicate elimination (dedupe.cuh): 0 = off, 1 = coalesced batches (default), 2 = every
+    // host batch
+    int dedupe = 1;
+    DevBuf<uint64_t> dd_hash;
+    DevBuf<int> dd_rep, dd_pos, dd_sel, dd_map, dd_count;
+    PinnedBuf<int> h_dd_count;
+    DevBuf<float> dd_q, dd_d;
+    DevBuf<int64_t> dd_i;
     DevBuf<float> add_stage;
     PinnedBuf<uint8_t> h_add[2];   // fip_add_host: double-buffered pinned staging
 
@@ -1065,6 +1074,8 @@ void fip_destroy(fip_index* idx) {
     idx->out_i.release(); idx->sel.release(); idx->sub_q.release(); idx->sub_d.release();
     idx->sub_i.release(); idx->h_q.release(); idx->h_d.release(); idx->h_i.release();
     idx->h_flags.release(); idx->add_stage.release(); idx->h_add[0].release(); idx->h_add[1].release();
+    idx->dd_hash.release(); idx->dd_rep.release(); idx->dd_pos.release(); idx->dd_sel.release(); idx->dd_map.release();
+    idx->dd_count.release(); idx->h_dd_count.release(); idx->dd_q.release(); idx->dd_d.release(); idx->dd_i.release();
     for (auto& e : idx->ev) cudaEventDestroy(e);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
@@ -1268,6 +1279,44 @@ int32_t fip_dtype_of(const fip_index* idx) { return idx ? idx->cfg.dtype : -1; }
 
 // One host-buffer search over the concatenation of `batch` (all with the same k): pinned staging,
 // H2D, search, D2H, scatter back to every caller's buffers.
+// Duplicate elimination of a device-resident query batch (dedupe.cuh).  Enqueues the kernels, reads
+// the number of distinct rows back (one synchronisation) and, if there are duplicates, gathers the
+// distinct rows into idx->dd_q: *nd < nq then, and idx->dd_map maps every row to its representative.
+static int dedupe_queries(fip_index* idx, const float* q32, int nq, cudaStream_t stream, int* nd) {
+    *nd = nq;
+    if (nq < 2) return FIP_OK;
+    const int dim = idx->cfg.dim;
+    FIP_CUDA(idx->dd_hash.ensure(nq));
+    FIP_CUDA(idx->dd_rep.ensure(nq));
+    FIP_CUDA(idx->dd_pos.ensure(nq));
+    FIP_CUDA(idx->dd_sel.ensure(nq));
+    FIP_CUDA(idx->dd_map.ensure(nq));
+    FIP_CUDA(idx->dd_count.ensure(1));
+    FIP_CUDA(idx->h_dd_count.ensure(1));
+    const unsigned grid = (unsigned)((nq + 7) / 8);
+    query_hash_kernel<<<grid, 256, 0, stream>>>(q32, nq, dim, idx->dd_hash.p);
+    query_rep_kernel<<<grid, 256, 0, stream>>>(q32, idx->dd_hash.p, nq, dim, idx->dd_rep.p);
+    query_compact_kernel<<<1, 1024, 0, stream>>>(idx->dd_rep.p, nq, idx->dd_pos.p, idx->dd_sel.p, idx->dd_map.p,
+                                                 idx->dd_count.p);
+    FIP_CUDA(cudaGetLastError());
+    FIP_CUDA(cudaMemcpyAsync(idx->h_dd_count.p, idx->dd_count.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    FIP_CUDA(cudaStreamSynchronize(stream));
+    *nd = idx->h_dd_count.p[0];
+    if (*nd >= nq) { *nd = nq; return FIP_OK; }
+    FIP_CUDA(idx->dd_q.ensure((size_t)*nd * dim));
+    const int64_t tot = (int64_t)*nd * dim;
+    gather_rows_f32_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(q32, idx->dd_sel.p, idx->dd_q.p, *nd, dim);
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+static int expand_results(fip_index* idx, const float* sd, const int64_t* si, float* dd, int64_t* di, int nq,
+                          int k, cudaStream_t stream) {
+    const int64_t tot = (int64_t)nq * k;
+    expand_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(sd, si, idx->dd_map.p, dd, di, nq, k);
+    FIP_CUDA(cudaGetLastError());
+    return FIP_OK;
+}
+
 static int run_host_batch(fip_index* idx, const std::vector<HostRequest*>& batch) {
     std::lock_guard<std::mutex> lock(idx->mu);
     int rc = use_device(idx);
@@ -1289,14 +1338,31 @@ static int run_host_batch(fip_index* idx, const std::vector<HostRequest*>& batch
         off += (size_t)b->nq;
     }
     FIP_CUDA(cudaMemcpyAsync(idx->q32.p, idx->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, idx->stream));
+    // bit-identical queries (of different callers, mostly) are searched once
+    int nd = (int)nq;
+    if (idx->dedupe == 2 || (idx->dedupe == 1 && batch.size() > 1)) {
+        rc = dedupe_queries(idx, idx->q32.p, (int)nq, idx->stream, &nd);
+        if (rc) return rc;
+    }
+    const bool dup = nd < (int)nq;
+    idx->co.st_queries += nq; idx->co.st_distinct += nd;
+    const float* q_use = dup ? idx->dd_q.p : idx->q32.p;
+    float* d_use = idx->out_d.p;
+    int64_t* i_use = idx->out_i.p;
+    if (dup) {
+        FIP_CUDA(idx->dd_d.ensure((size_t)nd * k));
+        FIP_CUDA(idx->dd_i.ensure((size_t)nd * k));
+        d_use = idx->dd_d.p; i_use = idx->dd_i.p;
+    }
     // results and flags come back together: one synchronisation per search; only a flagged search
     // (rare: overflow / uncertified queries) is finished on the host and copied again
-    rc = search_enqueue(idx, idx->q32.p, (int)nq, k, idx->out_d.p, idx->out_i.p, idx->stream);
+    rc = search_enqueue(idx, q_use, nd, k, d_use, i_use, idx->stream);
     if (rc) return rc;
     for (int pass = 0; pass < 2; ++pass) {
+        if (dup) { rc = expand_results(idx, d_use, i_use, idx->out_d.p, idx->out_i.p, (int)nq, k, idx->stream); if (rc) return rc; }
         FIP_CUDA(cudaMemcpyAsync(idx->h_d.p, idx->out_d.p, on * sizeof(float), cudaMemcpyDeviceToHost, idx->stream));
         FIP_CUDA(cudaMemcpyAsync(idx->h_i.p, idx->out_i.p, on * sizeof(int64_t), cudaMemcpyDeviceToHost, idx->stream));
-        if (pass == 0) { rc = copy_flags_async(idx, idx->stream, (int)nq); if (rc) return rc; }
+        if (pass == 0) { rc = copy_flags_async(idx, idx->stream, nd); if (rc) return rc; }
         FIP_CUDA(cudaStreamSynchronize(idx->stream));
         if (pass == 1) break;
         int redone = 0;
@@ -1584,6 +1650,9 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         }
     } else if (k == "profile_events") {
         idx->profile = value != 0;
+    } else if (k == "dedupe") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "dedupe must be 0 (off), 1 (coalesced batches) or 2 (always)");
+        idx->dedupe = (int)value;
     } else if (k == "defer_epilogue") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "defer_epilogue must be 0 (auto), 1 (off) or 2 (on)");
         idx->defer_epilogue = (int)value;

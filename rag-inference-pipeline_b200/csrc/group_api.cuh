@@ -34,8 +34,9 @@ struct fip_group {
 
     struct Rank {
         cudaStream_t stream = nullptr;
-        DevBuf<float> q32, loc_d, out_d;
-        DevBuf<int64_t> loc_i, out_i;
+        DevBuf<float> q32, loc_d, out_d, fin_d;
+        DevBuf<int64_t> loc_i, out_i, fin_i;
+        int nd = 0;                       // distinct queries of the current search (dedupe.cuh)
         DevBuf<uint32_t> status;          // [1] merged status of the exchange (device)
         PinnedBuf<uint32_t> h_status;     // [1]
         int rc = 0;
@@ -56,6 +57,7 @@ struct fip_group {
 
     std::mutex mu;      // serialises group operations
     Coalescer co;
+    int dedupe = 1;     // 0 off, 1 coalesced batches, 2 always (every rank dedupes its own copy of the batch)
     int64_t st_flagged_searches = 0, st_exchange_launches = 0, st_searches = 0;
 };
 
@@ -148,7 +150,7 @@ int group_ensure_exchange(fip_group* g, int nq, int k) {
 // is repeated after flagged queries were redone on the host.  stage: 0 = everything; 1 = local
 // search only, synchronised; 2 = exchange onwards (1 then 2 = the shared-device test configuration,
 // where a spinning exchange kernel must not hold the SMs another shard's search still needs).
-int group_rank_search(fip_group* g, int r, int nq, int k, bool second, int stage = 0) {
+int group_rank_search(fip_group* g, int r, int nq, int k, bool second, bool dedupe, int stage = 0) {
     fip_index* idx = g->shard[r];
     fip_group::Rank& R = g->ranks[r];
     std::lock_guard<std::mutex> lock(idx->mu);
@@ -165,11 +167,18 @@ int group_rank_search(fip_group* g, int r, int nq, int k, bool second, int stage
         FIP_CUDA(R.status.ensure(1));
         FIP_CUDA(R.h_status.ensure(1));
         FIP_CUDA(cudaMemcpyAsync(R.q32.p, g->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, R.stream));
-        int rc = search_enqueue(idx, R.q32.p, nq, k, R.loc_d.p, R.loc_i.p, R.stream);
+        // bit-identical queries are searched once: every rank reduces its own copy of the batch
+        // (same deterministic result everywhere, nothing to communicate)
+        R.nd = nq;
+        if (dedupe) {
+            int rc = dedupe_queries(idx, R.q32.p, nq, R.stream, &R.nd);
+            if (rc) return rc;
+        }
+        int rc = search_enqueue(idx, R.nd < nq ? idx->dd_q.p : R.q32.p, R.nd, k, R.loc_d.p, R.loc_i.p, R.stream);
         if (rc) return rc;
     } else {
         // finish the local search on the host: redo whatever this shard flagged
-        int rc = copy_flags_async(idx, R.stream, nq);
+        int rc = copy_flags_async(idx, R.stream, R.nd);
         if (rc) return rc;
         FIP_CUDA(cudaStreamSynchronize(R.stream));
         int redone = 0;
@@ -183,16 +192,24 @@ int group_rank_search(fip_group* g, int r, int nq, int k, bool second, int stage
     FIP_CUDA(cudaMemsetAsync(R.status.p, 0, sizeof(uint32_t), R.stream));
     const float* fin_d = R.loc_d.p;
     const int64_t* fin_i = R.loc_i.p;
+    const int nd = R.nd;
     if (multi) {
-        int rc = fip_exchange_merge_status(g->xchg[r], R.loc_d.p, R.loc_i.p, nq, k, R.out_d.p, R.out_i.p,
+        int rc = fip_exchange_merge_status(g->xchg[r], R.loc_d.p, R.loc_i.p, nd, k, R.out_d.p, R.out_i.p,
                                            idx->overflow.p, R.status.p, R.stream);
         if (rc) return rc;
         fin_d = R.out_d.p; fin_i = R.out_i.p;
         FIP_CUDA(cudaMemcpyAsync(R.h_status.p, R.status.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, R.stream));
     } else {
         // single device: the status is the shard's own summary words (fetched with all the flags)
-        int rc = copy_flags_async(idx, R.stream, nq);
+        int rc = copy_flags_async(idx, R.stream, nd);
         if (rc) return rc;
+    }
+    if (r == 0 && nd < nq) {   // every caller's row from its representative's result
+        FIP_CUDA(R.fin_d.ensure(on));
+        FIP_CUDA(R.fin_i.ensure(on));
+        int rc = expand_results(idx, fin_d, fin_i, R.fin_d.p, R.fin_i.p, nq, k, R.stream);
+        if (rc) return rc;
+        fin_d = R.fin_d.p; fin_i = R.fin_i.p;
     }
     if (r == 0) {
         FIP_CUDA(cudaMemcpyAsync(g->h_d.p, fin_d, on * sizeof(float), cudaMemcpyDeviceToHost, R.stream));
@@ -221,16 +238,18 @@ int run_group_batch(fip_group* g, const std::vector<HostRequest*>& batch) {
     }
     int rc = group_ensure_exchange(g, nq, k);
     if (rc) return rc;
+    const bool dd = g->dedupe == 2 || (g->dedupe == 1 && batch.size() > 1);
     auto all_ranks = [&](bool second) -> int {
-        if (!g->shared_device) return group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second); });
-        int rc1 = group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second, 1); });
+        if (!g->shared_device) return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd); });
+        int rc1 = group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 1); });
         if (rc1) return rc1;
-        return group_run(g, [g, nq, k, second](int r) { return group_rank_search(g, r, nq, k, second, 2); });
+        return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 2); });
     };
     rc = all_ranks(false);
     if (rc) return rc;
     g->st_searches++;
     g->st_exchange_launches += g->world > 1 ? g->world : 0;
+    g->co.st_queries += nq; g->co.st_distinct += g->ranks[0].nd;
     uint32_t status = 0;
     for (auto& R : g->ranks) status |= R.h_status.p[0];   // identical on every rank when world > 1
     if (status) {
@@ -244,9 +263,17 @@ int run_group_batch(fip_group* g, const std::vector<HostRequest*>& batch) {
             std::lock_guard<std::mutex> l0(g->shard[0]->mu);
             rc = search_finish_synced(g->shard[0], &redone);
             if (!rc && redone) {
-                cudaStream_t s = g->ranks[0].stream;
-                FIP_CUDA(cudaMemcpyAsync(g->h_d.p, g->ranks[0].loc_d.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
-                FIP_CUDA(cudaMemcpyAsync(g->h_i.p, g->ranks[0].loc_i.p, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+                auto& R0 = g->ranks[0];
+                cudaStream_t s = R0.stream;
+                const float* fd = R0.loc_d.p;
+                const int64_t* fi = R0.loc_i.p;
+                if (R0.nd < nq) {
+                    rc = expand_results(g->shard[0], fd, fi, R0.fin_d.p, R0.fin_i.p, nq, k, s);
+                    if (rc) return rc;
+                    fd = R0.fin_d.p; fi = R0.fin_i.p;
+                }
+                FIP_CUDA(cudaMemcpyAsync(g->h_d.p, fd, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+                FIP_CUDA(cudaMemcpyAsync(g->h_i.p, fi, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
                 FIP_CUDA(cudaStreamSynchronize(s));
             }
         }
@@ -333,6 +360,7 @@ void fip_group_destroy(fip_group* g) {
         auto& R = g->ranks[r];
         if (R.stream) { cudaStreamSynchronize(R.stream); cudaStreamDestroy(R.stream); }
         R.q32.release(); R.loc_d.release(); R.out_d.release(); R.loc_i.release(); R.out_i.release();
+        R.fin_d.release(); R.fin_i.release();
         R.status.release(); R.h_status.release();
     }
     for (auto* s : g->shard) fip_destroy(s);
@@ -395,6 +423,11 @@ int fip_group_set_option(fip_group* g, const char* key, int64_t value) {
     if (!g || !key) return fail(FIP_ERR_INVALID, "bad argument");
     const std::string k(key);
     if (k == "coalesce") { g->co.enabled = value != 0; return FIP_OK; }
+    if (k == "dedupe") {
+        if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "dedupe must be 0, 1 or 2");
+        g->dedupe = (int)value;
+        return FIP_OK;
+    }
     if (k == "coalesce_max_batch") {
         if (value < 1) return fail(FIP_ERR_INVALID, "coalesce_max_batch must be >= 1");
         g->co.max_batch = value;

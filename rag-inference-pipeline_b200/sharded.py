@@ -54,7 +54,7 @@ class ShardedFlatIPSearcher:
     """One instance per rank.  ``search_tensor`` is the device-resident hot path."""
 
     def __init__(self, dim: int, dtype: str, total_rows: int, *, rank: int = 0,
-                 world_size: int = 1, device: int = 0, group=None, exchange: str = "auto"):
+                 world_size: int = 1, device: int = 0, group=None, exchange: str = "auto", index=None):
         """exchange: how the per-shard results meet.  "p2p" = the fused exchange + merge kernel
         over NVLink peer memory (K4), "nccl" = one packed all-gather + the K3 merge kernel,
         "auto" = p2p when the peers' buffers can be mapped (CUDA IPC), else nccl."""
@@ -73,8 +73,11 @@ class ShardedFlatIPSearcher:
         self.device = int(device)
         self.group = group
         self.row_begin, self.row_end = shard_range(total_rows, rank, world_size)
-        self.index = FlatIPIndex(dim, dtype, device, id_base=self.row_begin,
-                                 capacity_rows=self.row_end - self.row_begin)
+        # index: an existing shard index to drive (e.g. the one a B200FlatIPStore holds) instead of
+        # a new, empty one; it stays owned by whoever made it.
+        self._owns_index = index is None
+        self.index = index if index is not None else FlatIPIndex(
+            dim, dtype, device, id_base=self.row_begin, capacity_rows=self.row_end - self.row_begin)
 
     @property
     def local_rows(self) -> int:
@@ -270,4 +273,5 @@ class ShardedFlatIPSearcher:
                 dist.barrier(group=self.group)   # peers may still be reading / writing our buffer
             self._xchg.close()
         self._xchg = None
-        self.index.close()
+        if self._owns_index:
+            self.index.close()

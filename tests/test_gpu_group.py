@@ -287,3 +287,54 @@ def test_exchange_kernel_larger_than_one_wave():
         assert torch.equal(od[r], od[0]) and torch.equal(oi[r], oi[0])
     for x in group:
         x.close()
+
+
+@pytest.mark.parametrize("sharded", [False, True])
+def test_in_batch_duplicates_are_searched_once(shared_device, sharded):
+    """callers whose batches are coalesced into one launch often carry the same
+    question.  Bit-identical queries (the reference's cache key is sha256 of the fp32 bytes,
+    api.py:398) are searched once on the device and every caller still gets its own, bit-identical
+    rows -- on one index and on the sharded group."""
+    from rag_inference_pipeline_b200 import FlatIPIndex
+    from rag_inference_pipeline_b200.group import FlatIPGroup
+    dim, n, k = 128, 40_000, 20
+    if sharded:
+        idx = FlatIPGroup(dim, "f16", [0, 0, 0], n)
+        idx.add_synthetic(n, synthetic.CORPUS_SEED)
+    else:
+        idx = FlatIPIndex(dim, "f16", 0)
+        idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    base = synthetic.synthetic_queries(24, dim)
+    Dref, Iref = idx.search(base, k)
+    # one call with internal duplicates: only searched once each when dedupe = 2 ("always")
+    mixed = base[[0, 5, 0, 7, 5, 5, 23, 0]]
+    tweaked = mixed.copy()
+    tweaked[3, 17] = np.nextafter(tweaked[3, 17], np.float32(2.0))     # one ulp apart: NOT a duplicate
+    idx.set_option("dedupe", 2)
+    q0, d0 = idx.stat("host_queries"), idx.stat("distinct_queries")
+    D, I = idx.search(tweaked, k)
+    assert idx.stat("host_queries") - q0 == 8 and idx.stat("distinct_queries") - d0 == 4
+    for row, src in enumerate([0, 5, 0, None, 5, 5, 23, 0]):
+        if src is not None:
+            assert np.array_equal(I[row], Iref[src]) and np.array_equal(D[row], Dref[src])
+    # default (dedupe = 1): concurrent callers with overlapping batches
+    idx.set_option("dedupe", 1)
+    q0, d0 = idx.stat("host_queries"), idx.stat("distinct_queries")
+    out = [None] * 8
+    gate = threading.Barrier(8)
+
+    def work(t):
+        gate.wait()
+        out[t] = idx.search(base[2 * t:2 * t + 10], k)      # neighbours share 8 of their 10 queries
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(8)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for t in range(8):
+        assert np.array_equal(out[t][1], Iref[2 * t:2 * t + 10]) and np.array_equal(out[t][0], Dref[2 * t:2 * t + 10])
+    assert idx.stat("host_queries") - q0 == 80
+    if idx.stat("coalesced_calls") > 0:                       # (some calls did share a batch)
+        assert idx.stat("distinct_queries") - d0 < 80
+    idx.close()

@@ -727,7 +727,7 @@ def _check_full(D, I, Dr, Ir, k):
     assert res["id_mismatch_total"] <= max(2, I.size // 200), res
     tol = FULL_RTOL * np.maximum(1.0, np.abs(Dr[:, k - 1].astype(np.float64)))
     clear = (Dr[:, k - 1].astype(np.float64) - Dr[:, k].astype(np.float64)) > 2 * tol
-    assert clear.mean() > 0.9
+    assert clear.mean() > 0.3      # (at k = 1024 of 1e7 rows about half of the boundaries are that close)
     for r in np.nonzero(clear)[0]:
         assert set(I[r].tolist()) == set(Ir[r, :k].tolist()), r
     assert np.all(np.diff(D, axis=1) <= 0)
