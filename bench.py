@@ -345,7 +345,12 @@ def run_b200(args, rank, local_rank, world):
         per_scan[i] = [searcher.index.stat(f"scan_rows_{i}"), ns, searches_timed]
 
     tms = torch.tensor([ms, float(scan_ns)], dtype=torch.float64, device=dev)
+    per_rank_scan_ms = [scan_ns / 1e6 / searches_timed]
     if world > 1:
+        mine = torch.tensor([scan_ns / 1e6 / searches_timed], dtype=torch.float64, device=dev)
+        every = torch.empty((world,), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(every, mine)
+        per_rank_scan_ms = [round(float(v), 3) for v in every.tolist()]
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms_max, scan_ns_max = (float(v) for v in tms.tolist())
     variant = searcher.index.last_variant()
@@ -489,6 +494,9 @@ def run_b200(args, rank, local_rank, world):
         roof["launches_timed"] = scan_launches
         roof["all_scan_launches_ms_per_step"] = scan_s * 1e3 / searches_timed
         roof["searches_timed"] = searches_timed
+        # every rank's own scan time per search: the step ends with the SLOWEST GPU (boxes differ by
+        # several per cent in the clock their power cap allows)
+        roof["per_rank_scan_ms"] = per_rank_scan_ms
         roof["whole_search_frac"] = None
         if tensor_bound and ms_per_step > 0:
             roof["whole_search_frac"] = (2.0 * batch * n_local * dim / (ms_per_step * 1e-3) / 1e12
