@@ -172,6 +172,16 @@ void fip_exchange_destroy(fip_exchange* x);
 typedef struct fip_group fip_group;
 int fip_group_create(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
                      int64_t planned_rows, fip_group** out);
+/* Same with shard sizes proportional to `weights` (n_devices positive numbers, e.g. the rates
+ * fip_calibrate_devices measured; null = equal shards): a search ends with the slowest GPU, and the
+ * GPUs of one box differ by several per cent in the clock their power cap lets them sustain. */
+int fip_group_create_weighted(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
+                              int64_t planned_rows, const double* weights, fip_group** out);
+/* Sustained search throughput (corpus rows per second of scan-kernel time) of every listed device,
+ * all measured at the same time on a `rows`-row synthetic corpus, `batch` queries, k results, for
+ * about `seconds` seconds (the first 30 % warms the chips up). */
+int fip_calibrate_devices(const int32_t* devices, int32_t n_devices, int32_t dim, int32_t dtype,
+                          int64_t rows, int32_t batch, int32_t k, double seconds, double* rates);
 void fip_group_destroy(fip_group* g);
 int32_t fip_group_size(const fip_group* g);
 /* Shard r as a plain index (options, statistics, reconstruct; do not add rows through it). */
@@ -185,7 +195,7 @@ int fip_group_reset(fip_group* g);
 int fip_group_search(fip_group* g, const float* queries, int64_t nq, int32_t k, float* distances,
                      int64_t* ids);
 /* Options are applied to every shard ("coalesce*" at the group); statistics are summed over the
- * shards' last searches, plus "devices", "rows_per_shard", "searches", "flagged_searches" (searches
+ * shards' last searches, plus "devices", "rows_per_shard", "shard_begin_<r>" (first global row of shard r; r = devices: the planned total), "searches", "flagged_searches" (searches
  * in which some shard had to redo a query, costing a second exchange), "exchange_launches". */
 int fip_group_set_option(fip_group* g, const char* key, int64_t value);
 int64_t fip_group_get_stat(const fip_group* g, const char* key);

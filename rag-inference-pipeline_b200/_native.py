@@ -40,7 +40,7 @@ EXPORTED_SYMBOLS = (
     "fip_exchange_connect_local", "fip_exchange_merge", "fip_exchange_merge_status",
     "fip_exchange_destroy",
     "fip_add_host", "fip_search_device_async", "fip_search_status", "fip_search_flags_device",
-    "fip_group_create", "fip_group_destroy", "fip_group_size", "fip_group_shard", "fip_group_ntotal",
+    "fip_group_create", "fip_group_create_weighted", "fip_calibrate_devices", "fip_group_destroy", "fip_group_size", "fip_group_shard", "fip_group_ntotal",
     "fip_group_add_synthetic", "fip_group_add_host", "fip_group_reset", "fip_group_search",
     "fip_group_set_option", "fip_group_get_stat",
 )
@@ -147,6 +147,12 @@ def load_library():
         lib.fip_group_create.argtypes = [c.POINTER(FipConfig), c.POINTER(c.c_int32), c.c_int32, c.c_int64,
                                          c.POINTER(P)]
         lib.fip_group_create.restype = c.c_int
+        lib.fip_group_create_weighted.argtypes = [c.POINTER(FipConfig), c.POINTER(c.c_int32), c.c_int32,
+                                                  c.c_int64, c.POINTER(c.c_double), c.POINTER(P)]
+        lib.fip_group_create_weighted.restype = c.c_int
+        lib.fip_calibrate_devices.argtypes = [c.POINTER(c.c_int32), c.c_int32, c.c_int32, c.c_int32, c.c_int64,
+                                              c.c_int32, c.c_int32, c.c_double, c.POINTER(c.c_double)]
+        lib.fip_calibrate_devices.restype = c.c_int
         lib.fip_group_destroy.argtypes = [P]
         lib.fip_group_destroy.restype = None
         lib.fip_group_size.argtypes = [P]

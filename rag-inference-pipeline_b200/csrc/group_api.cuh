@@ -5,9 +5,14 @@
 //     (/root/reference/src/pipeline/services/retrieval/api.py:383-389)
 // use all 8 GPUs of a box.  (Included at the end of flatip_api.cu: it uses the file's internals.)
 //
-// Layout: shard r lives on devices[r] and owns the contiguous global rows [r * per, (r + 1) * per)
-// (per = ceil(planned_rows / g); the last shard also takes whatever is added beyond the plan), so
-// "shard, then position" == "id ascending" and the fixed tie-break survives the merge.
+// Layout: shard r lives on devices[r] and owns the contiguous global rows [bound[r], bound[r + 1])
+// (uniform: bound[r] = r * ceil(planned_rows / g); the last shard also takes whatever is added
+// beyond the plan), so "shard, then position" == "id ascending" and the fixed tie-break survives
+// the merge.  WEIGHTED shards (fip_group_create_weighted): a search ends with the slowest GPU, and
+// under the ~1000 W cap the B200s of one box differ by up to 10 % in the clock they sustain
+// (measured: 59.4 vs 65.6 ms for equal halves of the headline corpus on a 2-GPU box), so bound[]
+// may follow measured per-device throughput (fip_calibrate_devices) instead: every GPU then
+// finishes at the same time.
 //
 // A search (run_group_batch):
 //   every rank, on its own persistent host thread and stream, in parallel:
@@ -19,6 +24,7 @@
 //   local searches on the host (redo of the flagged queries) and exchange + merge once more.
 #pragma once
 
+#include <chrono>
 #include <functional>
 #include <thread>
 
@@ -26,6 +32,7 @@ struct fip_group {
     int world = 0;
     int dim = 0, dtype = 0;
     int64_t planned_rows = 0, per = 0;
+    std::vector<int64_t> bound;   // [world + 1] global row boundaries of the shards (relative to row 0)
     std::vector<int> devices;
     std::vector<fip_index*> shard;
     std::vector<fip_exchange*> xchg;
@@ -110,8 +117,8 @@ struct GroupPiece { int r; int64_t first, count; };
 std::vector<GroupPiece> group_route(const fip_group* g, int64_t g0, int64_t n) {
     std::vector<GroupPiece> out;
     for (int r = 0; r < g->world && n > 0; ++r) {
-        const int64_t lo = (int64_t)r * g->per;
-        const int64_t hi = r + 1 == g->world ? INT64_MAX : lo + g->per;
+        const int64_t lo = g->bound[r];
+        const int64_t hi = r + 1 == g->world ? INT64_MAX : g->bound[r + 1];
         const int64_t b = std::max(g0, lo), e = std::min(g0 + n, hi);
         if (b < e) out.push_back({r, b - g0, e - b});
     }
@@ -302,6 +309,11 @@ extern "C" {
 
 int fip_group_create(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
                      int64_t planned_rows, fip_group** out) {
+    return fip_group_create_weighted(cfg, devices, n_devices, planned_rows, nullptr, out);
+}
+
+int fip_group_create_weighted(const fip_config* cfg, const int32_t* devices, int32_t n_devices,
+                              int64_t planned_rows, const double* weights, fip_group** out) {
     if (!cfg || !devices || !out) return fail(FIP_ERR_INVALID, "null argument");
     *out = nullptr;
     if (n_devices < 1 || n_devices > kMaxRanks) return fail(FIP_ERR_INVALID, "1 to 16 devices");
@@ -321,13 +333,32 @@ int fip_group_create(const fip_config* cfg, const int32_t* devices, int32_t n_de
     g->world = n_devices; g->dim = cfg->dim; g->dtype = cfg->dtype;
     g->planned_rows = planned_rows;
     g->per = std::max<int64_t>(1, (planned_rows + n_devices - 1) / n_devices);
+    g->bound.assign(n_devices + 1, 0);
+    double wsum = 0.0;
+    if (weights)
+        for (int r = 0; r < n_devices; ++r) {
+            if (!(weights[r] > 0.0)) { delete g; return fail(FIP_ERR_INVALID, "shard weights must be positive"); }
+            wsum += weights[r];
+        }
+    double acc = 0.0;
+    for (int r = 0; r < n_devices; ++r) {
+        if (weights) {
+            // proportional boundaries, on whole 256-row corpus tiles
+            acc += weights[r];
+            int64_t b = (int64_t)((double)planned_rows * (acc / wsum) / 256.0 + 0.5) * 256;
+            g->bound[r + 1] = std::max(g->bound[r], std::min(planned_rows, b));
+        } else {
+            g->bound[r + 1] = std::min(planned_rows, (int64_t)(r + 1) * g->per);
+        }
+    }
+    g->bound[n_devices] = planned_rows;
     g->devices.assign(devices, devices + n_devices);
     g->ranks.resize(n_devices);
     for (int r = 0; r < n_devices; ++r) {
         fip_config c = *cfg;
         c.device = devices[r];
-        c.id_base = cfg->id_base + (int64_t)r * g->per;
-        c.capacity_rows = planned_rows > 0 ? std::min<int64_t>(g->per, std::max<int64_t>(0, planned_rows - (int64_t)r * g->per)) : 0;
+        c.id_base = cfg->id_base + g->bound[r];
+        c.capacity_rows = g->bound[r + 1] - g->bound[r];
         fip_index* idx = nullptr;
         int rc = fip_create(&c, &idx);
         if (rc == FIP_OK && cudaStreamCreateWithFlags(&g->ranks[r].stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -437,11 +468,82 @@ int fip_group_set_option(fip_group* g, const char* key, int64_t value) {
     return FIP_OK;
 }
 
+// Sustained search throughput of every listed device, measured at the same time (the power cap is
+// what differs between the GPUs of a box, so they must all be under load): each device searches its
+// own `rows`-row synthetic corpus with `batch` queries, k results, for about `seconds`; rates[r] =
+// corpus rows scanned per second of scan-kernel time.
+int fip_calibrate_devices(const int32_t* devices, int32_t n_devices, int32_t dim, int32_t dtype,
+                          int64_t rows, int32_t batch, int32_t k, double seconds, double* rates) {
+    if (!devices || !rates || n_devices < 1 || n_devices > kMaxRanks || rows < 1024 || batch < 1 || k < 1)
+        return fail(FIP_ERR_INVALID, "bad argument");
+    std::vector<int> rcs(n_devices, 0);
+    std::vector<std::string> errs(n_devices);
+    std::vector<std::thread> th;
+    for (int r = 0; r < n_devices; ++r)
+        th.emplace_back([&, r]() {
+            auto body = [&]() -> int {
+                fip_config c{};
+                c.dim = dim; c.dtype = dtype; c.device = devices[r]; c.capacity_rows = rows;
+                fip_index* idx = nullptr;
+                int rc = fip_create(&c, &idx);
+                if (rc) return rc;
+                struct Guard { fip_index* i; ~Guard() { fip_destroy(i); } } guard{idx};
+                rc = fip_add_synthetic(idx, rows, 99, 0);
+                if (rc) return rc;
+                rc = fip_set_option(idx, "profile_events", 1);
+                if (rc) return rc;
+                DevBuf<float> q, d;
+                DevBuf<int64_t> i;
+                FIP_CUDA(q.ensure((size_t)batch * dim));
+                FIP_CUDA(d.ensure((size_t)batch * k));
+                FIP_CUDA(i.ensure((size_t)batch * k));
+                synthetic_fill_kernel<float><<<64, 256, 0, idx->stream>>>(q.p, batch, dim, 0, 4321, 1u);
+                FIP_CUDA(cudaGetLastError());
+                double scan_ms = 0.0;
+                int64_t searches = 0;
+                const auto t0 = std::chrono::steady_clock::now();
+                bool first = true;
+                while (true) {
+                    for (int it = 0; it < 8; ++it) {
+                        rc = fip_search_device_async(idx, q.p, batch, k, d.p, i.p, idx->stream);
+                        if (rc) break;
+                    }
+                    int32_t flagged = 0;
+                    if (!rc) rc = fip_search_status(idx, &flagged);
+                    if (rc) break;
+                    const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+                    if (!first && el > 0.3 * seconds) {   // the first 30 % only warms the chip up
+                        scan_ms += idx->st_scan_ms;
+                        searches += idx->st_scan_searches;
+                    }
+                    first = false;
+                    if (el > seconds) break;
+                }
+                q.release(); d.release(); i.release();
+                if (rc) return rc;
+                rates[r] = scan_ms > 0.0 ? (double)rows * (double)searches / (scan_ms * 1e-3) : 0.0;
+                return FIP_OK;
+            };
+            cudaSetDevice(devices[r]);
+            g_last_error.clear();
+            rcs[r] = body();
+            errs[r] = g_last_error;
+        });
+    for (auto& t : th) t.join();
+    for (int r = 0; r < n_devices; ++r)
+        if (rcs[r]) return fail(rcs[r], "device " + std::to_string(devices[r]) + ": " + errs[r]);
+    return FIP_OK;
+}
+
 int64_t fip_group_get_stat(const fip_group* g, const char* key) {
     if (!g || !key) return -1;
     const std::string k(key);
     if (k == "devices") return g->world;
     if (k == "rows_per_shard") return g->per;
+    if (k.rfind("shard_begin_", 0) == 0) {
+        const int r = atoi(k.c_str() + 12);
+        return (r >= 0 && r <= g->world) ? g->bound[r] : -1;
+    }
     if (k == "searches") return g->st_searches;
     if (k == "flagged_searches") return g->st_flagged_searches;
     if (k == "exchange_launches") return g->st_exchange_launches;

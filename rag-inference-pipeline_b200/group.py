@@ -40,8 +40,23 @@ class _ShardView:
         return out
 
 
+def calibrate_devices(devices, dim: int, dtype: str, *, batch: int = 1024, k: int = 100,
+                      rows: int = 2_000_000, seconds: float = 1.5) -> list[float]:
+    """Sustained search throughput (corpus rows per second of scan-kernel time) of every device,
+    measured on all of them AT THE SAME TIME: under the power cap the GPUs of one box differ by
+    several per cent, and a sharded search ends with the slowest one.  Feed the result to
+    ``FlatIPGroup(weights=...)`` / ``ShardedFlatIPSearcher(weights=...)``."""
+    lib = _native.load_library()
+    devices = [int(d) for d in devices]
+    arr = (ctypes.c_int32 * len(devices))(*devices)
+    out = (ctypes.c_double * len(devices))()
+    _native.check(lib.fip_calibrate_devices(arr, len(devices), int(dim), _native.DTYPE_CODES[dtype], int(rows),
+                                            int(batch), int(k), float(seconds), out))
+    return [float(v) for v in out]
+
+
 class FlatIPGroup:
-    def __init__(self, dim: int, dtype: str, devices, planned_rows: int, *, id_base: int = 0):
+    def __init__(self, dim: int, dtype: str, devices, planned_rows: int, *, id_base: int = 0, weights=None):
         if dtype not in _native.DTYPE_CODES:
             raise ValueError(f"unknown storage dtype {dtype!r}")
         devices = [int(d) for d in devices]
@@ -52,8 +67,13 @@ class FlatIPGroup:
                                 reserved=0, capacity_rows=0, id_base=int(id_base))
         arr = (ctypes.c_int32 * len(devices))(*devices)
         h = ctypes.c_void_p()
-        _native.check(self._lib.fip_group_create(ctypes.byref(cfg), arr, len(devices), int(planned_rows),
-                                                 ctypes.byref(h)))
+        warr = None
+        if weights is not None:
+            if len(weights) != len(devices):
+                raise ValueError("one weight per device")
+            warr = (ctypes.c_double * len(devices))(*[float(w) for w in weights])
+        _native.check(self._lib.fip_group_create_weighted(ctypes.byref(cfg), arr, len(devices), int(planned_rows),
+                                                          warr, ctypes.byref(h)))
         self._h = h
         self.d = int(dim)
         self.dtype = _native.DTYPE_NAMES[_native.DTYPE_CODES[dtype]]
@@ -80,6 +100,9 @@ class FlatIPGroup:
     @property
     def ntotal(self) -> int:
         return int(self._lib.fip_group_ntotal(self._handle()))
+
+    def shard_bounds(self) -> list[int]:
+        return [self.stat(f"shard_begin_{r}") for r in range(len(self.devices) + 1)]
 
     def shard(self, r: int) -> _ShardView:
         h = self._lib.fip_group_shard(self._handle(), int(r))

@@ -19,13 +19,28 @@ import numpy as np
 from .index import FlatIPIndex, merge_strided_device, torch_stream_handle
 
 
-def shard_range(total_rows: int, rank: int, world_size: int) -> tuple[int, int]:
-    """Global row range [begin, end) owned by `rank`."""
+def shard_range(total_rows: int, rank: int, world_size: int, weights=None) -> tuple[int, int]:
+    """Global row range [begin, end) owned by `rank`.  ``weights`` (one positive number per rank,
+    e.g. measured per-GPU throughput) makes the shards proportional -- boundaries on whole 256-row
+    tiles, same rule as the C ABI's fip_group_create_weighted -- instead of equal."""
     if world_size < 1 or not (0 <= rank < world_size):
         raise ValueError("bad rank / world_size")
-    per = -(-int(total_rows) // world_size)
-    begin = min(int(total_rows), rank * per)
-    end = min(int(total_rows), begin + per)
+    total_rows = int(total_rows)
+    if weights is not None:
+        if len(weights) != world_size or any(not (w > 0) for w in weights):
+            raise ValueError("need one positive weight per rank")
+        wsum = float(sum(weights))
+        bounds = [0]
+        acc = 0.0
+        for r in range(world_size):
+            acc += float(weights[r])
+            b = int(total_rows * (acc / wsum) / 256.0 + 0.5) * 256
+            bounds.append(max(bounds[-1], min(total_rows, b)))
+        bounds[-1] = total_rows
+        return bounds[rank], bounds[rank + 1]
+    per = -(-total_rows // world_size)
+    begin = min(total_rows, rank * per)
+    end = min(total_rows, begin + per)
     return begin, end
 
 
@@ -54,7 +69,8 @@ class ShardedFlatIPSearcher:
     """One instance per rank.  ``search_tensor`` is the device-resident hot path."""
 
     def __init__(self, dim: int, dtype: str, total_rows: int, *, rank: int = 0,
-                 world_size: int = 1, device: int = 0, group=None, exchange: str = "auto", index=None):
+                 world_size: int = 1, device: int = 0, group=None, exchange: str = "auto", index=None,
+                 weights=None):
         """exchange: how the per-shard results meet.  "p2p" = the fused exchange + merge kernel
         over NVLink peer memory (K4), "nccl" = one packed all-gather + the K3 merge kernel,
         "auto" = p2p when the peers' buffers can be mapped (CUDA IPC), else nccl."""
@@ -72,7 +88,7 @@ class ShardedFlatIPSearcher:
         self.world_size = int(world_size)
         self.device = int(device)
         self.group = group
-        self.row_begin, self.row_end = shard_range(total_rows, rank, world_size)
+        self.row_begin, self.row_end = shard_range(total_rows, rank, world_size, weights)
         # index: an existing shard index to drive (e.g. the one a B200FlatIPStore holds) instead of
         # a new, empty one; it stays owned by whoever made it.
         self._owns_index = index is None

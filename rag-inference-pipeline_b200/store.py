@@ -36,7 +36,7 @@ from urllib.parse import parse_qs
 import numpy as np
 
 from . import index_io
-from .group import FlatIPGroup
+from .group import FlatIPGroup, calibrate_devices
 from .index import FlatIPIndex, torch_stream_handle
 from .synthetic import CORPUS_SEED
 
@@ -76,6 +76,10 @@ class B200FlatIPStore:
         self.devices = _parse_devices(config.get("devices", os.environ.get("FLATIP_B200_DEVICES")))
         if self.devices:
             self.device = self.devices[0]
+        # shard sizes: "equal" (default), "auto" (proportional to the throughput every device
+        # sustains, measured at load() on all of them at once) or an explicit list of weights
+        self.shard_weights = config.get("shard_weights", os.environ.get("FLATIP_B200_SHARD_WEIGHTS", "equal"))
+        self.used_shard_weights = None
         # None = keep the dtype the file holds (fp32 for faiss files, like the reference).
         self.storage_dtype = config.get("storage_dtype", os.environ.get("FLATIP_B200_DTYPE"))
         self.id_base = int(config.get("id_base", 0))
@@ -88,7 +92,18 @@ class B200FlatIPStore:
     # ------------------------------------------------------------------------------- load
     def _new_index(self, dim: int, dtype: str, nrows: int, id_base: int):
         if self.devices and len(self.devices) > 1:
-            return FlatIPGroup(dim, dtype, self.devices, nrows, id_base=id_base)
+            weights = self.shard_weights
+            if isinstance(weights, str):
+                if weights == "auto":
+                    weights = calibrate_devices(
+                        self.devices, dim, dtype, batch=int(getattr(self.settings, "retrieval_batch_size", 32) or 32),
+                        k=int(getattr(self.settings, "retrieval_k", 10) or 10))
+                elif weights == "equal":
+                    weights = None
+                else:
+                    weights = [float(w) for w in weights.split(",")]
+            self.used_shard_weights = weights
+            return FlatIPGroup(dim, dtype, self.devices, nrows, id_base=id_base, weights=weights)
         return FlatIPIndex(dim, dtype, self.device, id_base=id_base, capacity_rows=nrows)
 
     def _load_synthetic(self):
