@@ -285,6 +285,18 @@ def run_b200(args, rank, local_rank, world):
     store_settings = _types.SimpleNamespace(
         faiss_index_path=f"synthetic:{total_rows}?dim={dim}&dtype={dtype}&seed={CORPUS_SEED}", faiss_dim=dim)
     gloo = dist.new_group(backend="gloo") if world > 1 else None   # host-only barriers for the e2e leg
+    # Shard sizes follow what every GPU sustains (N > 1): a search ends with the slowest GPU, and
+    # under the power cap the B200s of one box differ by up to 10 %.  Every rank measures its own
+    # device while all the others are under the same load (`--balance 0` = equal shards).
+    weights = None
+    if world > 1 and args.balance:
+        from rag_inference_pipeline_b200.group import calibrate_devices
+        dist.barrier()
+        rate = calibrate_devices([local_rank], dim, dtype, batch=batch, k=k, rows=2_000_000, seconds=1.5)[0]
+        every = [None] * world
+        dist.all_gather_object(every, rate)
+        if all(r and r > 0 for r in every):
+            weights = [float(r) for r in every]
     t0 = time.time()
     store = None
     if world == 1:
@@ -294,7 +306,7 @@ def run_b200(args, rank, local_rank, world):
                                          index=store.native_index)
     else:
         searcher = ShardedFlatIPSearcher(dim, dtype, total_rows, rank=rank, world_size=world,
-                                         device=local_rank, exchange=args.exchange)
+                                         device=local_rank, exchange=args.exchange, weights=weights)
         searcher.load_synthetic(CORPUS_SEED)
     load_s = time.time() - t0
     if args.variant != "auto":
@@ -382,9 +394,10 @@ def run_b200(args, rank, local_rank, world):
         tol = 1e-5 if dtype == "f32" else 1e-3
         blk = min(4096, total_rows)
         starts = {0, max(0, total_rows // 2 - blk // 2), max(0, total_rows - blk)}
-        per = -(-total_rows // world)
+        from rag_inference_pipeline_b200.sharded import shard_range
         for r_ in range(1, world):      # rows on both sides of every shard boundary
-            starts.add(max(0, min(total_rows - blk, r_ * per - blk // 2)))
+            b_, _ = shard_range(total_rows, r_, world, weights)
+            starts.add(max(0, min(total_rows - blk, b_ - blk // 2)))
         missed = 0
         rows_checked = 0
         kth = Dh[:, -1].astype(np.float64)
@@ -426,7 +439,8 @@ def run_b200(args, rank, local_rank, world):
         torch.cuda.empty_cache()
         dist.barrier(group=gloo)
         if rank == 0:
-            store = B200FlatIPStore(store_settings, {"devices": list(range(world))})
+            store = B200FlatIPStore(store_settings, {"devices": list(range(world)),
+                                                     "shard_weights": ",".join(repr(w) for w in weights) if weights else "equal"})
             store.load()
     if rank == 0:
         for kv in args.opt:
@@ -524,6 +538,7 @@ def run_b200(args, rank, local_rank, world):
             "variant": variant, "phases_per_search": st["phases"], "overflow_queries": st["overflow"],
             "uncertified_queries": st["uncertified"], "cta_group": st["cta_group"],
             "deferred_epilogue": st["deferred"], "options": args.opt, "exchange": st["exchange"],
+            "shard_weights": ([round(w / (sum(weights) / world), 4) for w in weights] if weights else "equal"),
             "corpus_load_s": load_s, "verify": verify,
         }
         sys.stdout.flush()
@@ -701,6 +716,8 @@ def main():
     ap.add_argument("--k", type=int, default=0)
     ap.add_argument("--variant", choices=["auto", "stream", "tensor"], default="auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--balance", type=int, default=1,
+                    help="N > 1: 1 = shard sizes proportional to measured per-GPU throughput, 0 = equal shards")
     ap.add_argument("--opt", action="append", default=[], help="index option key=value (A/B runs)")
     ap.add_argument("--exchange", choices=["auto", "p2p", "nccl"], default="auto",
                     help="N > 1: fused peer-memory exchange + merge kernel, or NCCL all-gather + merge")

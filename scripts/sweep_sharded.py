@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--batches", default="1,2,4,8,16,32,64,128,256,512,1024,2048,4096")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--exchange", default="auto")
+    ap.add_argument("--balance", type=int, default=0, help="1: shards proportional to measured per-GPU throughput")
     args = ap.parse_args()
 
     import torch
@@ -52,8 +53,16 @@ def main():
         torch.cuda.synchronize()
 
     peaks = load_peaks()
+    weights = None
+    if world > 1 and args.balance:
+        from rag_inference_pipeline_b200.group import calibrate_devices
+        dist.barrier()
+        rate = calibrate_devices([local], args.dim, args.dtype, batch=1024, k=args.k, rows=2_000_000, seconds=1.5)[0]
+        every = [None] * world
+        dist.all_gather_object(every, rate)
+        weights = [float(r) for r in every]
     s = ShardedFlatIPSearcher(args.dim, args.dtype, args.rows, rank=rank, world_size=world, device=local,
-                              exchange=args.exchange)
+                              exchange=args.exchange, weights=weights)
     s.load_synthetic(CORPUS_SEED)
     s.index.set_option("profile_events", 1)
     es = 4 if args.dtype == "f32" else 2

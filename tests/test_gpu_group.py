@@ -338,3 +338,24 @@ def test_in_batch_duplicates_are_searched_once(shared_device, sharded):
     if idx.stat("coalesced_calls") > 0:                       # (some calls did share a batch)
         assert idx.stat("distinct_queries") - d0 < 80
     idx.close()
+
+
+def test_weighted_shards_and_calibration(shared_device):
+    """Shard sizes proportional to measured per-device throughput (a search ends with the slowest
+    GPU): same answers as the single index bit for bit, boundaries where the weights put them."""
+    from rag_inference_pipeline_b200.group import FlatIPGroup, calibrate_devices
+    from rag_inference_pipeline_b200.sharded import shard_range
+    dim, n, nq, k = 128, 50_000, 70, 30
+    rates = calibrate_devices([0], dim, "f16", batch=64, k=10, rows=200_000, seconds=0.3)
+    assert len(rates) == 1 and rates[0] > 1e6            # rows per second of scan time
+    w = [1.0, 1.3, 0.8]
+    q = synthetic.synthetic_queries(nq, dim)
+    Ds, Is = _single(dim, "f16", n, q, k)
+    g = FlatIPGroup(dim, "f16", [0, 0, 0], n, weights=w)
+    g.add_synthetic(n, synthetic.CORPUS_SEED)
+    bounds = g.shard_bounds()
+    assert bounds == [shard_range(n, r, 3, w)[0] for r in range(3)] + [n]
+    assert [g.shard(r).ntotal for r in range(3)] == [bounds[r + 1] - bounds[r] for r in range(3)]
+    D, I = g.search(q, k)
+    assert np.array_equal(I, Is) and np.array_equal(D, Ds)
+    g.close()

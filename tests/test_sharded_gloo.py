@@ -157,3 +157,20 @@ def test_failed_peer_mapping_falls_back_to_nccl_for_good(tmp_path):
     mp.spawn(_xchg_fail_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     for rank in range(world):
         assert (tmp_path / f"ok{rank}").read_text() == "1"
+
+
+def test_weighted_shard_ranges():
+    """Shards proportional to per-GPU throughput: contiguous, ordered, on 256-row tiles, covering
+    the corpus exactly; equal weights reproduce (to a tile) the equal split."""
+    total, w = 100_000_000, [1.00, 1.12, 1.01, 1.06, 1.05, 1.08, 1.09, 1.05]
+    rng = [shard_range(total, r, 8, w) for r in range(8)]
+    assert rng[0][0] == 0 and rng[-1][1] == total
+    for (b0, e0), (b1, e1) in zip(rng, rng[1:]):
+        assert e0 == b1 and b1 % 256 == 0
+    sizes = [e - b for b, e in rng]
+    for r in range(8):
+        assert abs(sizes[r] / total - w[r] / sum(w)) < 1e-5
+    eq = [shard_range(10_000, r, 4, [1, 1, 1, 1]) for r in range(4)]
+    assert [b for b, _ in eq] == [0, 2560, 5120, 7424] and eq[-1][1] == 10_000
+    with pytest.raises(ValueError):
+        shard_range(100, 0, 2, [1.0, 0.0])
