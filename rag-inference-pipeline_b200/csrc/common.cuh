@@ -179,6 +179,23 @@ __device__ __forceinline__ bool append_candidate(const ScanArgs& a, int q, float
     return ((slot + 1u) & (kRefreshEvery - 1u)) == 0u;
 }
 
+// Per-search reset of the candidate lists and flag words (select.cuh flag_slot), one element per
+// thread i.  `sticky` (may be null): the summary words an earlier, never checked (asynchronous)
+// search left behind are folded into it before they are cleared, so fip_search_status still sees
+// them.  Run by init_lists_kernel, or fused into prepare_queries_kernel (one launch fewer).
+struct ListInit {
+    float* thr;
+    uint32_t* cnt;
+    uint32_t* flags;
+    uint32_t* sticky;
+    int nq;
+};
+__device__ __forceinline__ void init_lists_thread(const ListInit& a, int i) {
+    if (i < a.nq) { a.thr[i] = kNegInf; a.cnt[i] = 0u; }
+    if (i < 2 && a.sticky && a.flags[i]) atomicOr(a.sticky, 1u << i);
+    if (i < 2 + 2 * a.nq) a.flags[i] = 0u;
+}
+
 inline int next_pow2(int v) {
     int p = 1;
     while (p < v) p <<= 1;

@@ -132,10 +132,7 @@ int make_tmap(CUtensorMap* map, const void* base, int dtype, int dim, uint64_t r
 // checked (asynchronous) search left behind are folded into it before they are cleared, so
 // fip_search_status still sees them.  grid >= flag_words(nq) threads.
 __global__ void init_lists_kernel(float* thr, uint32_t* cnt, uint32_t* flags, uint32_t* sticky, int nq) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nq) { thr[i] = kNegInf; cnt[i] = 0u; }
-    if (i < 2 && sticky && flags[i]) atomicOr(sticky, 1u << i);
-    if (i < 2 + 2 * nq) flags[i] = 0u;
+    init_lists_thread(ListInit{thr, cnt, flags, sticky, nq}, (int)(blockIdx.x * blockDim.x + threadIdx.x));
 }
 __global__ void fold_sticky_kernel(uint32_t* flags, uint32_t* sticky) {
     if (threadIdx.x < 2 && flags[threadIdx.x]) { atomicOr(sticky, 1u << threadIdx.x); flags[threadIdx.x] = 0u; }
@@ -678,10 +675,13 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     FIP_CUDA(idx->cnt.ensure(nq));
     FIP_CUDA(idx->cand.ensure((size_t)nq * cap));
 
-    init_lists_kernel<<<(unsigned)((flag_words(nq) + 255) / 256), 256, 0, c.stream>>>(
-        idx->thr.p, idx->cnt.p, idx->overflow.p, c.level0 ? idx->sticky.p : nullptr, nq);
-    FIP_CUDA(cudaGetLastError());
-    c.launches++;
+    const ListInit linit{idx->thr.p, idx->cnt.p, idx->overflow.p, c.level0 ? idx->sticky.p : nullptr, nq};
+    if (variant != FIP_VARIANT_TENSOR) {   // (the tensor variant resets the lists inside prepare_queries_kernel)
+        init_lists_kernel<<<(unsigned)((flag_words(nq) + 255) / 256), 256, 0, c.stream>>>(
+            linit.thr, linit.cnt, linit.flags, linit.sticky, nq);
+        FIP_CUDA(cudaGetLastError());
+        c.launches++;
+    }
 
     CUtensorMap tmap_q{};
     int nq_pad = 0, n_qtiles = 0;
@@ -710,15 +710,15 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         float* ep = idx->q_eps.p;
         if (fdtype == kBF16) {
             auto* dst = reinterpret_cast<__nv_bfloat16*>(idx->qprep.p);
-            if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
-            else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
+            if (split == 2) tc::prepare_queries_kernel<__nv_bfloat16, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim, linit);
+            else tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim, linit);
         } else if (fdtype == kF16) {
             auto* dst = reinterpret_cast<__half*>(idx->qprep.p);
-            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
-            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim);
+            if (split == 2) tc::prepare_queries_kernel<__half, 2><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim, linit);
+            else tc::prepare_queries_kernel<__half, 1><<<pgrid, 256, 0, c.stream>>>(q32, dst, sc, ep, mn2, rel, nq, nq_pad, dim, linit);
         } else {
             tc::prepare_queries_kernel<float, 1><<<pgrid, 256, 0, c.stream>>>(
-                q32, reinterpret_cast<float*>(idx->qprep.p), sc, ep, mn2, rel, nq, nq_pad, dim);
+                q32, reinterpret_cast<float*>(idx->qprep.p), sc, ep, mn2, rel, nq, nq_pad, dim, linit);
         }
         FIP_CUDA(cudaGetLastError());
         c.launches++;

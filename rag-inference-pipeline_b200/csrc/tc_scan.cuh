@@ -522,7 +522,9 @@ template <typename T, int kSplit>
 __global__ void prepare_queries_kernel(const float* __restrict__ q32, T* __restrict__ qt,
                                        float* __restrict__ out_scale, float* __restrict__ out_eps,
                                        const float* __restrict__ max_norm2, float rel, int nq,
-                                       int nq_pad, int dim) {
+                                       int nq_pad, int dim, ListInit init) {
+    // fused list / flag reset (32 threads per padded query row >= 2 + 2 nq elements)
+    init_lists_thread(init, (int)(blockIdx.x * blockDim.x + threadIdx.x));
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= nq_pad) return;
