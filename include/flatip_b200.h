@@ -213,7 +213,9 @@ int64_t fip_group_get_stat(const fip_group* g, const char* key);
  * from other threads while a search is running are queued and served together as ONE batch, "profile_events" (0/1: time every scan launch with CUDA events),
  * "force_safe_mode" (0/1, testing the overflow fallback), "defer_epilogue" (0 auto: k >= 256 / 1 off /
  * 2 on: the tensor-core scan releases an accumulator right after the filter pass and writes the
- * survivors out from a shared-memory staging area afterwards, csrc/tc_scan.cuh), "dedupe" (1 default:
+ * survivors out from a shared-memory staging area afterwards, csrc/tc_scan.cuh), "fused_rescore"
+ * (1 default: the final select pass recomputes the survivors' scores exactly itself; 0: separate
+ * rescoring kernel, same bits), "dedupe" (1 default:
  * bit-identical queries inside a COALESCED host batch are searched once, on the device; 2: in every
  * host batch; 0: off), "debug_counts" (0/1: read the candidate-list lengths back after every filter
  * launch -> stats "list_entries_after_filter" / "list_max_after_filter"). */

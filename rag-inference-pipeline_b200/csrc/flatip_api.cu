@@ -248,6 +248,7 @@ struct fip_index {
     int cta_pair = 0;     // 0 = auto, 1 = single-CTA MMAs, 2 = CTA pairs (cta_group::2)
     int max_clusters[2] = {-1, -1};  // co-resident 2-CTA clusters of the pair kernel (plain / deferred epilogue)
     int defer_epilogue = 0;  // 0 = auto (k >= 256), 1 = never, 2 = always
+    int fused_rescore = 1;   // exact rescoring inside the final select pass (0: separate kernel)
     int64_t st_deferred = 0;
     int profile = 0;      // 1: bracket every scan launch with CUDA events (bench roofline)
     int debug_counts = 0; // 1: read the list lengths back after every filter launch (synchronises)
@@ -532,7 +533,8 @@ struct SearchInfo {
 int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool final_pass, float* out_d,
                   int64_t* out_i, const float* out_scale, int64_t dense_count = -1,
                   int keep_max = 0 /* > 0: exactness window on (tensor-core variant) */,
-                  bool live = false /* seed the live-threshold histogram */) {
+                  bool live = false /* seed the live-threshold histogram */,
+                  const float* rescore_q32 = nullptr /* final pass: recompute every score exactly first */) {
     SelectArgs s{};
     s.cand = idx->cand.p; s.cnt = idx->cnt.p; s.thr = idx->thr.p; s.cap = (uint32_t)cap; s.k = k;
     s.final_pass = final_pass ? 1 : 0; s.out_d = out_d; s.out_i = out_i; s.id_base = idx->cfg.id_base;
@@ -543,7 +545,22 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
     }
     if (live && !final_pass) { s.hist = idx->hist.p; s.hbase = idx->hbase.p; }
     size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
-    if (select_wants_big(cap)) {
+    if (rescore_q32) {
+        s.rs_corpus = idx->corpus; s.rs_q32 = rescore_q32; s.rs_dim = idx->cfg.dim;
+        const bool big = select_wants_big(cap);
+        auto go = [&](auto kern) -> int {
+            FIP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            kern<<<nq, big ? kSelectThreadsBig : kSelectThreads, smem, c.stream>>>(s);
+            return FIP_OK;
+        };
+        int rc;
+        switch (idx->cfg.dtype) {
+            case kF32: rc = big ? go(select_rescore_kernel_big<float>) : go(select_rescore_kernel<float>); break;
+            case kF16: rc = big ? go(select_rescore_kernel_big<__half>) : go(select_rescore_kernel<__half>); break;
+            default: rc = big ? go(select_rescore_kernel_big<__nv_bfloat16>) : go(select_rescore_kernel<__nv_bfloat16>); break;
+        }
+        if (rc) return rc;
+    } else if (select_wants_big(cap)) {
         FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         select_topk_kernel_big<<<nq, kSelectThreadsBig, smem, c.stream>>>(s);
     } else {
@@ -799,8 +816,13 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max, live);
         if (rc) return rc;
     }
-    if (rescore) {
-        // lists now hold the k' best by approximate score: recompute them exactly, then select k.
+    if (rescore && idx->fused_rescore) {
+        // lists now hold the k' best by approximate score: the final pass recomputes them exactly
+        // (fused, select.cuh) and keeps the k best.
+        rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr, -1, 0, false, q32);
+        if (rc) return rc;
+    } else if (rescore) {
+        // the same in two launches (A/B and bit-equality tests: "fused_rescore" = 0)
         const int k_res = certify ? keep_max : k_plan;   // list slots that may hold a candidate
         const int64_t warps = (int64_t)nq * ((k_res + 3) / 4);   // a warp rescoring 4 candidates at a time
         const unsigned grid = (unsigned)std::min<int64_t>((warps + 7) / 8, (int64_t)idx->num_sms * 8);
@@ -1650,6 +1672,8 @@ int fip_set_option(fip_index* idx, const char* key, int64_t value) {
         }
     } else if (k == "profile_events") {
         idx->profile = value != 0;
+    } else if (k == "fused_rescore") {
+        idx->fused_rescore = value != 0;
     } else if (k == "dedupe") {
         if (value < 0 || value > 2) return fail(FIP_ERR_INVALID, "dedupe must be 0 (off), 1 (coalesced batches) or 2 (always)");
         idx->dedupe = (int)value;

@@ -10,6 +10,8 @@
 //   * after the all-gather (merge g sorted shard lists).
 #pragma once
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "stream_scan.cuh"
 
@@ -61,7 +63,53 @@ struct SelectArgs {
     // histogram with the candidates it keeps and publishes the bucket origin.  Null = off.
     uint32_t* hist;           // [nq, 256]
     uint32_t* hbase;          // [nq]
+    // Fused exact rescoring (final pass of the tensor-core variant; null = keys are final): every
+    // candidate's score is recomputed from the stored row and the original fp32 query before the k
+    // best are picked -- the rescoring kernel and one launch + one pass over the lists saved.
+    const void* rs_corpus;    // [n_rows, dim] storage dtype of the kernel instantiation
+    const float* rs_q32;      // [nq, dim]
+    int rs_dim;
 };
+
+// Exact fp32 scores of G candidate rows for one query, by one warp: lane l accumulates the 16-byte
+// vectors l, l + 32, ... of every row in order, then the 32 partial sums are combined with xor
+// shuffles.  ONE definition for the stand-alone rescoring kernel and the fused rescoring of the
+// final select pass, so both give the same bits.  Rows are loaded G at a time: the rows are
+// scattered (one per candidate), the work is latency-bound, memory-level parallelism is what counts.
+template <typename T, int G>
+__device__ __forceinline__ void rescore_group(const T* __restrict__ corpus, const float* __restrict__ qv, int dim,
+                                              const uint32_t (&rows)[G], float (&acc)[G], int lane) {
+    constexpr int EPV = 16 / sizeof(T);
+    const int nvec = dim / EPV;
+    const T* x[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) { x[g] = corpus + (size_t)rows[g] * dim; acc[g] = 0.f; }
+    for (int v = lane; v < nvec; v += 32) {
+        uint4 raw[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) raw[g] = *reinterpret_cast<const uint4*>(x[g] + (size_t)v * EPV);
+        float4 qq[EPV / 4];
+#pragma unroll
+        for (int h = 0; h < EPV / 4; ++h) qq[h] = *reinterpret_cast<const float4*>(qv + (size_t)v * EPV + 4 * h);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float xf[EPV];
+            VecOps<T>::unpack(raw[g], xf);
+#pragma unroll
+            for (int h = 0; h < EPV / 4; ++h) {
+                acc[g] = fmaf(xf[4 * h + 0], qq[h].x, acc[g]);
+                acc[g] = fmaf(xf[4 * h + 1], qq[h].y, acc[g]);
+                acc[g] = fmaf(xf[4 * h + 2], qq[h].z, acc[g]);
+                acc[g] = fmaf(xf[4 * h + 3], qq[h].w, acc[g]);
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc[g] += __shfl_xor_sync(0xFFFFFFFFu, acc[g], off);
+}
+constexpr int kRescoreGroup = 4;
 
 constexpr int kSelectThreads = 256;
 
@@ -154,7 +202,8 @@ __device__ __forceinline__ uint64_t kth_largest_key(const uint64_t* s_keys, int 
 // (cap + next_pow2(k)) * 8 bytes.  Intermediate passes only need the k best as a SET (any order)
 // and the new threshold: radix select + compaction.  The final pass sorts those k (bitonic over
 // next_pow2(k) keys) and emits.
-template <int kThreads>
+struct NoRescore {};
+template <int kThreads, typename T>
 __device__ __forceinline__ void select_topk_body(const SelectArgs& a) {
     constexpr int kSelectThreads = kThreads;
     extern __shared__ __align__(16) uint64_t s_keys[];
@@ -171,6 +220,25 @@ __device__ __forceinline__ void select_topk_body(const SelectArgs& a) {
     for (int i = tid; i < (int)c; i += kSelectThreads) s_keys[i] = raw_to_key(list[i]);
     if (tid == 0) s_count = 0u;
     __syncthreads();
+    if constexpr (!std::is_same<T, NoRescore>::value) {
+        // exact scores for everything in the list (the filter's scores were approximate)
+        const int lane = tid & 31, warp = tid >> 5;
+        const float* qv = a.rs_q32 + (size_t)q * a.rs_dim;
+        for (int g0 = warp * kRescoreGroup; g0 < (int)c; g0 += (kSelectThreads / 32) * kRescoreGroup) {
+            uint32_t rows[kRescoreGroup];
+            float acc[kRescoreGroup];
+#pragma unroll
+            for (int g = 0; g < kRescoreGroup; ++g) rows[g] = key_row(s_keys[min(g0 + g, (int)c - 1)]);
+            rescore_group<T, kRescoreGroup>(reinterpret_cast<const T*>(a.rs_corpus), qv, a.rs_dim, rows, acc, lane);
+            if (lane < kRescoreGroup && g0 + lane < (int)c) {
+                float mine = acc[0];
+#pragma unroll
+                for (int g = 1; g < kRescoreGroup; ++g) if (lane == g) mine = acc[g];
+                s_keys[g0 + lane] = make_key(mine, key_row(s_keys[g0 + lane]));
+            }
+        }
+        __syncthreads();
+    }
     const int keep = min((int)c, a.k);
     uint64_t kth = 0ull;  // every key >= kth is kept (all of them when c <= k)
     if ((int)c > a.k) kth = kth_largest_key<kThreads>(s_keys, (int)c, a.k, s_hist, s_red);
@@ -268,9 +336,14 @@ __device__ __forceinline__ void select_topk_body(const SelectArgs& a) {
         a.out_i[(size_t)q * a.k + i] = valid ? a.id_base + (int64_t)key_row(key) : -1;
     }
 }
-__global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs a) { select_topk_body<kSelectThreads>(a); }
+__global__ void __launch_bounds__(kSelectThreads) select_topk_kernel(SelectArgs a) { select_topk_body<kSelectThreads, NoRescore>(a); }
 constexpr int kSelectThreadsBig = 1024;
-__global__ void __launch_bounds__(kSelectThreadsBig) select_topk_kernel_big(SelectArgs a) { select_topk_body<kSelectThreadsBig>(a); }
+__global__ void __launch_bounds__(kSelectThreadsBig) select_topk_kernel_big(SelectArgs a) { select_topk_body<kSelectThreadsBig, NoRescore>(a); }
+// final pass with fused exact rescoring, per storage type
+template <typename T>
+__global__ void __launch_bounds__(kSelectThreads) select_rescore_kernel(SelectArgs a) { select_topk_body<kSelectThreads, T>(a); }
+template <typename T>
+__global__ void __launch_bounds__(kSelectThreadsBig) select_rescore_kernel_big(SelectArgs a) { select_topk_body<kSelectThreadsBig, T>(a); }
 // Lists of 8 K entries and more (k >= 256) get the 1024-thread form: one CTA per SM either way (the
 // list fills the shared memory), so the per-key passes run 4x wider.
 inline bool select_wants_big(int cap) { return cap >= 8192; }
@@ -285,55 +358,27 @@ template <typename T>
 __global__ void rescore_kernel(uint64_t* __restrict__ cand, const uint32_t* __restrict__ cnt,
                                uint32_t cap, int nq, int kprime, const T* __restrict__ corpus,
                                const float* __restrict__ q32, int dim) {
-    constexpr int EPV = 16 / sizeof(T);
-    constexpr int G = 4;    // candidates a warp keeps in flight: the kernel is latency-bound (one
-                            // scattered row per candidate), so memory-level parallelism is what counts
+    constexpr int G = kRescoreGroup;
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int nvec = dim / EPV;
     const int groups = (kprime + G - 1) / G;            // per query: slots [G g, G g + G)
     for (int64_t w = warp; w < (int64_t)nq * groups; w += nwarps) {
         const int q = (int)(w / groups), s0 = (int)(w - (int64_t)q * groups) * G;
         const int have = (int)min(cnt[q], cap);
         if (s0 >= have) continue;  // warp-uniform
-        const float* qv = q32 + (size_t)q * dim;
         uint64_t key[G];
-        const T* x[G];
-#pragma unroll
-        for (int g = 0; g < G; ++g) {
-            key[g] = s0 + g < have ? cand[(size_t)q * cap + s0 + g] : 0ull;
-            x[g] = corpus + (size_t)key_row(key[g] ? key[g] : cand[(size_t)q * cap + s0]) * dim;
-        }
+        uint32_t rows[G];
         float acc[G];
 #pragma unroll
-        for (int g = 0; g < G; ++g) acc[g] = 0.f;
-        for (int v = lane; v < nvec; v += 32) {
-            uint4 raw[G];
-#pragma unroll
-            for (int g = 0; g < G; ++g) raw[g] = *reinterpret_cast<const uint4*>(x[g] + (size_t)v * EPV);
-            float4 qq[EPV / 4];
-#pragma unroll
-            for (int h = 0; h < EPV / 4; ++h) qq[h] = *reinterpret_cast<const float4*>(qv + (size_t)v * EPV + 4 * h);
-#pragma unroll
-            for (int g = 0; g < G; ++g) {
-                float xf[EPV];
-                VecOps<T>::unpack(raw[g], xf);
-#pragma unroll
-                for (int h = 0; h < EPV / 4; ++h) {
-                    acc[g] = fmaf(xf[4 * h + 0], qq[h].x, acc[g]);
-                    acc[g] = fmaf(xf[4 * h + 1], qq[h].y, acc[g]);
-                    acc[g] = fmaf(xf[4 * h + 2], qq[h].z, acc[g]);
-                    acc[g] = fmaf(xf[4 * h + 3], qq[h].w, acc[g]);
-                }
-            }
-        }
-#pragma unroll
         for (int g = 0; g < G; ++g) {
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) acc[g] += __shfl_xor_sync(0xFFFFFFFFu, acc[g], off);
-            if (lane == 0 && key[g]) cand[(size_t)q * cap + s0 + g] = make_raw_key(acc[g], key_row(key[g]));
+            key[g] = cand[(size_t)q * cap + min(s0 + g, have - 1)];
+            rows[g] = key_row(key[g]);
         }
+        rescore_group<T, G>(corpus, q32 + (size_t)q * dim, dim, rows, acc, lane);
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+            if (lane == 0 && s0 + g < have) cand[(size_t)q * cap + s0 + g] = make_raw_key(acc[g], rows[g]);
     }
 }
 

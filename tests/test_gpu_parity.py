@@ -793,3 +793,24 @@ def test_cfg5_full_size():
     idx.close()
     Dr, Ir = _c_oracle_chunked(q, 0, n, dim, "f16", k + 1, 5_000_000)
     _check_full(D, I, Dr, Ir, k)
+
+
+@pytest.mark.parametrize("dtype,n,dim,nq,k", [("f16", 60000, 768, 100, 100), ("bf16", 30000, 128, 7, 10),
+                                              ("f32", 40000, 96, 40, 20), ("f16", 50000, 384, 130, 1024)])
+def test_fused_rescore_equals_separate_kernel(dtype, n, dim, nq, k):
+    """The final select pass recomputes the survivors' scores itself (one launch and one pass over
+    the lists less); the stand-alone rescoring kernel + select must give the same bits."""
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    idx.set_variant("tensor")
+    q = synthetic.synthetic_queries(nq, dim)
+    D1, I1 = idx.search(q, k)
+    l1 = idx.stat("launches")
+    idx.set_option("fused_rescore", 0)
+    D0, I0 = idx.search(q, k)
+    assert idx.stat("launches") == l1 + 1
+    assert np.array_equal(I0, I1) and np.array_equal(D0, D1)
+    corpus = c_oracle.synthetic_corpus(0, n, dim, dtype)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k + 1)
+    _check(D1, I1, Dr[:, :k], Ir[:, :k], dtype, Dr[:, k])
+    idx.close()
