@@ -697,7 +697,8 @@ def run_ivf(args):
             "gpu_launches": launches, "roofline": roof, "cpu_baseline": cb,
             "timing": "wall clock around the blocking search call (planning and both synchronisations included)",
             "list_sizes": {"min": int(sizes.min()), "mean": float(sizes.mean()), "max": int(sizes.max())},
-            "index_build_s": build_s, "verify": verify}
+            "index_build_s": build_s, "verify": verify,
+            "coarse": {"tensor": index.stat("coarse_tensor"), "redone_queries": index.stat("coarse_redone_queries")}}
     index.close()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)

@@ -56,6 +56,15 @@ struct fivf_index {
     bool x16_failed = false;       // the copy did not fit: stay on tf32
     float x2max_host = 0.f;        // max ||x||^2 (fp16 range check)
     int tensor_format = 0;         // 0: fp16 filter copy when representable, 1: tf32 on the fp32 rows
+    // Coarse quantizer on the tensor cores: the centroid table as a flat fp32 inner-product index
+    // of its own (K1 + exact rescoring, flatip_api.cu) over AUGMENTED rows c' = [2c, -||c||^2, 0..]
+    // searched with q' = [q, 1, 0..]: <q', c'> = 2<q,c> - ||c||^2, the score the FFMA kernel
+    // computes, so "the nprobe nearest centroids" = an exact top-nprobe flat search.
+    fip_index* coarse = nullptr;
+    bool coarse_valid = false;
+    int coarse_tensor = 1;         // 0: FFMA coarse_scores_kernel + select (also used for assignment)
+    DevBuf<float> q_aug;
+    int64_t st_coarse_tensor = 0, st_coarse_redone = 0;
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
     // workspace
     DevBuf<uint64_t> ckeys, cand;
@@ -114,7 +123,45 @@ int fivf_assign_device(fivf_index* h, const float* x_dev, int64_t n, int32_t* ou
     return FIP_OK;
 }
 
+// rows [2c, -||c||^2, 0 ...] (centroids) or [q, 1, 0 ...] (queries) of width dim + 64
+__global__ void augment_rows_kernel(const float* __restrict__ src, const float* __restrict__ norm2, int n,
+                                    int dim, float scale, float* __restrict__ dst) {
+    const int wide = dim + 64;
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= (int64_t)n * wide) return;
+    const int r = (int)(i / wide), c = (int)(i - (int64_t)r * wide);
+    dst[i] = c < dim ? scale * src[(size_t)r * dim + c] : (c == dim ? (norm2 ? -norm2[r] : 1.0f) : 0.f);
+}
+
+// (Re)builds the flat index over the augmented centroids.  Enqueue only.
+int fivf_build_coarse(fivf_index* h) {
+    const int wide = h->dim + 64;
+    if (!h->coarse) {
+        fip_config c{};
+        c.dim = wide; c.dtype = FIP_F32; c.device = h->device; c.capacity_rows = h->nlist;
+        int rc = fip_create(&c, &h->coarse);
+        if (rc) return rc;
+        h->coarse->co.enabled = 0;
+    }
+    fip_index* ci = h->coarse;
+    int rc = reserve_rows(ci, h->nlist);
+    if (rc) return rc;
+    const int64_t tot = (int64_t)h->nlist * wide;
+    augment_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->cent.p, h->cnorm.p, h->nlist, h->dim,
+                                                                            2.0f, (float*)ci->corpus);
+    FIP_CUDA(cudaGetLastError());
+    FIP_CUDA(cudaMemsetAsync(ci->max_norm2.p, 0, sizeof(float), h->stream));
+    row_norm_max_kernel<float><<<(unsigned)std::min<int64_t>((h->nlist + 7) / 8, (int64_t)ci->num_sms * 16), 256, 0, h->stream>>>(
+        (const float*)ci->corpus, h->nlist, wide, ci->max_norm2.p);
+    FIP_CUDA(cudaGetLastError());
+    ci->n_rows = h->nlist;
+    ci->tmap_x_valid = false; ci->corpus_gen++;
+    h->coarse_valid = true;
+    return FIP_OK;
+}
+
 int fivf_update_cnorm(fivf_index* h) {
+    h->coarse_valid = false;
     FIP_CUDA(h->cnorm.ensure(h->nlist));
     ivf::row_norm2_kernel<<<(h->nlist + 7) / 8, 256, 0, h->stream>>>(h->cent.p, h->nlist, h->dim, h->cnorm.p);
     FIP_CUDA(cudaGetLastError());
@@ -482,7 +529,26 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     init_lists_kernel<<<(2 * nq + 2 + 255) / 256, 256, 0, h->stream>>>(h->thr.p, h->cnt.p, h->flags.p, nullptr, nq);
     FIP_CUDA(cudaGetLastError());
     // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
-    {
+    h->st_coarse_tensor = 0;
+    if (h->coarse_tensor && dim % 64 == 0 && nlist >= 256) {
+        // ... on the tensor cores: an exact flat search (K1 filter + fp32 rescoring) over the
+        // augmented centroid table; the queries get their constant 1 appended
+        if (!h->coarse_valid) { int rc = fivf_build_coarse(h); if (rc) return rc; }
+        const int wide = dim + 64;
+        FIP_CUDA(h->q_aug.ensure((size_t)nq * wide));
+        const int64_t tot = (int64_t)nq * wide;
+        augment_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(q_dev, nullptr, nq, dim, 1.0f, h->q_aug.p);
+        FIP_CUDA(cudaGetLastError());
+        int rc = search_checked(h->coarse, h->q_aug.p, nq, nprobe, h->probe_d.p, h->probe_i.p, h->stream);
+        if (rc) return rc;
+        launches += 1 + (int)h->coarse->st_launches;
+        h->st_coarse_tensor = 1;
+        h->st_coarse_redone = h->coarse->st_uncert + h->coarse->st_overflow;
+        // The certificate's error bound grows with max ||c'|| ~ ||c||^2: on data with large norms
+        // most queries would be redone on the exact streaming kernel.  Then the FFMA quantizer is
+        // the faster exact route: switch for good.
+        if (nq >= 8 && h->st_coarse_redone * 4 > nq) h->coarse_tensor = 0;
+    } else {
         dim3 grid((nlist + ivf::CO_T - 1) / ivf::CO_T, (nq + ivf::CO_T - 1) / ivf::CO_T);
         ivf::coarse_scores_kernel<<<grid, 256, 0, h->stream>>>(q_dev, nq, h->cent.p, nlist, h->cnorm.p, dim,
                                                               h->ckeys.p, (uint32_t)nlist);
@@ -861,6 +927,8 @@ void fivf_destroy(fivf_index* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->x); cudaFree(h->ids); cudaFree(h->xnorm); cudaFree(h->pend_x); cudaFree(h->x16);
+    if (h->coarse) fip_destroy(h->coarse);
+    h->q_aug.release();
     h->cent.release(); h->cnorm.release(); h->ckeys.release(); h->cand.release(); h->qnorm.release();
     h->probe_d.release(); h->thr.release(); h->sc.release(); h->q32.release(); h->out_d.release();
     h->stage.release(); h->x2max.release(); h->eps.release(); h->ones.release(); h->probe_i.release(); h->pos.release(); h->out_i.release(); h->perm.release();
@@ -1144,6 +1212,7 @@ int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
     else if (k == "profile_events") h->profile = (int)value;
     else if (k == "tensor_min_queries") h->tc_min = (int)value;
     else if (k == "tensor_format") h->tensor_format = value ? 1 : 0;
+    else if (k == "coarse_tensor") h->coarse_tensor = value ? 1 : 0;
     else if (k == "device_plan") h->device_plan = value < 0 ? 0 : (value > 2 ? 2 : (int)value);
     else return fail(FIP_ERR_INVALID, "unknown option " + k);
     return FIP_OK;
@@ -1168,6 +1237,8 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "crowded_window") return h->st_crowded;
     if (k == "crowded_window_unresolved") return h->st_crowded_final;
     if (k == "device_plan") return h->st_device_plan;
+    if (k == "coarse_tensor") return h->st_coarse_tensor;
+    if (k == "coarse_redone_queries") return h->st_coarse_redone;
     if (k == "tensor_f16") return h->st_f16;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;

@@ -342,3 +342,24 @@ def test_store_loads_faiss_ivfflat_file(tmp_path):
     assert np.array_equal(It.cpu().numpy(), I) and np.array_equal(Dt.cpu().numpy(), D)
     store.unload()
     assert not store.is_loaded
+
+
+def test_ivf_coarse_quantizer_on_tensor_cores_matches_ffma():
+    """The coarse quantizer as an exact flat search on the tensor cores (augmented centroid table
+    [2c, -||c||^2], K1 filter + fp32 rescoring) selects the same probes as the fp32 FFMA GEMM +
+    select: identical search results, and both match the oracle."""
+    from rag_inference_pipeline_b200 import IVFFlatL2Index
+
+    x, q = _data(60000, 128, 300, seed=3, clustered=True)
+    index = IVFFlatL2Index(128, 512)
+    index.train(x[:20000])
+    index.add(x)
+    D1, I1 = _check(index, q, 10, 32)
+    assert index.stat("coarse_tensor") == 1
+    assert index.stat("coarse_redone_queries") <= 30
+    index.set_option("coarse_tensor", 0)
+    D0, I0 = _check(index, q, 10, 32)
+    assert index.stat("coarse_tensor") == 0
+    ok = _stable_probe_rows(q, index.centroids(), 32)
+    assert np.array_equal(I0[ok], I1[ok]) and np.array_equal(D0[ok], D1[ok])
+    index.close()
