@@ -347,19 +347,33 @@ def test_store_loads_faiss_ivfflat_file(tmp_path):
 def test_ivf_coarse_quantizer_on_tensor_cores_matches_ffma():
     """The coarse quantizer as an exact flat search on the tensor cores (augmented centroid table
     [2c, -||c||^2], K1 filter + fp32 rescoring) selects the same probes as the fp32 FFMA GEMM +
-    select: identical search results, and both match the oracle."""
+    select on L2-normalised rows (what embedding corpora are): identical search results, both
+    matching the oracle.  On rows with large norms the certificate's global bound (max ||c'||)
+    makes most queries fall back to the exact streaming kernel, so the operator switches the
+    tensor route off by itself after the first batch -- results stay exact either way."""
     from rag_inference_pipeline_b200 import IVFFlatL2Index
 
     x, q = _data(60000, 128, 300, seed=3, clustered=True)
+    xn = (x / np.linalg.norm(x, axis=1, keepdims=True)).astype(np.float32)
+    qn = (q / np.linalg.norm(q, axis=1, keepdims=True)).astype(np.float32)
     index = IVFFlatL2Index(128, 512)
-    index.train(x[:20000])
-    index.add(x)
-    D1, I1 = _check(index, q, 10, 32)
-    assert index.stat("coarse_tensor") == 1
-    assert index.stat("coarse_redone_queries") <= 30
+    index.train(xn[:20000])
+    index.add(xn)
+    D1, I1 = _check(index, qn, 10, 32, scale=0.1)
+    assert index.stat("coarse_tensor") == 1 and index.stat("coarse_redone_queries") <= 30
+    D1b, I1b = index.search(qn, 10, nprobe=32)
+    assert index.stat("coarse_tensor") == 1                      # still on
     index.set_option("coarse_tensor", 0)
-    D0, I0 = _check(index, q, 10, 32)
+    D0, I0 = _check(index, qn, 10, 32, scale=0.1)
     assert index.stat("coarse_tensor") == 0
-    ok = _stable_probe_rows(q, index.centroids(), 32)
+    ok = _stable_probe_rows(qn, index.centroids(), 32, 0.1)
     assert np.array_equal(I0[ok], I1[ok]) and np.array_equal(D0[ok], D1[ok])
     index.close()
+    big = IVFFlatL2Index(128, 512)                               # rows of norm ~45: bound too loose
+    big.train(x[:20000])
+    big.add(x)
+    _check(big, q, 10, 32)
+    assert big.stat("coarse_tensor") == 1 and big.stat("coarse_redone_queries") > 75
+    _check(big, q, 10, 32)
+    assert big.stat("coarse_tensor") == 0                        # switched itself off
+    big.close()
