@@ -544,7 +544,8 @@ int launch_select(SearchCtx& c, fip_index* idx, int nq, int k, int cap, bool fin
         s.uncert = idx->overflow.p + 1;
     }
     if (live && !final_pass) { s.hist = idx->hist.p; s.hbase = idx->hbase.p; }
-    size_t smem = ((size_t)cap + (size_t)next_pow2(std::min(k, cap))) * sizeof(uint64_t);
+    // (a finishing pass also parks the window's candidates, up to keep_max, behind the list)
+    size_t smem = ((size_t)cap + (size_t)std::max(next_pow2(std::min(k, cap)), rescore_q32 ? keep_max : 0)) * sizeof(uint64_t);
     if (rescore_q32) {
         s.rs_corpus = idx->corpus; s.rs_q32 = rescore_q32; s.rs_dim = idx->cfg.dim;
         const bool big = select_wants_big(cap);
@@ -791,17 +792,21 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         if (keep_max > 0) { a.win_eps = idx->q_eps.p; a.win_scale = idx->q_scale.p; }
     }
     int phases = 0;
-    // phase 0: no threshold yet, every score of the first rows is written (slot = row).  For small
-    // k a 1024-row sample gives a good enough first threshold (the filter launch raises it live)
-    // and the first select pass sorts 1024 instead of 4096 keys per query: at batch 32 that pass
-    // is a visible part of a 0.3 ms search.
-    const int64_t dense_rows = (!mode.safe && live && k_plan <= 64) ? std::min(1024, cap) : cap;
+    // phase 0: no threshold yet, every score of the first rows is written (slot = row).  A sample of
+    // 8 k' rows (at least 1024) gives a good enough first threshold -- the filter launch raises it
+    // live -- and the first select pass sorts that many keys per query instead of a whole list:
+    // at batch 32 that pass is a visible part of a 0.3 ms search.
+    const int64_t dense_rows = (!mode.safe && live) ? std::min(std::max(1024, 8 * next_pow2(k_plan)), cap) : cap;
     int64_t m = std::min<int64_t>(n, dense_rows);
     int rc = scan(0, m, true);
     if (rc) return rc;
     int64_t pos = m;
     phases++;
-    rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, m, keep_max, live);
+    // After the LAST scan of a certified tensor-core search ONE pass finishes the query: window on the
+    // approximate scores, exact rescoring of what is inside, the k best sorted and emitted.
+    const bool finish = rescore && certify && idx->fused_rescore && keep_max > 0;
+    if (pos == n && finish) rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr, m, keep_max, false, q32);
+    else rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, m, keep_max, live);
     if (rc) return rc;
     while (pos < n) {
         if (mode.safe) m = std::max<int64_t>(256, (int64_t)(cap - std::max(k_plan, keep_max)) / 256 * 256);
@@ -817,10 +822,13 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         }
         pos += m;
         phases++;
-        rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max, live);
+        if (pos == n && finish) rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr, -1, keep_max, false, q32);
+        else rc = launch_select(c, idx, nq, k_sel, cap, pos == n && !rescore, out_d, out_i, out_scale, -1, keep_max, live);
         if (rc) return rc;
     }
-    if (rescore && idx->fused_rescore) {
+    if (finish) {
+        // done by the finishing pass above
+    } else if (rescore && idx->fused_rescore) {
         // lists now hold the k' best by approximate score: the final pass recomputes them exactly
         // (fused, select.cuh) and keeps the k best.
         rc = launch_select(c, idx, nq, k_out, cap, true, out_d, out_i, nullptr, -1, 0, false, q32);

@@ -221,7 +221,37 @@ __device__ __forceinline__ void select_topk_body(const SelectArgs& a) {
     if (tid == 0) s_count = 0u;
     __syncthreads();
     if constexpr (!std::is_same<T, NoRescore>::value) {
-        // exact scores for everything in the list (the filter's scores were approximate)
+        if (a.win_eps && (int)c > a.k) {
+            // FINISH mode (the pass after the last filter launch): first the exactness window on
+            // the APPROXIMATE scores -- exactly what an intermediate pass would keep -- compacted
+            // into the spare region behind the list, so that only those candidates are rescored.
+            const uint64_t kth_a = kth_largest_key<kThreads>(s_keys, (int)c, a.k, s_hist, s_red);
+            uint64_t lim = kth_a - 1ull;
+            const float win = 2.0f * a.win_eps[q] / a.win_scale[q];
+            const float ta = key_score(kth_a);
+            if (win > 0.f && ta > kNegInf)
+                lim = ((uint64_t)orderable_f32(nextafterf(ta - win, kNegInf)) << 32) | 0xFFFFFFFFull;
+            uint64_t* s_tmp = s_keys + a.cap;
+            for (int i = tid; i < (int)c; i += kSelectThreads) {
+                const uint64_t x = s_keys[i];
+                if (x > lim) {
+                    const uint32_t slot = atomicAdd(&s_count, 1u);
+                    if ((int)slot < a.keep_max) s_tmp[slot] = x;
+                }
+            }
+            __syncthreads();
+            uint32_t kept = s_count;
+            if ((int)kept > a.keep_max) {   // crowded window: flagged, the host redoes the query
+                if (tid == 0) { a.uncert[0] = 1u; a.uncert[flag_slot(q)] = 1u; }
+                kept = (uint32_t)a.keep_max;
+            }
+            __syncthreads();
+            for (int i = tid; i < (int)kept; i += kSelectThreads) s_keys[i] = s_tmp[i];
+            if (tid == 0) s_count = 0u;
+            c = kept;
+            __syncthreads();
+        }
+        // exact scores for everything (left) in the list (the filter's scores were approximate)
         const int lane = tid & 31, warp = tid >> 5;
         const float* qv = a.rs_q32 + (size_t)q * a.rs_dim;
         for (int g0 = warp * kRescoreGroup; g0 < (int)c; g0 += (kSelectThreads / 32) * kRescoreGroup) {
