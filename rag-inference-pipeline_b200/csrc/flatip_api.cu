@@ -792,11 +792,17 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         if (keep_max > 0) { a.win_eps = idx->q_eps.p; a.win_scale = idx->q_scale.p; }
     }
     int phases = 0;
-    // phase 0: no threshold yet, every score of the first rows is written (slot = row).  A sample of
-    // 8 k' rows (at least 1024) gives a good enough first threshold -- the filter launch raises it
-    // live -- and the first select pass sorts that many keys per query instead of a whole list:
-    // at batch 32 that pass is a visible part of a 0.3 ms search.
-    const int64_t dense_rows = (!mode.safe && live) ? std::min(std::max(1024, 8 * next_pow2(k_plan)), cap) : cap;
+    // phase 0: no threshold yet, every score of the first rows is written (slot = row).  For small
+    // k a sample smaller than the list capacity gives a good enough first threshold -- the filter
+    // launch raises it live -- and the first select pass sorts that many keys per query instead of
+    // a whole list: at batch 32 that pass is a visible part of a 0.3 ms search.
+    // Lower bound: every CTA filters with the threshold it fetched up to two tiles earlier, so about
+    // 2 x SMs x 256 rows are scanned against the FIRST threshold whatever the histogram does; at a
+    // pass rate of k' / sample those must fit the list with room to spare (factor 2), or every query
+    // overflows and is redone in safe mode (what tests/test_gpu_parity.py caught with k = 100).
+    const int64_t first_wave = 2ll * idx->num_sms * tc::BN;
+    const int64_t need = ((int64_t)k_plan * first_wave * 2 / cap + 255) / 256 * 256;
+    const int64_t dense_rows = (!mode.safe && live) ? std::min<int64_t>(std::max<int64_t>(1024, need), cap) : cap;
     int64_t m = std::min<int64_t>(n, dense_rows);
     int rc = scan(0, m, true);
     if (rc) return rc;
