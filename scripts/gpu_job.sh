@@ -1,13 +1,14 @@
 #!/bin/bash
 # Round-2 GPU job (overwritten per gpurun call; results land in gpurun_out/ and are summarised under profiles/).
 mkdir -p gpurun_out
-T=r2l
-timeout 1800 python -m pytest tests -m gpu -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/${T}_pytest.log | cut -c1-300
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke rc=$?"
-for w in cfg2 cfg5 cfg4; do
-  timeout 300 python bench.py --workload $w --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_bench_${w}.json 2> gpurun_out/${T}_bench_${w}.err; echo "bench $w rc=$?"; python -c "
-import json; d=json.load(open('gpurun_out/${T}_bench_${w}.json')); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['whole_search_frac'], d['roofline']['kernel_share_of_step'], d['gpu_launches'], d['verify']['ok'], d['verify']['ids_sha256'][:10])"; tail -2 gpurun_out/${T}_bench_${w}.err
+T=r2m
+N=$(nvidia-smi -L | wc -l); echo "gpus=$N"
+timeout 900 python -m pytest tests/test_gpu_group.py tests/test_gpu_multi.py -m gpu -q > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/${T}_pytest.log | cut -c1-300
+g=$N
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 29741 bench.py --gpus $g --steps 20 --warmup 5 > gpurun_out/${T}_bench_cfg3_n$g.json 2> gpurun_out/${T}_bench_cfg3_n$g.err; echo "bench cfg3 n$g rc=$?"; python -c "
+import json; d=json.load(open('gpurun_out/${T}_bench_cfg3_n$g.json')); r=d['roofline']; print(d['value'], d['ms_per_step'], 'e2e', d['e2e']['value'], 'ranks', r['per_rank_scan_ms'], 'frac', r['frac'], 'whole', r['whole_search_frac'], 'share', r['kernel_share_of_step'], d['gpu_launches'], d['verify']['ok'], d['verify']['ids_sha256'][:12], d['e2e']['result_equals_device_loop'])"; tail -2 gpurun_out/${T}_bench_cfg3_n$g.err | cut -c1-300
+for g in 8 4 2; do
+  [ $g -le $N ] || continue
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $g --master-addr 127.0.0.1 --master-port 2975$g scripts/sweep_sharded.py > gpurun_out/${T}_sweep_cfg4_n$g.jsonl 2> gpurun_out/${T}_sweep_n$g.err; echo "sweep n$g rc=$?"; cut -c1-260 gpurun_out/${T}_sweep_cfg4_n$g.jsonl; tail -2 gpurun_out/${T}_sweep_n$g.err | cut -c1-200
 done
-timeout 300 python bench.py --rows 12500000 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/${T}_bench_shard.json 2> gpurun_out/${T}_bench_shard.err; echo "bench shard rc=$?"; python -c "
-import json; d=json.load(open('gpurun_out/${T}_bench_shard.json')); print(d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['whole_search_frac'], d['roofline']['kernel_share_of_step'], d['gpu_launches'])"
-timeout 600 python scripts/sweep.py --batches 1,2,4,8,32,128,256,512,1024 > gpurun_out/${T}_sweep.jsonl 2> gpurun_out/${T}_sweep.err; cut -c1-200 gpurun_out/${T}_sweep.jsonl
+timeout 600 python scripts/sweep.py > gpurun_out/${T}_sweep_cfg4_n1.jsonl 2> gpurun_out/${T}_sweep_n1.err; echo "sweep n1 rc=$?"; cut -c1-260 gpurun_out/${T}_sweep_cfg4_n1.jsonl
