@@ -1578,6 +1578,7 @@ int fip_exchange_connect_local(fip_exchange* x, fip_exchange* const* all) {
     if (!x || !all) return fail(FIP_ERR_INVALID, "null argument");
     std::lock_guard<std::mutex> lock(x->mu);
     FIP_CUDA(cudaSetDevice(x->device));
+    x->share = 1;
     for (int r = 0; r < x->world; ++r) {
         if (r == x->rank) continue;
         const fip_exchange* o = all[r];
