@@ -216,3 +216,47 @@ def test_unrecognised_file(tmp_path):
     p.write_bytes(b"IwFl" + b"\0" * 100)   # an IVF fourcc: not a flat index
     with pytest.raises(ValueError, match="unrecognised"):
         index_io.read_header(str(p))
+
+
+def test_group_abi_fails_loudly_without_a_gpu(native_lib, tmp_path):
+    """The multi-device entry points behave like the single-device ones on a box without a GPU:
+    argument errors are reported as such, everything else is FIP_ERR_NODEVICE -- never a CPU path."""
+    import ctypes
+
+    from rag_inference_pipeline_b200 import B200FlatIPStore, _native
+    from rag_inference_pipeline_b200.group import FlatIPGroup, calibrate_devices
+
+    if gpu_available():
+        pytest.skip("this check is for boxes without a GPU")
+    cfg = _native.FipConfig(dim=64, dtype=1, device=0, reserved=0, capacity_rows=0, id_base=0)
+    devs = (ctypes.c_int32 * 2)(0, 1)
+    h = ctypes.c_void_p()
+    assert native_lib.fip_group_create(ctypes.byref(cfg), devs, 0, 100, ctypes.byref(h)) == _native.FIP_ERR_INVALID
+    assert native_lib.fip_group_create(ctypes.byref(cfg), devs, 2, -1, ctypes.byref(h)) == _native.FIP_ERR_INVALID
+    w = (ctypes.c_double * 2)(1.0, 0.0)
+    assert native_lib.fip_group_create_weighted(ctypes.byref(cfg), devs, 2, 100, w, ctypes.byref(h)) in (
+        _native.FIP_ERR_INVALID, _native.FIP_ERR_NODEVICE)
+    assert native_lib.fip_group_create(ctypes.byref(cfg), devs, 2, 100, ctypes.byref(h)) == _native.FIP_ERR_NODEVICE
+    assert not h.value
+    assert native_lib.fip_group_search(None, None, 1, 1, None, None) == _native.FIP_ERR_INVALID
+    flagged = ctypes.c_int32(7)
+    assert native_lib.fip_search_status(None, ctypes.byref(flagged)) == _native.FIP_ERR_INVALID
+    with pytest.raises(_native.FlatIPError) as e:
+        FlatIPGroup(64, "f16", [0, 1], 1000)
+    assert e.value.code == _native.FIP_ERR_NODEVICE
+    with pytest.raises(_native.FlatIPError):
+        calibrate_devices([0], 64, "f16", rows=10)           # bad argument (rows < 1024)
+    with pytest.raises(_native.FlatIPError):
+        calibrate_devices([0], 64, "f16", rows=4096, seconds=0.01)   # no device
+    store = B200FlatIPStore(_settings("synthetic:1000?dim=768&dtype=f16"), {"devices": [0, 1]})
+    with pytest.raises(RuntimeError, match="FAISS index loading failed"):
+        store.load()
+    assert not store.is_loaded
+
+
+def test_store_device_list_parsing():
+    from rag_inference_pipeline_b200.store import _parse_devices
+
+    assert _parse_devices(None) is None and _parse_devices("") is None
+    assert _parse_devices("0,1, 2") == [0, 1, 2] and _parse_devices([3, 1]) == [3, 1]
+    assert _parse_devices("5") == [5]
