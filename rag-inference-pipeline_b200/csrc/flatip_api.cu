@@ -642,8 +642,9 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     if (variant == FIP_VARIANT_AUTO) {
         // Arithmetic intensity of a flat scan is 2*nq / sizeof(storage) flop per corpus byte.  The
         // CUDA-core kernel (FMA + unpack + LDS per element) keeps up with HBM up to ~2 flop/byte
-        // (measured: 0.94-0.98 of the copy bandwidth at nq = 2 for 16-bit and nq = 4 for fp32
-        // storage, 0.73 at twice that); above it the tensor pipe is needed to stay on the HBM
+        // (measured: 1.00 of the copy bandwidth at nq = 1 and 0.89-0.92 at nq = 2 for 16-bit storage
+        // -- where the tensor-core kernel holds 1.05 from nq = 2 on, so 16-bit storage streams only
+        // single queries -- and 0.94-0.98 at nq = 4 for fp32 storage); above it the tensor pipe is needed to stay on the HBM
         // roof, and above ~210 flop/byte (nq > ~210 for 16-bit storage) the tensor pipe itself is
         // the roof.  The streaming kernel maps the 32 lanes of a warp onto the 16-byte vectors of a
         // row, so rows shorter than 1 KB (2 x 512 bytes) leave lanes idle (0.68-0.83 measured at
@@ -654,7 +655,7 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
         // would: it wins at every batch size)
         const int stream_max = idx->stream_max_batch > 0 ? idx->stream_max_batch
                                : copy16                  ? 0
-                                                         : (long_rows ? dtype_size(dtype) : 0);
+                                                         : (long_rows ? (dtype == kF32 ? 4 : 1) : 0);
         variant = (tc_ok && nq > stream_max) ? FIP_VARIANT_TENSOR : FIP_VARIANT_STREAM;
     }
     if (variant == FIP_VARIANT_TENSOR && !tc_ok)
