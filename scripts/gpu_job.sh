@@ -1,13 +1,9 @@
 #!/bin/bash
 # Round-2 GPU job (overwritten per gpurun call; results land in gpurun_out/ and are summarised under profiles/).
 mkdir -p gpurun_out
-T=r2n
-for f in 1 0 1 0; do
-timeout 300 python bench.py --rows 12500000 --steps 20 --warmup 3 --no-cpu-baseline --opt fused_rescore=$f > gpurun_out/${T}_bench_shard_f$f.json 2> gpurun_out/${T}_bench_shard_f$f.err; echo "bench shard fused=$f rc=$?"; python -c "
-import json; d=json.load(open('gpurun_out/${T}_bench_shard_f$f.json')); r=d['roofline']; print(d['value'], d['ms_per_step'], r['all_scan_launches_ms_per_step'], 'nonscan', d['ms_per_step']-r['all_scan_launches_ms_per_step'], d['gpu_launches'])"
-done
-for f in 1 0; do
-CMD="python bench.py --rows 12500000 --steps 2 --warmup 3 --no-cpu-baseline --opt fused_rescore=$f"
-$CMD > gpurun_out/${T}_plain_$f.log 2>&1 && timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches_shard_f$f.csv $CMD > gpurun_out/${T}_ncu_$f.log 2>&1; echo "ncu f=$f rc=$?"
-done
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5
+T=r2o
+timeout 1800 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/${T}_pytest.log | cut -c1-300
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.log 2>&1; echo "smoke rc=$?"; tail -4 gpurun_out/${T}_smoke.log
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/${T}_bench_cfg3_n1.json 2> gpurun_out/${T}_bench_cfg3_n1.err; echo "bench default rc=$?"; cut -c1-3500 gpurun_out/${T}_bench_cfg3_n1.json; tail -2 gpurun_out/${T}_bench_cfg3_n1.err
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_reference.json 2> gpurun_out/${T}_bench_reference.err; echo "reference rc=$?"; cut -c1-1800 gpurun_out/${T}_bench_reference.json
+timeout 300 python scripts/sweep.py --batches 1,2,3,4 > gpurun_out/${T}_sweep.jsonl 2> gpurun_out/${T}_sweep.err; cut -c1-230 gpurun_out/${T}_sweep.jsonl
