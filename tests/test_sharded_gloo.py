@@ -174,3 +174,23 @@ def test_weighted_shard_ranges():
     assert [b for b, _ in eq] == [0, 2560, 5120, 7424] and eq[-1][1] == 10_000
     with pytest.raises(ValueError):
         shard_range(100, 0, 2, [1.0, 0.0])
+
+
+def test_shard_ranges_property():
+    """Any positive weights, any size: contiguous, ordered, exact cover; interior boundaries on tiles."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=200, deadline=None)
+    @given(st.integers(0, 3_000_000_000), st.lists(st.floats(0.05, 20.0), min_size=1, max_size=16))
+    def check(total, weights):
+        g = len(weights)
+        prev = 0
+        for r in range(g):
+            b, e = shard_range(total, r, g, weights)
+            assert b == prev and b <= e <= total
+            if 0 < r and b < total:
+                assert b % 256 == 0
+            prev = e
+        assert prev == total
+
+    check()
