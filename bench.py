@@ -645,6 +645,7 @@ def run_ivf(args):
         return
 
     index.set_option("profile_events", 1)
+    index.set_option("coarse_tensor", args.ivf_coarse)
     qd = torch.from_numpy(q).cuda()
     D = torch.empty((B, k), dtype=torch.float32, device="cuda")
     I = torch.empty((B, k), dtype=torch.int64, device="cuda")
@@ -698,7 +699,7 @@ def run_ivf(args):
             "timing": "wall clock around the blocking search call (planning and both synchronisations included)",
             "list_sizes": {"min": int(sizes.min()), "mean": float(sizes.mean()), "max": int(sizes.max())},
             "index_build_s": build_s, "verify": verify,
-            "coarse": {"tensor": index.stat("coarse_tensor"), "redone_queries": index.stat("coarse_redone_queries")}}
+            "coarse": {"tensor": index.stat("coarse_tensor")}}
     index.close()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
@@ -712,6 +713,7 @@ def main():
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["ivf"], default="cfg3")
     ap.add_argument("--ivf-train", type=int, default=0, help="--workload ivf: rows the quantizer is trained on")
+    ap.add_argument("--ivf-coarse", type=int, default=1, help="--workload ivf: 1 = coarse quantizer on the tensor cores, 0 = FFMA")
     ap.add_argument("--rows", type=int, default=0, help="override total corpus rows")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--k", type=int, default=0)

@@ -79,11 +79,10 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
  * "device_plan" (default 1: for batches of >= 1024 (query, probe) pairs the probe table is inverted into
  * work lists by GPU kernels and only their sizes are read back; 2: for every batch; 0: always on the
  * host, which safe mode does anyway).
- * "coarse_tensor" (1 default: the coarse quantizer runs as an exact flat search on the tensor cores --
- * K1 + fp32 rescoring over the augmented centroid table [2c, -||c||^2], dim % 64 == 0 and nlist >= 256;
- * it switches itself off when the certificate has to redo more than a quarter of a batch, i.e. on
- * data with very large norms; 0: fp32 FFMA GEMM + select).
- * stats of the last search: "coarse_tensor" (1: used), "coarse_redone_queries", "launches", "phases", "tiles", "tiles16", "rows_scanned",
+ * "coarse_tensor" (1 default, nlist >= 256: the coarse quantizer runs on the tensor cores with
+ * fp32-accurate scores -- every fp32 value split into three bf16 terms, the six significant products
+ * laid side by side along K (K' = 6 dim), K1's dense mode, fp32 accumulation; 0: fp32 FFMA GEMM).
+ * stats of the last search: "coarse_tensor" (1: used), "launches", "phases", "tiles", "tiles16", "rows_scanned",
  * "pairs_scored", "distinct_rows" (rows of the lists probed by at least one query), "scan_ns",
  * "tensor_items", "tensor_pairs", "crowded_window" (1: the tf32 filter's exactness window overflowed
  * for some query and the batch was redone with the fp32 filter, then -- clusters of more than 2k + 64

@@ -865,6 +865,55 @@ int run_search(SearchCtx& c, const float* q32, int nq, int k, float* out_d, int6
     return FIP_OK;
 }
 
+// K1 in DENSE mode only: keys[q * cap + r] = raw key (score bits, row r) of <q, x_r> for every stored
+// row r < n_rows <= cap, nothing else (no thresholds, no selection).  The operands are rounded to
+// the index's 16-bit storage type by the tensor-core path, so this is for callers that feed values
+// already representable there -- the IVF coarse quantizer's bf16 x 3 split (ivf_api.cuh), which gets
+// fp32-accurate inner products out of six bf16 products laid side by side along K.  Enqueue only.
+int dense_scores(fip_index* idx, const float* q32, int nq, uint64_t* keys, uint32_t cap, cudaStream_t stream,
+                 int* launches) {
+    const int dim = idx->cfg.dim, dtype = idx->cfg.dtype;
+    const int64_t n = idx->n_rows;
+    if (dtype == kF32 || (dim * 2) % tc::BK_BYTES != 0 || n > (int64_t)cap || n == 0)
+        return fail(FIP_ERR_INVALID, "dense_scores: needs a 16-bit index with 128-byte-multiple rows that fits the key rows");
+    SearchCtx c{idx, stream};
+    int n_qtiles = (nq + tc::BM - 1) / tc::BM;
+    const bool pair = n_qtiles >= 2 && (n_qtiles % 2 == 0 || n_qtiles >= 7);
+    if (pair) n_qtiles = (n_qtiles + 1) / 2 * 2;
+    const int nq_pad = n_qtiles * tc::BM;
+    FIP_CUDA(idx->qprep.ensure((size_t)nq_pad * dim * 2));
+    FIP_CUDA(idx->q_scale.ensure(nq));
+    FIP_CUDA(idx->q_eps.ensure(nq));
+    FIP_CUDA(idx->thr.ensure(nq));
+    FIP_CUDA(idx->cnt.ensure(nq));
+    FIP_CUDA(idx->overflow.ensure(std::max<size_t>(flag_words(nq), flag_words(4096))));
+    const ListInit linit{idx->thr.p, idx->cnt.p, idx->overflow.p, nullptr, nq};
+    const unsigned pgrid = (nq_pad + 7) / 8;
+    if (dtype == kBF16)
+        tc::prepare_queries_kernel<__nv_bfloat16, 1><<<pgrid, 256, 0, stream>>>(
+            q32, reinterpret_cast<__nv_bfloat16*>(idx->qprep.p), idx->q_scale.p, idx->q_eps.p, idx->max_norm2.p, 0.f, nq, nq_pad, dim, linit);
+    else
+        return fail(FIP_ERR_INVALID, "dense_scores: bf16 storage only (fp16 queries are rescaled per query)");
+    FIP_CUDA(cudaGetLastError());
+    CUtensorMap tmap_q{};
+    int rc = make_tmap(&tmap_q, idx->qprep.p, dtype, dim, (uint64_t)nq_pad);
+    if (rc) return rc;
+    if (!idx->tmap_x_valid) {
+        rc = make_tmap(&idx->tmap_x, idx->corpus, dtype, dim, (uint64_t)n);
+        if (rc) return rc;
+        idx->tmap_x_valid = true;
+    }
+    c.tmap_scan = &idx->tmap_x;
+    ScanArgs a{};
+    a.corpus = idx->corpus; a.n_rows = n; a.dim = dim; a.nq = nq; a.dtype = dtype;
+    a.thr = idx->thr.p; a.cnt = idx->cnt.p; a.cand = keys; a.cap = cap;
+    a.row_begin = 0u; a.row_end = (uint32_t)n; a.dense = 1;
+    rc = launch_tc_phase(c, a, tmap_q, n_qtiles, 1, pair, false);
+    if (rc) return rc;
+    if (launches) *launches += 1 + c.launches;
+    return FIP_OK;
+}
+
 // Flags of the search just enqueued: copy_flags_async enqueues the D2H copy, parse_flags (after the
 // stream has been synchronised) appends the flagged queries, translated through `ids` (null =
 // identity), to `over` / `uncert`.  collect_flags = both with the synchronisation in between.

@@ -56,15 +56,20 @@ struct fivf_index {
     bool x16_failed = false;       // the copy did not fit: stay on tf32
     float x2max_host = 0.f;        // max ||x||^2 (fp16 range check)
     int tensor_format = 0;         // 0: fp16 filter copy when representable, 1: tf32 on the fp32 rows
-    // Coarse quantizer on the tensor cores: the centroid table as a flat fp32 inner-product index
-    // of its own (K1 + exact rescoring, flatip_api.cu) over AUGMENTED rows c' = [2c, -||c||^2, 0..]
-    // searched with q' = [q, 1, 0..]: <q', c'> = 2<q,c> - ||c||^2, the score the FFMA kernel
-    // computes, so "the nprobe nearest centroids" = an exact top-nprobe flat search.
+    // Coarse quantizer on the tensor cores with fp32-accurate scores: every fp32 value v is split
+    // into three bf16 terms v = v1 + v2 + v3 (24 mantissa bits, exact), and <q, c> ~= q1c1 + q1c2 +
+    // q2c1 + q1c3 + q2c2 + q3c1 (the dropped terms are below 2^-24 relative) becomes ONE bf16 GEMM
+    // by laying the six products side by side along K: q' = [q1 q1 q2 q1 q2 q3], c' = [c1 c2 c1 c3 c2
+    // c1] (K' = 6 dim).  `coarse` holds the c' rows as a bf16 flat index; K1's dense mode
+    // (dense_scores, flatip_api.cu) writes the whole [nq, nlist] score matrix as candidate keys,
+    // one small kernel turns <q,c> into 2<q,c> - ||c||^2, and the usual select picks the nprobe
+    // best.  fp32 accumulation in the tensor core: the scores differ from the FFMA kernel's by
+    // summation order only (~1e-7 relative), like any two fp32 GEMMs.
     fip_index* coarse = nullptr;
     bool coarse_valid = false;
-    int coarse_tensor = 1;         // 0: FFMA coarse_scores_kernel + select (also used for assignment)
+    int coarse_tensor = 1;         // 0: FFMA coarse_scores_kernel (always used for assignment at add time)
     DevBuf<float> q_aug;
-    int64_t st_coarse_tensor = 0, st_coarse_redone = 0;
+    int64_t st_coarse_tensor = 0;
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
     // workspace
     DevBuf<uint64_t> ckeys, cand;
@@ -123,22 +128,40 @@ int fivf_assign_device(fivf_index* h, const float* x_dev, int64_t n, int32_t* ou
     return FIP_OK;
 }
 
-// rows [2c, -||c||^2, 0 ...] (centroids) or [q, 1, 0 ...] (queries) of width dim + 64
-__global__ void augment_rows_kernel(const float* __restrict__ src, const float* __restrict__ norm2, int n,
-                                    int dim, float scale, float* __restrict__ dst) {
-    const int wide = dim + 64;
+// v = v1 + v2 + v3 in bf16 (exact for fp32 v); row layouts along K' = 6 dim:
+//   kQuery: [v1 v1 v2 v1 v2 v3]   (written as fp32 values that ARE bf16 numbers: the tensor-core
+//                                   path's own rounding of the queries is then exact)
+//   else  : [v1 v2 v1 v3 v2 v1]   (written as bf16 into the coarse index's storage)
+template <bool kQuery, typename Out>
+__global__ void split3_rows_kernel(const float* __restrict__ src, int n, int dim, Out* __restrict__ dst) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= (int64_t)n * wide) return;
-    const int r = (int)(i / wide), c = (int)(i - (int64_t)r * wide);
-    dst[i] = c < dim ? scale * src[(size_t)r * dim + c] : (c == dim ? (norm2 ? -norm2[r] : 1.0f) : 0.f);
+    if (i >= (int64_t)n * dim) return;
+    const int r = (int)(i / dim), c = (int)(i - (int64_t)r * dim);
+    const float v = src[i];
+    const float v1 = __bfloat162float(__float2bfloat16_rn(v));
+    const float v2 = __bfloat162float(__float2bfloat16_rn(v - v1));
+    const float v3 = __bfloat162float(__float2bfloat16_rn(v - v1 - v2));
+    const float seg[6] = {v1, kQuery ? v1 : v2, kQuery ? v2 : v1, kQuery ? v1 : v3, v2, kQuery ? v3 : v1};
+    Out* o = dst + (size_t)r * 6 * dim + c;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) o[(size_t)t * dim] = to_storage<Out>(seg[t]);
+}
+// keys[q][c]: score <q,c>  ->  2 <q,c> - ||c||^2 (the coarse score; same raw-key layout)
+__global__ void coarse_bias_kernel(uint64_t* __restrict__ keys, const float* __restrict__ cnorm, int nq, int nlist) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= (int64_t)nq * nlist) return;
+    const int c = (int)(i % nlist);
+    const uint64_t k = keys[i];
+    const float s = fmaf(2.0f, __uint_as_float((uint32_t)(k >> 32)), -cnorm[c]);
+    keys[i] = ((uint64_t)__float_as_uint(s) << 32) | (k & 0xFFFFFFFFull);
 }
 
-// (Re)builds the flat index over the augmented centroids.  Enqueue only.
+// (Re)builds the bf16 x 3 centroid table.  Enqueue only.
 int fivf_build_coarse(fivf_index* h) {
-    const int wide = h->dim + 64;
+    const int wide = 6 * h->dim;
     if (!h->coarse) {
         fip_config c{};
-        c.dim = wide; c.dtype = FIP_F32; c.device = h->device; c.capacity_rows = h->nlist;
+        c.dim = wide; c.dtype = FIP_BF16; c.device = h->device; c.capacity_rows = h->nlist;
         int rc = fip_create(&c, &h->coarse);
         if (rc) return rc;
         h->coarse->co.enabled = 0;
@@ -146,13 +169,9 @@ int fivf_build_coarse(fivf_index* h) {
     fip_index* ci = h->coarse;
     int rc = reserve_rows(ci, h->nlist);
     if (rc) return rc;
-    const int64_t tot = (int64_t)h->nlist * wide;
-    augment_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(h->cent.p, h->cnorm.p, h->nlist, h->dim,
-                                                                            2.0f, (float*)ci->corpus);
-    FIP_CUDA(cudaGetLastError());
-    FIP_CUDA(cudaMemsetAsync(ci->max_norm2.p, 0, sizeof(float), h->stream));
-    row_norm_max_kernel<float><<<(unsigned)std::min<int64_t>((h->nlist + 7) / 8, (int64_t)ci->num_sms * 16), 256, 0, h->stream>>>(
-        (const float*)ci->corpus, h->nlist, wide, ci->max_norm2.p);
+    const int64_t tot = (int64_t)h->nlist * h->dim;
+    split3_rows_kernel<false, __nv_bfloat16><<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(
+        h->cent.p, h->nlist, h->dim, (__nv_bfloat16*)ci->corpus);
     FIP_CUDA(cudaGetLastError());
     ci->n_rows = h->nlist;
     ci->tmap_x_valid = false; ci->corpus_gen++;
@@ -530,24 +549,29 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     FIP_CUDA(cudaGetLastError());
     // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
     h->st_coarse_tensor = 0;
-    if (h->coarse_tensor && dim % 64 == 0 && nlist >= 256) {
-        // ... on the tensor cores: an exact flat search (K1 filter + fp32 rescoring) over the
-        // augmented centroid table; the queries get their constant 1 appended
+    if (h->coarse_tensor && nlist >= 256) {
+        // ... on the tensor cores (bf16 x 3 split, see fivf_index::coarse): dense K1 pass, bias, select
         if (!h->coarse_valid) { int rc = fivf_build_coarse(h); if (rc) return rc; }
-        const int wide = dim + 64;
+        const int wide = 6 * dim;
         FIP_CUDA(h->q_aug.ensure((size_t)nq * wide));
-        const int64_t tot = (int64_t)nq * wide;
-        augment_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(q_dev, nullptr, nq, dim, 1.0f, h->q_aug.p);
+        const int64_t tot = (int64_t)nq * dim;
+        split3_rows_kernel<true, float><<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(q_dev, nq, dim, h->q_aug.p);
         FIP_CUDA(cudaGetLastError());
-        int rc = search_checked(h->coarse, h->q_aug.p, nq, nprobe, h->probe_d.p, h->probe_i.p, h->stream);
+        int rc = dense_scores(h->coarse, h->q_aug.p, nq, h->ckeys.p, (uint32_t)nlist, h->stream, &launches);
         if (rc) return rc;
-        launches += 1 + (int)h->coarse->st_launches;
+        const int64_t nk = (int64_t)nq * nlist;
+        coarse_bias_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, h->stream>>>(h->ckeys.p, h->cnorm.p, nq, nlist);
+        FIP_CUDA(cudaGetLastError());
+        SelectArgs s{};
+        s.cand = h->ckeys.p; s.cnt = h->cnt.p; s.thr = h->thr.p; s.cap = (uint32_t)nlist; s.k = nprobe;
+        s.final_pass = 1; s.out_d = h->probe_d.p; s.out_i = h->probe_i.p; s.id_base = 0;
+        s.overflow = h->flags.p; s.dense_count = nlist;
+        const size_t smem = ((size_t)nlist + (size_t)next_pow2(nprobe)) * sizeof(uint64_t);
+        FIP_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        select_topk_kernel<<<nq, kSelectThreads, smem, h->stream>>>(s);
+        FIP_CUDA(cudaGetLastError());
+        launches += 3;
         h->st_coarse_tensor = 1;
-        h->st_coarse_redone = h->coarse->st_uncert + h->coarse->st_overflow;
-        // The certificate's error bound grows with max ||c'|| ~ ||c||^2: on data with large norms
-        // most queries would be redone on the exact streaming kernel.  Then the FFMA quantizer is
-        // the faster exact route: switch for good.
-        if (nq >= 8 && h->st_coarse_redone * 4 > nq) h->coarse_tensor = 0;
     } else {
         dim3 grid((nlist + ivf::CO_T - 1) / ivf::CO_T, (nq + ivf::CO_T - 1) / ivf::CO_T);
         ivf::coarse_scores_kernel<<<grid, 256, 0, h->stream>>>(q_dev, nq, h->cent.p, nlist, h->cnorm.p, dim,
@@ -1238,7 +1262,6 @@ int64_t fivf_get_stat(const fivf_index* h, const char* key) {
     if (k == "crowded_window_unresolved") return h->st_crowded_final;
     if (k == "device_plan") return h->st_device_plan;
     if (k == "coarse_tensor") return h->st_coarse_tensor;
-    if (k == "coarse_redone_queries") return h->st_coarse_redone;
     if (k == "tensor_f16") return h->st_f16;
     if (k == "scan16_ctas_per_sm") return h->st_occ16;
     return -1;
