@@ -79,7 +79,7 @@ int fivf_search_device(fivf_index* h, const float* queries_dev, int64_t nq, int3
  * "device_plan" (default 1: for batches of >= 1024 (query, probe) pairs the probe table is inverted into
  * work lists by GPU kernels and only their sizes are read back; 2: for every batch; 0: always on the
  * host, which safe mode does anyway).
- * "coarse_tensor" (1 default, nlist >= 256: the coarse quantizer runs on the tensor cores with
+ * "coarse_tensor" (1 default: batches of >= 512 queries, 2: every batch, nlist >= 256: the coarse quantizer runs on the tensor cores with
  * fp32-accurate scores -- every fp32 value split into three bf16 terms, the six significant products
  * laid side by side along K (K' = 6 dim), K1's dense mode, fp32 accumulation; 0: fp32 FFMA GEMM).
  * stats of the last search: "coarse_tensor" (1: used), "launches", "phases", "tiles", "tiles16", "rows_scanned",

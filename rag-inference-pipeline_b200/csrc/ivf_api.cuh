@@ -67,7 +67,7 @@ struct fivf_index {
     // summation order only (~1e-7 relative), like any two fp32 GEMMs.
     fip_index* coarse = nullptr;
     bool coarse_valid = false;
-    int coarse_tensor = 1;         // 0: FFMA coarse_scores_kernel (always used for assignment at add time)
+    int coarse_tensor = 1;         // 0: FFMA coarse_scores_kernel (always used for assignment at add time), 1: tensor cores for batches >= 512, 2: always
     DevBuf<float> q_aug;
     int64_t st_coarse_tensor = 0;
     cudaEvent_t ev[8] = {};   // profile: start/stop pairs around the scan launches of up to 4 phases
@@ -549,7 +549,9 @@ int fivf_run(fivf_index* h, const float* q_dev, int nq, int k, int nprobe, float
     FIP_CUDA(cudaGetLastError());
     // coarse quantizer: every centroid scored, the nprobe nearest selected (nearest first)
     h->st_coarse_tensor = 0;
-    if (h->coarse_tensor && nlist >= 256) {
+    // (measured at the reference's index shape, 4096 x 768: 2.26 vs 2.36 ms per search at B = 1024,
+    //  1.19 vs 1.17 ms at B = 32 -- the K' = 6 dim pass is latency-bound on few tiles -- hence auto = large batches)
+    if (nlist >= 256 && (h->coarse_tensor == 2 || (h->coarse_tensor == 1 && nq >= 512))) {
         // ... on the tensor cores (bf16 x 3 split, see fivf_index::coarse): dense K1 pass, bias, select
         if (!h->coarse_valid) { int rc = fivf_build_coarse(h); if (rc) return rc; }
         const int wide = 6 * dim;
@@ -1236,7 +1238,7 @@ int fivf_set_option(fivf_index* h, const char* key, int64_t value) {
     else if (k == "profile_events") h->profile = (int)value;
     else if (k == "tensor_min_queries") h->tc_min = (int)value;
     else if (k == "tensor_format") h->tensor_format = value ? 1 : 0;
-    else if (k == "coarse_tensor") h->coarse_tensor = value ? 1 : 0;
+    else if (k == "coarse_tensor") h->coarse_tensor = value < 0 ? 0 : (value > 2 ? 2 : (int)value);
     else if (k == "device_plan") h->device_plan = value < 0 ? 0 : (value > 2 ? 2 : (int)value);
     else return fail(FIP_ERR_INVALID, "unknown option " + k);
     return FIP_OK;

@@ -358,6 +358,7 @@ def test_ivf_coarse_quantizer_on_tensor_cores_matches_ffma():
         index = IVFFlatL2Index(128, 512)
         index.train(rows[:20000])
         index.add(rows)
+        index.set_option("coarse_tensor", 2)                          # every batch (auto: >= 512 queries)
         D1, I1 = _check(index, queries, 10, 32, scale=scale)
         assert index.stat("coarse_tensor") == 1
         index.set_option("coarse_tensor", 0)
@@ -365,9 +366,12 @@ def test_ivf_coarse_quantizer_on_tensor_cores_matches_ffma():
         assert index.stat("coarse_tensor") == 0
         ok = _stable_probe_rows(queries, index.centroids(), 32, scale)
         assert np.array_equal(I0[ok], I1[ok]) and np.array_equal(D0[ok], D1[ok])
-        index.set_option("coarse_tensor", 1)
+        index.set_option("coarse_tensor", 2)
         D2, I2 = index.search(queries[:1], 10, nprobe=32)           # single query
         assert index.stat("coarse_tensor") == 1
+        index.set_option("coarse_tensor", 1)
+        index.search(queries, 10, nprobe=32)
+        assert index.stat("coarse_tensor") == 0                      # auto: 300 queries stay on FFMA
         if ok[0]:
             assert np.array_equal(I2[0], I1[0])
         index.close()
