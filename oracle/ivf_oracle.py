@@ -101,8 +101,10 @@ def compare_ivf(D, I, Dr, Ir, D64r, rtol=1e-5, atol=1e-4):
     k = D.shape[1]
     gap_prev = np.full(D64r.shape, np.inf)
     gap_next = np.full(D64r.shape, np.inf)
-    gap_prev[:, 1:] = D64r[:, 1:] - D64r[:, :-1]
-    gap_next[:, :-1] = D64r[:, 1:] - D64r[:, :-1]
+    with np.errstate(invalid="ignore"):   # padding slots hold inf: inf - inf is a NaN gap, never "near"
+        diff = D64r[:, 1:] - D64r[:, :-1]
+    gap_prev[:, 1:] = diff
+    gap_next[:, :-1] = diff
     near = (np.minimum(gap_prev, gap_next)[:, :k] <= 2 * tol)
     excused = mism & near
     return {"dist_bad": dist_bad, "pad_bad": pad_bad, "id_mismatch_total": int(mism.sum()),
