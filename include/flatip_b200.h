@@ -111,6 +111,34 @@ int fip_search_status(fip_index* idx, int32_t* flagged);
 const uint32_t* fip_search_flags_device(const fip_index* idx);
 
 /*
+ * The same exact search for callers that must not touch the CUDA allocator.  No counterpart in the
+ * reference (faiss-cpu owns its own host memory); it exists because of where a drop-in GPU retriever
+ * ends up living: next to an LLM server that has already taken almost all of HBM for its KV cache
+ * (a few MB of cudaMalloc at search time then fails), or inside a serving process whose pooling
+ * allocator owns the device and bans raw cudaMalloc / cudaFree because both stall every stream of
+ * the GPU.  Such a caller keeps the corpus and the result buffers in memory it already owns and
+ * passes plain device pointers; the library's own workspace (candidate lists, thresholds, flag
+ * words) sits in ONE static __device__ array of 8 455 680 bytes (~8.1 MiB) that every GPU loading
+ * the library holds until the process exits.  The call makes no cudaMalloc / cudaFree or any other
+ * allocating CUDA call.
+ *   rows_dev      [n_rows, dim] in `dtype` (fip_dtype), row-major, 16-byte aligned, row size a
+ *                 multiple of 16 bytes, n_rows < 2^31
+ *   queries_dev   fp32 [nq, dim]; distances_dev fp32 [nq, k]; ids_dev int64 [nq, k] (id = id_base + row)
+ *   cuda_stream   cudaStream_t to run on (0 = the default stream); blocking on it
+ * Limits: nq <= 64 and k <= 2048 per call -- anything larger is refused with FIP_ERR_INVALID and a
+ * message naming the limit (split the batch, or use fip_search_device).  Results: same order, padding
+ * and bits as fip_search_device with option "variant" = FIP_VARIANT_STREAM.
+ * All calls on one GPU share the array and find the previous call's contents in it; each call
+ * resets what has to start clean.  Calls whose kernels overlapped on a GPU would corrupt each
+ * other's candidate lists, so the entry point holds a per-device lock until its stream has drained:
+ * threads of one process wait for one another.  The first call on a device also looks up the
+ * array's device address; make that call before starting any stream capture.
+ */
+int fip_search_rows_static(int32_t device, const void* rows_dev, int64_t n_rows, int32_t dim,
+                           int32_t dtype, int64_t id_base, const float* queries_dev, int64_t nq,
+                           int32_t k, float* distances_dev, int64_t* ids_dev, void* cuda_stream);
+
+/*
  * Cross-shard merge (K3): in_d / in_i are device buffers [g, nq, k_in] as an all-gather of the
  * per-shard search results leaves them (shard r holds lower ids than shard r+1); writes the
  * global best k_out per query to out_d / out_i [nq, k_out].  No faiss-cpu equivalent in the

@@ -43,6 +43,7 @@ EXPORTED_SYMBOLS = (
     "fip_group_create", "fip_group_create_weighted", "fip_calibrate_devices", "fip_group_destroy", "fip_group_size", "fip_group_shard", "fip_group_ntotal",
     "fip_group_add_synthetic", "fip_group_add_host", "fip_group_reset", "fip_group_search",
     "fip_group_set_option", "fip_group_get_stat",
+    "fip_search_rows_static",
 )
 # include/ivfflat_b200.h (IVF-Flat L2 operator, same shared library)
 IVF_EXPORTED_SYMBOLS = (
@@ -115,6 +116,9 @@ def load_library():
         lib.fip_search.restype = c.c_int
         lib.fip_search_device.argtypes = [P, P, c.c_int64, c.c_int32, P, P, P]
         lib.fip_search_device.restype = c.c_int
+        lib.fip_search_rows_static.argtypes = [c.c_int32, P, c.c_int64, c.c_int32, c.c_int32, c.c_int64, P,
+                                               c.c_int64, c.c_int32, P, P, P]
+        lib.fip_search_rows_static.restype = c.c_int
         lib.fip_merge_device.argtypes = [c.c_int32, P, P, c.c_int32, c.c_int64, c.c_int32,
                                          c.c_int32, P, P, P]
         lib.fip_merge_device.restype = c.c_int

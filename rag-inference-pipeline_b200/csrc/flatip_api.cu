@@ -1809,3 +1809,5 @@ int32_t fip_compiled_sm(void) { return 100; }
 #include "ivf_api.cuh"
 // Multi-GPU group behind one search call: include/flatip_b200.h (fip_group_*)
 #include "group_api.cuh"
+// Search with the workspace in a static device array (no allocator calls): fip_search_rows_static
+#include "static_scratch.cuh"

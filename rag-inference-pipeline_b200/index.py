@@ -154,6 +154,23 @@ def raw_rows(x: np.ndarray, dtype: str, dim: int):
     return x.ctypes.data, x.shape[0], code
 
 
+STATIC_MAX_QUERIES = 64   # fip_search_rows_static: queries per call its fixed workspace holds
+
+
+def search_rows_static(device: int, rows_ptr: int, n_rows: int, dim: int, dtype: str, q_ptr: int, nq: int,
+                       k: int, d_ptr: int, i_ptr: int, stream: int = 0, id_base: int = 0) -> None:
+    """Exact search over caller-owned device rows without a single allocator call
+    (``fip_search_rows_static``): for hosts that share the GPU with a server that has claimed all
+    of HBM, or whose own allocator forbids raw ``cudaMalloc``.  Raw device pointers in, results
+    written to ``d_ptr`` / ``i_ptr``; at most ``STATIC_MAX_QUERIES`` queries and k <= 2048 per call
+    (``FlatIPError`` otherwise).  Blocking; calls on one GPU take turns."""
+    lib = _native.load_library()
+    P = ctypes.c_void_p
+    _native.check(lib.fip_search_rows_static(
+        int(device), P(rows_ptr), int(n_rows), int(dim), _native.DTYPE_CODES[dtype], int(id_base),
+        P(q_ptr), int(nq), int(k), P(d_ptr), P(i_ptr), P(stream)))
+
+
 def merge_device(device: int, in_d_ptr: int, in_i_ptr: int, g: int, nq: int, k_in: int, k_out: int,
                  out_d_ptr: int, out_i_ptr: int, stream: int = 0) -> None:
     """K3 cross-shard merge on raw device pointers ([g, nq, k_in] -> [nq, k_out])."""
