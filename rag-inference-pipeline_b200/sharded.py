@@ -114,7 +114,16 @@ class ShardedFlatIPSearcher:
     # ------------------------------------------------------------------ device-resident path
     def search_tensor(self, queries, k: int):
         """queries: torch.float32 CUDA tensor [B, dim] (same on every rank).
-        Returns (D [B, k] float32, I [B, k] int64) CUDA tensors holding the GLOBAL result."""
+        Returns (D [B, k] float32, I [B, k] int64) CUDA tensors holding the GLOBAL result.
+
+        DEFERRED VERDICT: on a single rank and on the p2p exchange this only ENQUEUES the search on
+        the caller's stream -- the tensors are filled once that stream reaches them, and they are
+        final only if ``check()`` (one synchronisation, any time later) returns 0.  A nonzero
+        status means some search since the previous ``check()`` overflowed a candidate list or
+        could not be certified exact and has to be redone; ``search_tensor_checked`` does
+        search + check + redo in one call and is the form to use when the result is consumed
+        right away.  (``exchange="nccl"`` runs the blocking, self-checking local search: its
+        results need no ``check()``, which then returns 0.)"""
         import torch
 
         if queries.dtype != torch.float32 or not queries.is_cuda or queries.dim() != 2:

@@ -32,7 +32,8 @@ def main():
         for nq, k in [(48, 100), (1, 10), (300, 7), (48, 100), (1100, 130)]:
             q = torch.from_numpy(synthetic.synthetic_queries(nq, dim)).to(dev)
             D, I = s.search_tensor(q, k)
-            torch.cuda.synchronize()
+            status = s.check()     # deferred verdict (p2p: global, the same on every rank)
+            assert status == 0, (mode, nq, k, status)
             assert s.exchange_used == mode, (s.exchange_used, mode)
             out.append((nq, k, D.cpu().numpy(), I.cpu().numpy()))
         results[mode] = out

@@ -572,7 +572,7 @@ def test_sharded_searcher_single_rank_matches_oracle():
     s.load_synthetic(synthetic.CORPUS_SEED)
     q = synthetic.synthetic_queries(nq, dim)
     D, I = s.search_tensor(torch.from_numpy(q).cuda(), k)
-    torch.cuda.synchronize()
+    assert s.check() == 0          # search_tensor only enqueues: the verdict comes from check()
     corpus = synthetic.synthetic_corpus(0, n, dim, "f16")
     Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
     _check(D.cpu().numpy(), I.cpu().numpy(), Dr, Ir, "f16")
