@@ -54,6 +54,10 @@ struct ExchangeArgs {
     int64_t status_off;         // byte offset of the status words: [parity][source rank] u32
     const uint32_t* flags_loc;  // this rank's two summary flag words (null = clean)
     uint32_t* out_status;       // OR-accumulated: bit 0 some shard overflowed, bit 1 uncertified (null = unused)
+    int phase;                  // 0 = publish, wait, merge (the normal single launch); 1 = publish only;
+                                // 2 = wait + merge only.  1 then 2, with every rank's publish launch
+                                // finished in between, is for ranks that SHARE a device (tests, smoke):
+                                // nothing then depends on two kernels being resident together.
 };
 
 __device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
@@ -74,7 +78,7 @@ __global__ void exchange_merge_kernel(ExchangeArgs a) {
     const int64_t parity_off = (int64_t)parity * a.g * a.slot_bytes;
 
     // ---- publish: my rows q -> slot [parity][my rank] of every rank's buffer
-    for (int q = blockIdx.x; q < a.nq; q += gridDim.x) {
+    for (int q = blockIdx.x; q < a.nq && a.phase != 2; q += gridDim.x) {
         const float* src_d = a.d_loc + (size_t)q * a.k;
         const int64_t* src_i = a.i_loc + (size_t)q * a.k;
         for (int p = 0; p < a.g; ++p) {
@@ -98,6 +102,7 @@ __global__ void exchange_merge_kernel(ExchangeArgs a) {
         }
     }
 
+    if (a.phase == 1) return;
     uint8_t* mine = a.peer[a.rank];
     const int total = a.g * a.k;
     int n = 1;

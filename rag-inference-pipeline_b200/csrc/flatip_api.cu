@@ -1559,7 +1559,7 @@ int fip_merge_device(int32_t device, const float* in_d, const int64_t* in_i, int
 struct fip_exchange {
     int device = 0, world = 1, rank = 0, nq_max = 0, k_max = 0;
     int64_t slot_bytes = 0, flags_off = 0, status_off = 0, total_bytes = 0;
-    int resident_ctas[12] = {};   // per log2(block threads): co-resident CTAs of the kernel (0 = not queried)
+    int resident_ctas[16] = {};   // per log2(merged list length): co-resident CTAs of the kernel (0 = not queried)
     int share = 1;                // ranks of the group living on THIS device (tests): they split the residency
     uint8_t* local = nullptr;
     uint8_t* peer[kMaxRanks] = {};
@@ -1654,9 +1654,10 @@ int fip_exchange_merge(fip_exchange* x, const float* d_loc, const int64_t* i_loc
     return fip_exchange_merge_status(x, d_loc, i_loc, nq, k, out_d, out_i, nullptr, nullptr, cuda_stream);
 }
 
-int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
-                              float* out_d, int64_t* out_i, const uint32_t* flags_loc_dev,
-                              uint32_t* out_status_dev, void* cuda_stream) {
+// phase: ExchangeArgs::phase.  0 and 1 open a new epoch, 2 finishes the one its phase-1 launch opened.
+static int exchange_launch(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
+                           float* out_d, int64_t* out_i, const uint32_t* flags_loc_dev,
+                           uint32_t* out_status_dev, void* cuda_stream, int phase) {
     if (!x || (nq > 0 && (!d_loc || !i_loc || !out_d || !out_i))) return fail(FIP_ERR_INVALID, "null argument");
     if (nq < 0 || nq > x->nq_max || k < 1 || k > x->k_max)
         return fail(FIP_ERR_INVALID, "nq / k exceed what the exchange was created for");
@@ -1665,24 +1666,29 @@ int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t
     std::lock_guard<std::mutex> lock(x->mu);
     // every rank makes the same sequence of calls (like a collective), so the epoch advances in
     // lock-step and consecutive launches alternate buffer parity
-    x->epoch++;
-    if (x->epoch == 0) x->epoch = 2;  // wrapped (0xFFFFFFFF -> 2 keeps the parity alternating); 0 = "never written"
+    // (committed only once the kernel has been launched: a call that fails before that must not
+    // leave this rank one epoch ahead of its peers)
+    uint32_t epoch = phase == 2 ? x->epoch : x->epoch + 1;
+    if (epoch == 0) epoch = 2;  // wrapped (0xFFFFFFFF -> 2 keeps the parity alternating); 0 = "never written"
     FIP_CUDA(cudaSetDevice(x->device));
     ExchangeArgs a{};
     for (int r = 0; r < x->world; ++r) a.peer[r] = x->peer[r];
-    a.g = x->world; a.rank = x->rank; a.nq = (int)nq; a.k = k; a.epoch = x->epoch;
+    a.g = x->world; a.rank = x->rank; a.nq = (int)nq; a.k = k; a.epoch = epoch;
     a.slot_bytes = x->slot_bytes; a.flags_off = x->flags_off; a.nq_max = x->nq_max;
     a.off_i = (int)round_up16(nq * k * 4);
     a.d_loc = d_loc; a.i_loc = i_loc; a.out_d = out_d; a.out_i = out_i;
     a.status_off = x->status_off; a.flags_loc = flags_loc_dev; a.out_status = out_status_dev;
+    a.phase = phase;
     const int n = next_pow2(x->world * k);
     const size_t smem = (size_t)n * sizeof(uint64_t);
     FIP_CUDA(cudaFuncSetAttribute(exchange_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)std::max<size_t>(smem, 1024)));
     const int threads = std::min(1024, std::max(64, n / 2));
     // grid bounded by what is resident at once (every CTA loops over its queries)
+    // (cached per list length n: n fixes both the CTA size and its shared memory, and with 1024
+    // threads the shared memory alone decides between 2 CTAs per SM and 1)
     int lg = 0;
-    while ((1 << lg) < threads) lg++;
+    while ((1 << lg) < n) lg++;
     if (!x->resident_ctas[lg]) {
         int per_sm = 0, sms = 0;
         FIP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, exchange_merge_kernel, threads, smem));
@@ -1692,7 +1698,14 @@ int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t
     const unsigned grid = (unsigned)std::min<int64_t>(nq, std::max(1, x->resident_ctas[lg] / x->share));
     exchange_merge_kernel<<<grid, threads, smem, (cudaStream_t)cuda_stream>>>(a);
     FIP_CUDA(cudaGetLastError());
+    x->epoch = epoch;
     return FIP_OK;
+}
+
+int fip_exchange_merge_status(fip_exchange* x, const float* d_loc, const int64_t* i_loc, int64_t nq, int32_t k,
+                              float* out_d, int64_t* out_i, const uint32_t* flags_loc_dev,
+                              uint32_t* out_status_dev, void* cuda_stream) {
+    return exchange_launch(x, d_loc, i_loc, nq, k, out_d, out_i, flags_loc_dev, out_status_dev, cuda_stream, 0);
 }
 
 void fip_exchange_destroy(fip_exchange* x) {

@@ -24,6 +24,7 @@
 //   local searches on the host (redo of the flagged queries) and exchange + merge once more.
 #pragma once
 
+#include <atomic>
 #include <chrono>
 #include <functional>
 #include <thread>
@@ -65,6 +66,7 @@ struct fip_group {
     std::mutex mu;      // serialises group operations
     Coalescer co;
     int dedupe = 1;     // 0 off, 1 coalesced batches, 2 always (every rank dedupes its own copy of the batch)
+    std::atomic<int> debug_fail_rank{0};   // testing: r + 1 = rank r fails its next local part (once)
     int64_t st_flagged_searches = 0, st_exchange_launches = 0, st_searches = 0;
 };
 
@@ -154,9 +156,17 @@ int group_ensure_exchange(fip_group* g, int nq, int k) {
 }
 
 // One rank's share of a group search (runs on that rank's worker thread).  second = the exchange
-// is repeated after flagged queries were redone on the host.  stage: 0 = everything; 1 = local
-// search only, synchronised; 2 = exchange onwards (1 then 2 = the shared-device test configuration,
-// where a spinning exchange kernel must not hold the SMs another shard's search still needs).
+// is repeated after flagged queries were redone on the host.  stage: 0 = everything (single
+// device); 1 = the local part: every allocation this search needs, H2D, dedupe, the search
+// enqueued (synchronised only in the shared-device test configuration, where a spinning exchange
+// kernel must not hold the SMs another shard's search still needs); 2 = exchange onwards;
+// 3 = publish launch of the exchange only, synchronised, and 4 = its wait + merge launch onwards:
+// 1, 3, 4 is the shared-device sequence, in which no kernel ever waits for a kernel that has not
+// finished yet (so it also completes when a profiler serialises every launch).
+// Several devices always run 1 then 2 as two rounds over the workers (run_group_batch): the K4
+// kernels wait for one another on the GPUs, so a rank may launch its own only once EVERY rank is
+// known to have got through the part that can fail (out of memory, a bad launch), and no
+// cudaMalloc / cudaFree happens on any rank while a peer's exchange kernel may be resident.
 int group_rank_search(fip_group* g, int r, int nq, int k, bool second, bool dedupe, int stage = 0) {
     fip_index* idx = g->shard[r];
     fip_group::Rank& R = g->ranks[r];
@@ -164,15 +174,19 @@ int group_rank_search(fip_group* g, int r, int nq, int k, bool second, bool dedu
     FIP_CUDA(cudaSetDevice(g->devices[r]));
     const size_t qn = (size_t)nq * g->dim, on = (size_t)nq * k;
     const bool multi = g->world > 1;
-    if (stage == 2) {
+    if (stage >= 2) {
         // stage 1 already ran the local part
     } else if (!second) {
+        int want = r + 1;
+        if (g->debug_fail_rank.compare_exchange_strong(want, 0))
+            return fail(FIP_ERR_CUDA, "injected failure of the local part (option debug_fail_rank)");
         FIP_CUDA(R.q32.ensure(qn));
         FIP_CUDA(R.loc_d.ensure(on));
         FIP_CUDA(R.loc_i.ensure(on));
         if (multi) { FIP_CUDA(R.out_d.ensure(on)); FIP_CUDA(R.out_i.ensure(on)); }
         FIP_CUDA(R.status.ensure(1));
         FIP_CUDA(R.h_status.ensure(1));
+        if (r == 0 && dedupe) { FIP_CUDA(R.fin_d.ensure(on)); FIP_CUDA(R.fin_i.ensure(on)); }
         FIP_CUDA(cudaMemcpyAsync(R.q32.p, g->h_q.p, qn * sizeof(float), cudaMemcpyHostToDevice, R.stream));
         // bit-identical queries are searched once: every rank reduces its own copy of the batch
         // (same deterministic result everywhere, nothing to communicate)
@@ -193,16 +207,23 @@ int group_rank_search(fip_group* g, int r, int nq, int k, bool second, bool dedu
         if (rc) return rc;
     }
     if (stage == 1) {
+        if (g->shared_device) FIP_CUDA(cudaStreamSynchronize(R.stream));
+        return FIP_OK;
+    }
+    const int nd = R.nd;
+    if (stage == 3) {
+        int rc = exchange_launch(g->xchg[r], R.loc_d.p, R.loc_i.p, nd, k, R.out_d.p, R.out_i.p, idx->overflow.p,
+                                 R.status.p, R.stream, 1);
+        if (rc) return rc;
         FIP_CUDA(cudaStreamSynchronize(R.stream));
         return FIP_OK;
     }
     FIP_CUDA(cudaMemsetAsync(R.status.p, 0, sizeof(uint32_t), R.stream));
     const float* fin_d = R.loc_d.p;
     const int64_t* fin_i = R.loc_i.p;
-    const int nd = R.nd;
     if (multi) {
-        int rc = fip_exchange_merge_status(g->xchg[r], R.loc_d.p, R.loc_i.p, nd, k, R.out_d.p, R.out_i.p,
-                                           idx->overflow.p, R.status.p, R.stream);
+        int rc = exchange_launch(g->xchg[r], R.loc_d.p, R.loc_i.p, nd, k, R.out_d.p, R.out_i.p, idx->overflow.p,
+                                 R.status.p, R.stream, stage == 4 ? 2 : 0);
         if (rc) return rc;
         fin_d = R.out_d.p; fin_i = R.out_i.p;
         FIP_CUDA(cudaMemcpyAsync(R.h_status.p, R.status.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, R.stream));
@@ -247,10 +268,19 @@ int run_group_batch(fip_group* g, const std::vector<HostRequest*>& batch) {
     if (rc) return rc;
     const bool dd = g->dedupe == 2 || (g->dedupe == 1 && batch.size() > 1);
     auto all_ranks = [&](bool second) -> int {
-        if (!g->shared_device) return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd); });
-        int rc1 = group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 1); });
-        if (rc1) return rc1;
-        return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 2); });
+        if (g->world == 1) return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd); });
+        const int rc1 = group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 1); });
+        if (rc1) {
+            // some rank failed before the exchange: NO rank launches it (the epochs stay in step,
+            // nothing spins).  Drain what the others enqueued: their H2D copies read g->h_q.
+            const std::string why = g_last_error;
+            group_run(g, [g](int r) { cudaStreamSynchronize(g->ranks[r].stream); cudaGetLastError(); return 0; });
+            return fail(rc1, why);
+        }
+        if (!g->shared_device) return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 2); });
+        const int rc3 = group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 3); });
+        if (rc3) return rc3;
+        return group_run(g, [g, nq, k, second, dd](int r) { return group_rank_search(g, r, nq, k, second, dd, 4); });
     };
     rc = all_ranks(false);
     if (rc) return rc;
@@ -404,6 +434,30 @@ int32_t fip_group_size(const fip_group* g) { return g ? g->world : 0; }
 fip_index* fip_group_shard(fip_group* g, int32_t r) { return (g && r >= 0 && r < g->world) ? g->shard[r] : nullptr; }
 int64_t fip_group_ntotal(const fip_group* g) { return g ? group_ntotal(g) : 0; }
 
+namespace {
+// An add that failed on one shard after others had succeeded would leave the sum of the shards'
+// rows out of step with bound[] (later rows routed to the wrong shard, wrong ids): put every shard
+// back to the row count it had before the call.  The appended rows stay in the allocation, unused.
+int group_add_rollback(fip_group* g, const std::vector<int64_t>& before, int rc) {
+    const std::string why = g_last_error;
+    for (int r = 0; r < g->world; ++r) {
+        fip_index* idx = g->shard[r];
+        std::lock_guard<std::mutex> l(idx->mu);
+        if (idx->n_rows != before[r]) {
+            idx->n_rows = before[r];
+            idx->tmap_x_valid = false;
+            idx->corpus_gen++;
+        }
+    }
+    return fail(rc, why + " (group unchanged: rows other shards had already taken were dropped again)");
+}
+std::vector<int64_t> group_rows_now(const fip_group* g) {
+    std::vector<int64_t> v;
+    for (auto* s : g->shard) v.push_back(s->n_rows);
+    return v;
+}
+}  // namespace
+
 int fip_group_add_synthetic(fip_group* g, int64_t n, uint64_t seed) {
     if (!g || n < 0) return fail(FIP_ERR_INVALID, "bad argument");
     if (n == 0) return FIP_OK;
@@ -411,11 +465,16 @@ int fip_group_add_synthetic(fip_group* g, int64_t n, uint64_t seed) {
     const int64_t g0 = group_ntotal(g);
     const int64_t base = g->shard[0]->cfg.id_base;
     const auto pieces = group_route(g, g0, n);
-    return group_run(g, [g, pieces, seed, g0, base](int r) {
+    const auto before = group_rows_now(g);
+    const int rc = group_run(g, [g, pieces, seed, g0, base](int r) {
+        int want = r + 1;
+        if (g->debug_fail_rank.compare_exchange_strong(want, 0))
+            return fail(FIP_ERR_NOMEM, "injected failure of the add (option debug_fail_rank)");
         for (const auto& p : pieces)
             if (p.r == r) return fip_add_synthetic(g->shard[r], p.count, seed, base + g0 + p.first);
         return (int)FIP_OK;
     });
+    return rc ? group_add_rollback(g, before, rc) : FIP_OK;
 }
 
 int fip_group_add_host(fip_group* g, const void* rows, int64_t n, int32_t dtype) {
@@ -425,12 +484,14 @@ int fip_group_add_host(fip_group* g, const void* rows, int64_t n, int32_t dtype)
     const int64_t g0 = group_ntotal(g);
     const auto pieces = group_route(g, g0, n);
     const size_t src_row = (size_t)g->dim * dtype_size(dtype);
-    return group_run(g, [g, pieces, rows, dtype, src_row](int r) {
+    const auto before = group_rows_now(g);
+    const int rc = group_run(g, [g, pieces, rows, dtype, src_row](int r) {
         for (const auto& p : pieces)
             if (p.r == r)
                 return fip_add_host(g->shard[r], (const char*)rows + (size_t)p.first * src_row, p.count, dtype);
         return (int)FIP_OK;
     });
+    return rc ? group_add_rollback(g, before, rc) : FIP_OK;
 }
 
 int fip_group_reset(fip_group* g) {
@@ -464,6 +525,11 @@ int fip_group_set_option(fip_group* g, const char* key, int64_t value) {
         g->co.max_batch = value;
         return FIP_OK;
     }
+    if (k == "debug_fail_rank") {   // tests: shard `value - 1` fails the local part of its next search
+        if (value < 0 || value > g->world) return fail(FIP_ERR_INVALID, "debug_fail_rank must be in [0, devices]");
+        g->debug_fail_rank = (int)value;
+        return FIP_OK;
+    }
     for (auto* s : g->shard) { int rc = fip_set_option(s, key, value); if (rc) return rc; }
     return FIP_OK;
 }
@@ -494,6 +560,10 @@ int fip_calibrate_devices(const int32_t* devices, int32_t n_devices, int32_t dim
                 if (rc) return rc;
                 DevBuf<float> q, d;
                 DevBuf<int64_t> i;
+                struct Scratch {   // released on every way out of this body
+                    DevBuf<float>&q, &d; DevBuf<int64_t>& i;
+                    ~Scratch() { q.release(); d.release(); i.release(); }
+                } scratch{q, d, i};
                 FIP_CUDA(q.ensure((size_t)batch * dim));
                 FIP_CUDA(d.ensure((size_t)batch * k));
                 FIP_CUDA(i.ensure((size_t)batch * k));
@@ -519,7 +589,6 @@ int fip_calibrate_devices(const int32_t* devices, int32_t n_devices, int32_t dim
                     first = false;
                     if (el > seconds) break;
                 }
-                q.release(); d.release(); i.release();
                 if (rc) return rc;
                 rates[r] = scan_ms > 0.0 ? (double)rows * (double)searches / (scan_ms * 1e-3) : 0.0;
                 return FIP_OK;

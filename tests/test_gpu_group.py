@@ -132,6 +132,40 @@ def test_group_redoes_flagged_queries_and_exchanges_again(shared_device):
     g.close()
 
 
+def test_group_survives_a_rank_that_fails_before_the_exchange(shared_device):
+    """One shard fails its local part (injected; in production: out of memory, a bad launch).  No
+    rank may then launch the exchange kernel -- the others would wait 30 s for the missing rows and
+    trap -- so the call must come back at once with the error, and because the exchange epochs stay
+    in step the NEXT search of the same group is correct."""
+    import time
+    from rag_inference_pipeline_b200._native import FlatIPError
+    from rag_inference_pipeline_b200.group import FlatIPGroup
+    dim, n, nq, k, dtype = 128, 40_000, 20, 10, "f16"
+    q = synthetic.synthetic_queries(nq, dim)
+    corpus = synthetic.synthetic_corpus(0, n, dim, dtype)
+    Dr, Ir = flatip_oracle.flat_ip_search(q, corpus, k)
+    g = FlatIPGroup(dim, dtype, [0, 0, 0], n)
+    # an add that fails on ONE shard leaves the group as it was (no shard keeps its share)
+    g.set_option("debug_fail_rank", 2)
+    with pytest.raises(FlatIPError, match="group unchanged"):
+        g.add_synthetic(n, synthetic.CORPUS_SEED)
+    assert g.ntotal == 0 and [g.shard(r).ntotal for r in range(3)] == [0, 0, 0]
+    g.add_synthetic(n, synthetic.CORPUS_SEED)
+    assert g.ntotal == n
+    D, I = g.search(q, k)
+    for failing in (1, 0, 2):
+        g.set_option("debug_fail_rank", failing + 1)
+        t0 = time.time()
+        with pytest.raises(FlatIPError, match="injected failure"):
+            g.search(q, k)
+        assert time.time() - t0 < 5.0
+        D2, I2 = g.search(q, k)
+        assert np.array_equal(I2, I) and np.array_equal(D2, D)
+    res = flatip_oracle.compare_with_oracle(D, I, Dr, Ir, rtol=SCORE_RTOL[dtype])
+    assert res["score_ok"] and res["id_mismatch_outside_window"] == 0, res
+    g.close()
+
+
 def test_group_coalesces_concurrent_callers(shared_device):
     from rag_inference_pipeline_b200.group import FlatIPGroup
     dim, n, k = 64, 20_000, 5
