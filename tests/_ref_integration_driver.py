@@ -8,7 +8,9 @@ its third-party imports (faiss, lz4, orjson, zstandard, sentence_transformers, o
 instrumentation) are absent from this image and have to be stubbed in sys.modules first
 (SURVEY.md Appendix C.3).  No GPU in the build container: with --backend oracle the store's native
 index is replaced by an oracle-backed stand-in (TEST ONLY); with --backend native the real CUDA
-library is used (needs a B200 and /root/reference on the same box).
+library is used (on the B200 box the reference comes from baseline/_ref/, see REF_SRC).
+--devices 0,0 puts the corpus behind a two-shard group; --cache on runs the reference's LRU path
+(api.py:392-425) and sends every request twice, so the second round is answered from its cache.
 """
 import argparse
 import asyncio
@@ -21,7 +23,11 @@ import types
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
-REF_SRC = "/root/reference/src"
+# The reference's sources: where they are mounted in the build container, else the untracked,
+# read-only copy __graft_entry__.build() stages under baseline/_ref/ (git-ignored; it travels to the
+# GPU box with the snapshot like the built .so does).
+REF_SRC = next((p for p in ("/root/reference/src", os.path.join(ROOT, "baseline", "_ref", "src"))
+                if os.path.isdir(os.path.join(p, "pipeline"))), "/root/reference/src")
 
 
 def install_stubs():
@@ -106,7 +112,11 @@ async def run(args):
 
     os.environ.update({"NODE_NUMBER": "1", "FAISS_INDEX_PATH": path, "faiss_dim": str(dim),
                        "retrieval_k": str(k), "retrieval_batch_size": str(args.batch),
-                       "retrieval_max_batch_delay_ms": "20", "DISABLE_CACHE_FOR_PROFILING": "true"})
+                       "retrieval_max_batch_delay_ms": "20",
+                       "DISABLE_CACHE_FOR_PROFILING": "false" if args.cache == "on" else "true"})
+    devices = [int(v) for v in args.devices.split(",")] if args.devices not in ("", "none") else None
+    if devices and len(set(devices)) < len(devices):
+        os.environ["FLATIP_B200_ALLOW_SHARED_DEVICE"] = "1"   # one-GPU box: both shards on cuda:0
     install_stubs()
     sys.path.insert(0, REF_SRC)
     from pipeline import component_factory
@@ -124,7 +134,9 @@ async def run(args):
                                           index_io.read_header(str(self.index_path)))))
     # 1. the reference's factory map now builds the B200 store for type "faiss"
     install(component_factory.COMPONENT_FACTORIES)
-    store = component_factory.create_component(ComponentType.FAISS, settings, {})
+    assert bool(getattr(settings, "disable_cache_for_profiling", True)) == (args.cache != "on")
+    store = component_factory.create_component(ComponentType.FAISS, settings,
+                                               {"devices": devices} if devices else {})
     assert isinstance(store, B200FlatIPStore)
     # 2. the reference's registry runs load() through its load hook
     registry = ComponentRegistry()
@@ -136,18 +148,39 @@ async def run(args):
     queries = synthetic.synthetic_queries(nreq, dim)
     items = [RetrievalRequestItem(request_id=f"r{i}", query="q", embedding=queries[i].tolist())
              for i in range(nreq)]
-    responses = await asyncio.gather(*[executor.process_request(it) for it in items])
-    await executor.stop()
+    calls = []
+    real_search = store.search
+
+    def counting_search(x, kk):
+        calls.append(int(len(x)))
+        return real_search(x, kk)
+
+    store.search = counting_search
     Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k)
-    ids_ok = all([d.doc_id for d in r.docs] == Ir[i].tolist() for i, r in enumerate(responses))
-    max_err = max(abs(d.score - float(Dr[i, j])) for i, r in enumerate(responses)
-                  for j, d in enumerate(r.docs))
-    order_ok = all(r.request_id == f"r{i}" for i, r in enumerate(responses))
+    ids_ok, order_ok, max_err, total = True, True, 0.0, 0
+    rounds = 2 if args.cache == "on" else 1
+    searched = []
+    for _ in range(rounds):
+        before = sum(calls)
+        responses = await asyncio.gather(*[executor.process_request(it) for it in items])
+        searched.append(sum(calls) - before)
+        total += len(responses)
+        ids_ok &= all([d.doc_id for d in r.docs] == Ir[i].tolist() for i, r in enumerate(responses))
+        # north_star's fp32 rule: 1e-5 relative (to max(1, |score|)); reported in those units x 1e-5 .. 1e-4
+        max_err = max(max_err, max(abs(d.score - float(Dr[i, j])) / max(1.0, abs(float(Dr[i, j]))) * 10.0
+                                   for i, r in enumerate(responses) for j, d in enumerate(r.docs)))
+        order_ok &= all(r.request_id == f"r{i}" for i, r in enumerate(responses))
+    await executor.stop()
+    # cache on: the second round must have been answered by the reference's LRU, not by a search
+    cache_ok = args.cache != "on" or (searched[0] == nreq and searched[1] == 0)
     registry.unload_all()
-    print(json.dumps({"ok": bool(ids_ok and order_ok and max_err < 1e-4), "ids_ok": bool(ids_ok),
-                      "max_score_err": max_err, "responses": len(responses),
+    print(json.dumps({"ok": bool(ids_ok and order_ok and cache_ok and max_err < 1e-4), "ids_ok": bool(ids_ok),
+                      "max_score_err": max_err, "responses": total, "search_calls": len(calls),
+                      "largest_batch": max(calls), "queries_searched_per_round": searched,
                       "docs_per_response": len(responses[0].docs), "unloaded": not store.is_loaded,
-                      "backend": args.backend}))
+                      "backend": args.backend, "devices": devices, "cache": args.cache,
+                      "store": type(store).__name__, "group": bool(devices and len(devices) > 1),
+                      "reference_src": REF_SRC}))
 
 
 if __name__ == "__main__":
@@ -158,4 +191,6 @@ if __name__ == "__main__":
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--requests", type=int, default=70)
     ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--devices", default="none", help="'none' or a device list such as 0,0 / 0,1")
+    ap.add_argument("--cache", choices=["off", "on"], default="off")
     asyncio.run(run(ap.parse_args()))

@@ -340,6 +340,10 @@ def test_in_batch_duplicates_are_searched_once(shared_device, sharded):
         idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
     base = synthetic.synthetic_queries(24, dim)
     Dref, Iref = idx.search(base, k)
+    # the expected rows are themselves checked against the CPU oracle, not only against the CUDA path
+    Dor, Ior = flatip_oracle.flat_ip_search(base, synthetic.synthetic_corpus(0, n, dim, "f16"), k)
+    res = flatip_oracle.compare_with_oracle(Dref, Iref, Dor, Ior, rtol=SCORE_RTOL["f16"])
+    assert res["score_ok"] and res["id_mismatch_outside_window"] == 0, res
     # one call with internal duplicates: only searched once each when dedupe = 2 ("always")
     mixed = base[[0, 5, 0, 7, 5, 5, 23, 0]]
     tweaked = mixed.copy()
@@ -392,4 +396,7 @@ def test_weighted_shards_and_calibration(shared_device):
     assert [g.shard(r).ntotal for r in range(3)] == [bounds[r + 1] - bounds[r] for r in range(3)]
     D, I = g.search(q, k)
     assert np.array_equal(I, Is) and np.array_equal(D, Ds)
+    Dor, Ior = flatip_oracle.flat_ip_search(q, synthetic.synthetic_corpus(0, n, dim, "f16"), k)
+    res = flatip_oracle.compare_with_oracle(D, I, Dor, Ior, rtol=SCORE_RTOL["f16"])
+    assert res["score_ok"] and res["id_mismatch_outside_window"] == 0, res
     g.close()

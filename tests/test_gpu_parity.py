@@ -87,7 +87,39 @@ CASES = [
     ("tensor", "f32", 33333, 96, 150, 100),     # fp32, dim % 32 == 0 only, two query tiles (CTA pair)
     ("tensor", "f16", 30000, 768, 1000, 100),   # 8 query tiles: CTA-pair kernel, ragged last tile
     ("tensor", "bf16", 25000, 128, 900, 50),    # 8 tiles (7 padded to 8), bf16 hi+lo terms, pair
+    ("tensor", "f16", 20000, 256, 2048, 100),   # 16 query tiles (the sweep's B = 2048)
+    ("tensor", "bf16", 15000, 128, 4096, 10),   # 32 query tiles (the sweep's B = 4096)
+    ("tensor", "f16", 20000, 128, 127, 10),     # one tile, one row short
+    ("tensor", "f16", 20000, 128, 129, 10),     # two tiles, the second holds one query
+    ("tensor", "bf16", 20000, 128, 255, 10),    # two tiles (CTA pair), one row short
+    ("tensor", "bf16", 20000, 128, 257, 10),    # three tiles: no pair
 ]
+
+# Both sides of every switch of the AUTO rule (flatip_api.cu run_search): 16-bit storage streams
+# only a single query, fp32 storage without the filter copy streams up to four.
+AUTO_CASES = [
+    # dtype, dim, nq, filter_copy, expected variant
+    ("bf16", 512, 1, 1, "stream"), ("bf16", 512, 2, 1, "tensor"),
+    ("f16", 512, 1, 1, "stream"), ("f16", 512, 2, 1, "tensor"),
+    ("f32", 256, 4, 0, "stream"), ("f32", 256, 5, 0, "tensor"),
+    ("f32", 256, 1, 1, "tensor"),
+]
+
+
+@pytest.mark.parametrize("dtype,dim,nq,filter_copy,expect", AUTO_CASES)
+def test_auto_variant_switch_points_match_oracle(dtype, dim, nq, filter_copy, expect):
+    n, k = 30000, 20
+    corpus = c_oracle.synthetic_corpus(0, n, dim, dtype)
+    queries = synthetic.synthetic_queries(nq, dim)
+    Dr, Ir = flatip_oracle.flat_ip_search(queries, corpus, k + 1)
+    idx = _index(dim, dtype)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    if dtype == "f32":
+        idx.set_option("filter_copy", filter_copy)
+    D, I = idx.search(queries, k)
+    assert idx.last_variant() == expect
+    _check(D, I, Dr[:, :k], Ir[:, :k], dtype, Dr[:, k])
+    idx.close()
 
 
 @pytest.mark.parametrize("variant,dtype,n,dim,nq,k", CASES)
@@ -485,6 +517,10 @@ def test_concurrent_callers_are_coalesced_into_one_batch():
     idx.set_option("coalesce", 0)
     serial = [idx.search(q, k) for q in qs]
     assert idx.stat("coalesced_calls") == 0
+    # what the coalesced calls are compared with is itself checked against the CPU oracle
+    Dr, Ir = _c_oracle_chunked(np.concatenate(qs), 0, n, dim, "f16", k + 1, 1_000_000)
+    _check(np.concatenate([s[0] for s in serial]), np.concatenate([s[1] for s in serial]),
+           Dr[:, :k], Ir[:, :k], "f16", Dr[:, k])
     idx.set_option("coalesce", 1)
     errors = []
     start = threading.Barrier(nthreads)
@@ -778,6 +814,20 @@ def test_cfg3_shard_full_size():
     assert I.min() >= row0 and I.max() < row0 + n
     idx.close()
     Dr, Ir = _c_oracle_chunked(q, row0, n, dim, "f16", k + 1, 2_500_000)
+    _check_full(D, I, Dr, Ir, k)
+
+
+def test_cfg4_full_size():
+    """BASELINE configs[3] in full at the largest batch the sweep quotes a roofline fraction for:
+    10 M x 768 bf16, batch 1024, k = 100, against the C port over the same rows."""
+    dim, n, nq, k = 768, 10_000_000, 1024, 100
+    q = synthetic.synthetic_queries(nq, dim)
+    idx = _index(dim, "bf16", capacity_rows=n)
+    idx.add_synthetic(n, synthetic.CORPUS_SEED, 0)
+    D, I = idx.search(q, k)
+    assert idx.last_variant() == "tensor" and idx.stat("overflow_queries") == 0
+    idx.close()
+    Dr, Ir = _c_oracle_chunked(q, 0, n, dim, "bf16", k + 1, 2_500_000)
     _check_full(D, I, Dr, Ir, k)
 
 

@@ -155,6 +155,30 @@ def test_search_passes_through_and_casts(tmp_path):
     assert isinstance(i[0].tolist()[0], int) and isinstance(d[0].tolist()[0], float)
 
 
+def test_search_k_outside_the_library_limit_is_a_value_error(tmp_path):
+    """faiss takes any k, this library stops at 2048: the store says so with the exception type the
+    retrieval service treats as a bad request, before the native layer is reached."""
+    store = _loaded_store(tmp_path)
+    x = np.random.rand(2, 768).astype("float32")
+    for bad in (0, -1, 2049, 10.0, True):
+        with pytest.raises(ValueError, match=r"k must be an integer in \[1, 2048\]"):
+            store.search(x, k=bad)
+    d, i = store.search(x, k=2048)
+    assert i.shape == (2, 2048)
+    assert store.search(x, k=np.int64(7))[1].shape == (2, 7)
+
+
+def test_search_lists_equals_the_callers_per_row_loop(tmp_path):
+    """api.py:390 builds ``[row.tolist() for row in indices], [row.tolist() for row in distances]``;
+    search_lists returns the same nested lists (same Python types) from one tolist() per matrix."""
+    store = _loaded_store(tmp_path)
+    x = np.random.rand(5, 768).astype("float32")
+    distances, indices = store.search(x, 6)
+    ids, dists = store.search_lists(x, 6)
+    assert ids == [row.tolist() for row in indices] and dists == [row.tolist() for row in distances]
+    assert type(ids[0][0]) is int and type(dists[0][0]) is float
+
+
 def test_unload_and_is_loaded(tmp_path):
     store = _loaded_store(tmp_path)
     assert store.is_loaded and store.index_size == 10
