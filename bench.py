@@ -398,21 +398,28 @@ def run_b200(args, rank, local_rank, world):
         for r_ in range(1, world):      # rows on both sides of every shard boundary
             b_, _ = shard_range(total_rows, r_, world, weights)
             starts.add(max(0, min(total_rows - blk, b_ - blk // 2)))
+        # ... plus 1024-row blocks at seeded random places, 64 blocks in all:
+        # the structural blocks alone covered 0.01-0.04 % of the corpus and only its edges
+        blocks = [(b0, blk) for b0 in sorted(starts)]
+        small = min(1024, total_rows)
+        pick = np.random.default_rng(20240607)
+        while len(blocks) < 64 and total_rows > small:
+            blocks.append((int(pick.integers(0, total_rows - small + 1)), small))
         missed = 0
         rows_checked = 0
         kth = Dh[:, -1].astype(np.float64)
         margin = tol * np.maximum(1.0, np.abs(kth))
-        for b0 in sorted(starts):
-            xb = synthetic_corpus(b0, blk, dim, dtype).astype(np.float32)
-            sc = (q_np @ xb.T).astype(np.float64)                 # [batch, blk]
-            rows_checked += blk
+        for b0, nb in blocks:
+            xb = synthetic_corpus(b0, nb, dim, dtype).astype(np.float32)
+            sc = (q_np @ xb.T).astype(np.float64)                 # [batch, nb]
+            rows_checked += nb
             better = sc > (kth + margin)[:, None]
             for qi, ci in zip(*np.nonzero(better)):
                 if (b0 + int(ci)) not in set(Ih[qi].tolist()):
                     missed += 1
         verify = {"sorted": ok_sorted, "ids_in_range": ok_range, "ids_distinct_per_row": ok_distinct,
                   "max_abs_err_of_9_recomputed_scores": max(errs),
-                  "h5_blocks": len(starts), "h5_rows_regenerated": rows_checked,
+                  "h5_blocks": len(blocks), "h5_rows_regenerated": rows_checked,
                   "h5_rows_missed": missed,
                   "ids_sha256": hashlib.sha256(np.ascontiguousarray(Ih).tobytes()).hexdigest(),
                   "distances_sha256": hashlib.sha256(np.ascontiguousarray(Dh).tobytes()).hexdigest(),
