@@ -1,9 +1,10 @@
 """The reference's ONLY caller of the path, driven against the CUDA store on the GPU box.
 
-`/root/reference` does not travel to the GPU box, so the reference's own RetrievalExecutor cannot
-run there (tests/test_reference_integration.py drives it here, on CPU, against the oracle-backed
-store).  What CAN run next to the kernels is the caller's contract, restated from
-``/root/reference/src/pipeline/services/retrieval/api.py``:
+FALLBACK for a box without the staged reference: tests/test_gpu_reference_caller.py runs the
+reference's real RetrievalExecutor / BatchScheduler / ComponentRegistry against the CUDA store
+(from the untracked copy under baseline/_ref/).  This file keeps the caller's contract restated by
+hand from ``/root/reference/src/pipeline/services/retrieval/api.py``, so the same properties are
+still checked where that copy is absent:
 
   * ``:383``      the store is looked up as ``registry.get("faiss_store")`` (factory.install);
   * ``:348-349``  ``_process_batch_sync`` runs on ``loop.run_in_executor(None, ...)`` threads, several
